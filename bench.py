@@ -1,0 +1,197 @@
+#!/usr/bin/env python
+"""Headline benchmark: word2vec skip-gram negative-sampling training throughput (words/sec)
+on the parameter server — BASELINE.json config 2 (synthetic Zipf corpus, vocab 1M, dim 128).
+
+    python bench.py --gpus N --steps K --warmup W            # ours (N>1: launched by torchrun)
+    python bench.py --impl reference --gpus N ...             # the reference's ZeroMQ CPU build
+
+One rank per GPU hosts server shard g and worker g.  Weak scaling: every worker consumes
+``--tokens-per-step`` tokens per step.  Timing: CUDA events around exactly K steps after W
+warm-up steps, barrier + synchronize on both sides, max over ranks.  ``value`` is the
+device-timed number with the token batches already resident on the device; ``e2e`` runs the
+same K steps through the public ``Word2VecTrainer`` API including, every step, the H2D copy of
+the step's token batch from pinned host memory and the D2H read of the step's loss.
+The 1 GiB+ table is larger than L2 (126 MB), so no explicit L2 flush is used.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "word2vec_sgns_words_per_sec"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl"])
+    ap.add_argument("--vocab", type=int, default=1_000_000)
+    ap.add_argument("--dim", type=int, default=128)
+    ap.add_argument("--window", type=int, default=5)
+    ap.add_argument("--negatives", type=int, default=5)
+    ap.add_argument("--neg-pool", type=int, default=16)
+    ap.add_argument("--tokens-per-step", type=int, default=262144)
+    ap.add_argument("--optimizer", default="sgd", choices=["sgd", "adagrad"])
+    ap.add_argument("--tile-impl", default="auto", choices=["auto", "cuda_core", "tcgen05"])
+    ap.add_argument("--lr", type=float, default=0.025)
+    ap.add_argument("--ref-tokens", type=int, default=200_000, help="tokens per worker for the reference arm")
+    return ap.parse_args()
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from swiftsnails_b200 import _lib
+    from swiftsnails_b200.models.word2vec import (Word2VecConfig, Word2VecTrainer, Word2VecWorker,
+                                                  synthetic_corpus)
+    from swiftsnails_b200.ops._util import u32_tensor
+    from swiftsnails_b200.parallel.cluster import make_table
+    from swiftsnails_b200.utils.clocks import ClockSampler
+
+    rank, world, local = dist_env()
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torchrun for --gpus > 1")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    tile_impl = args.tile_impl
+    if tile_impl == "auto":
+        tile_impl = "tcgen05" if (_lib.has_symbol("ssb_sgns_tiles_tc") and args.dim == 128
+                                  and os.environ.get("SSB200_NO_TC") != "1") else "cuda_core"
+    cfg = Word2VecConfig(vocab=args.vocab, dim=args.dim, window=args.window, negatives=args.negatives,
+                         neg_pool=args.neg_pool, tokens_per_step=args.tokens_per_step, lr=args.lr,
+                         optimizer=args.optimizer, seed=1 + rank, tile_impl=tile_impl)
+    # 2*vocab keys (input + output vectors) spread over `world` shards at load factor 0.5
+    rows_per_shard = (2 * cfg.vocab + world - 1) // world
+    table = make_table(rows_per_shard, cfg.dim, dev, with_state=(cfg.optimizer == "adagrad"),
+                       init_scale=1.0 / cfg.dim, frag_num=max(1024, world))
+    K, W, B = args.steps, args.warmup, cfg.tokens_per_step
+    corpus = synthetic_corpus(cfg.vocab, (K + W) * B, s=cfg.zipf_s, seed=100 + rank)
+    host = torch.from_numpy(corpus.view(np.int32)).reshape(K + W, B).pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---------------- device-timed arm: batches already on the device -------------------------
+    worker = Word2VecWorker(cfg, table, dev)
+    dev_tokens = host.to(dev)
+    for s in range(W):
+        worker.step(dev_tokens[s])
+    barrier()
+    sampler = ClockSampler(gpu_index=local).start()
+    time.sleep(0.3)
+    worker.reset_loss()
+    launches0 = _lib.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    e0.record()
+    for s in range(W, W + K):
+        worker.step(dev_tokens[s])
+    e1.record()
+    barrier()
+    t1 = time.time()
+    launches = _lib.launch_count - launches0
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    loss_dev = worker.mean_loss()
+    n_pairs = float(worker.loss[1].item())
+    sampler.stop()
+    clocks = sampler.summary(t0, t1)
+    del dev_tokens
+
+    # ---------------- end-to-end arm: public API, H2D tokens + D2H loss every step -------------
+    trainer = Word2VecTrainer(cfg, table, dev)
+    trainer.worker.step_idx = worker.step_idx
+    for s in range(W):
+        trainer.train_step(host[s])
+    trainer.finish()
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for s in range(W, W + K):
+        trainer.train_step(host[s])
+    last_loss = trainer.finish()
+    f1.record()
+    barrier()
+    ms_e2e = max_over_ranks(f0.elapsed_time(f1))
+
+    words = float(K) * B * world
+    value = words / (ms / 1e3)
+    e2e_value = words / (ms_e2e / 1e3)
+    if rank == 0:
+        out = {
+            "metric": METRIC, "value": value, "unit": "words/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "fp32 table, tf32 tensor-core tiles" if tile_impl == "tcgen05" else "fp32",
+            "data": "synthetic Zipf(s=1) corpus, random-init table", "impl": "ours",
+            "config": {"model": "word2vec skip-gram negative sampling", "vocab": cfg.vocab, "dim": cfg.dim,
+                       "window": cfg.window, "negatives": cfg.negatives,
+                       "neg_pool_per_128_pair_tile": cfg.neg_pool, "global_batch": B * world,
+                       "tokens_per_step_per_gpu": B, "seq_len": cfg.sent_len, "optimizer": cfg.optimizer,
+                       "parallelism": "ps%d (1 server shard + 1 worker per GPU, P2P pull/push)" % world,
+                       "tile_impl": tile_impl, "pairs_per_step_per_gpu": n_pairs / K,
+                       "l2": "no flush: table (%.2f GiB/shard) and caches exceed the 126 MB L2"
+                             % (table.owned[0].nbytes() / 2 ** 30)},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "words/s", "ms_per_step": ms_e2e / K,
+                    "h2d_bytes_per_step": trainer.h2d_bytes, "d2h_bytes_per_step": trainer.d2h_bytes},
+            "gpu_launches": launches,
+            "loss": {"device_arm_mean": loss_dev, "e2e_last": last_loss},
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    try:
+        from baseline.run_reference import run as ref_run
+    except Exception as e:  # harness missing
+        print(json.dumps({"impl": "reference", "unavailable": "reference harness not importable: %r" % (e,)}))
+        return
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return  # the reference arm is CPU-only: rank 0 launches all master/server/worker processes
+    print(json.dumps(ref_run(args)))
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

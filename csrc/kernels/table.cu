@@ -1,0 +1,352 @@
+// table.cu — K3/K4/K7/K8/K10/K11: the HBM-resident sharded sparse table.
+//
+// ref: parameter/sparsetable.h:69-121 (SparseTable), :123-160 (PullAccessAgent: lazy
+//      init_param on miss), :162-198 (PushAccessAgent::apply_push_value, Hogwild),
+//      parameter/global_pull_access.h:40-120 + system/server/init.h:49-69 (pull RPC),
+//      parameter/global_push_access.h:36-149 + system/server/init.h:116-132 (push RPC).
+//
+// Design (not a translation): a shard is three flat arrays in HBM — keys[cap], rows[cap][D],
+// state[cap][D] — mapped into every worker process (own memory or a peer's over NVLink).
+// A pull is ONE kernel: hash the key to its owner shard, probe the owner's 128-byte key bucket
+// with one warp-wide load (local or remote), claim+initialise the row if it is missing, and
+// gather the row straight into the worker's cache — no request/response messages, no host.
+// A push is ONE kernel: vector `red`/`atom` of the update straight into the owner's row.
+//
+// Slot claim protocol (readers never observe a half-initialised row):
+//   CAS(key slot: EMPTY -> LOCKED) ; write init row ; st.release.sys(key slot = key).
+// Probers that see LOCKED in their bucket re-read until it resolves (the holder is a resident
+// warp that never waits, so this cannot deadlock). No deletion, no rehash: capacity is fixed,
+// which is also what makes caching (shard, slot) on the worker legal.
+#include "common.cuh"
+
+namespace ssb {
+
+struct Probe {
+  int owner;
+  uint32_t slot;   // slot within the owner shard, or SSB_INVALID_SLOT
+  bool is_new;     // we hold the slot LOCKED and must publish it
+};
+
+// Warp-cooperative: all 32 lanes call with the same key.
+__device__ __forceinline__ Probe probe_insert(const SsbTableView& v, uint32_t key, bool insert, int lane) {
+  Probe p;
+  p.owner = owner_of(key, v.frag_map, v.frag_num);
+  p.slot = SSB_INVALID_SLOT;
+  p.is_new = false;
+  if (p.owner < 0 || p.owner >= v.num_shards) { p.owner = 0; return p; }
+  uint32_t* kbase = v.keys[p.owner];
+  const uint32_t nb = v.capacity / SSB_BUCKET;
+  uint32_t b = reduce_range(slot_hash(key), nb);
+  for (uint32_t probes = 0; probes < nb;) {
+    uint32_t kv = ld_acquire_sys(kbase + (size_t)b * SSB_BUCKET + lane);
+    unsigned m = __ballot_sync(0xffffffffu, kv == key);
+    if (m) { p.slot = b * SSB_BUCKET + (__ffs(m) - 1); return p; }
+    unsigned locked = __ballot_sync(0xffffffffu, kv == SSB_LOCKED_KEY);
+    if (locked) { __nanosleep(100); continue; }
+    unsigned empties = __ballot_sync(0xffffffffu, kv == SSB_EMPTY_KEY);
+    if (empties) {
+      if (!insert) return p;
+      int e = __ffs(empties) - 1;
+      uint32_t old = 0;
+      if (lane == e) old = cas_sys(kbase + (size_t)b * SSB_BUCKET + e, SSB_EMPTY_KEY, SSB_LOCKED_KEY);
+      old = __shfl_sync(0xffffffffu, old, e);
+      if (old == SSB_EMPTY_KEY) { p.slot = b * SSB_BUCKET + e; p.is_new = true; return p; }
+      continue;  // lost the race: re-read the bucket
+    }
+    b = (b + 1 == nb) ? 0 : b + 1;
+    ++probes;
+  }
+  return p;  // table full
+}
+
+__device__ __forceinline__ void publish(const SsbTableView& v, const Probe& p, uint32_t key, int lane) {
+  __syncwarp();
+  if (lane == 0) st_release_sys(v.keys[p.owner] + p.slot, key);
+}
+
+__device__ __forceinline__ uint32_t effective_n(int64_t n, const uint32_t* n_dev) {
+  uint32_t ne = (uint32_t)n;
+  if (n_dev) { uint32_t d = *n_dev; if (d < ne) ne = d; }
+  return ne;
+}
+
+// ---- pull ---------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ keys, int64_t n,
+            const uint32_t* __restrict__ n_dev, uint32_t* __restrict__ gslot_out,
+            float* __restrict__ rows_out, float* __restrict__ grads_zero, int insert,
+            uint32_t* __restrict__ stats) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t ne = effective_n(n, n_dev);
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const int D = v.dim;
+  const bool vec = (D & 3) == 0;
+  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
+    const uint32_t key = __ldg(keys + w);
+    Probe p;
+    p.owner = 0; p.slot = SSB_INVALID_SLOT; p.is_new = false;
+    const bool valid = key < SSB_LOCKED_KEY;
+    if (valid) p = probe_insert(v, key, insert != 0, lane);
+    const bool have = p.slot != SSB_INVALID_SLOT;
+    float* row = have ? v.rows[p.owner] + (size_t)p.slot * D : nullptr;
+    float* out = rows_out ? rows_out + (size_t)w * D : nullptr;
+    float* gz = grads_zero ? grads_zero + (size_t)w * D : nullptr;
+    if (vec) {
+      for (int j = lane * 4; j < D; j += 128) {
+        float4 val;
+        if (have && !p.is_new) {
+          val = out ? ld_row_f4(row + j) : make_float4(0, 0, 0, 0);
+        } else if (valid) {
+          val.x = init_value(key, j, v.seed, v.init_scale);
+          val.y = init_value(key, j + 1, v.seed, v.init_scale);
+          val.z = init_value(key, j + 2, v.seed, v.init_scale);
+          val.w = init_value(key, j + 3, v.seed, v.init_scale);
+          if (p.is_new) *reinterpret_cast<float4*>(row + j) = val;
+        } else {
+          val = make_float4(0, 0, 0, 0);
+        }
+        if (out) *reinterpret_cast<float4*>(out + j) = val;
+        if (gz) *reinterpret_cast<float4*>(gz + j) = make_float4(0, 0, 0, 0);
+      }
+    } else {
+      for (int j = lane; j < D; j += 32) {
+        float val;
+        if (have && !p.is_new) {
+          val = out ? ld_row_f1(row + j) : 0.f;
+        } else if (valid) {
+          val = init_value(key, j, v.seed, v.init_scale);
+          if (p.is_new) row[j] = val;
+        } else {
+          val = 0.f;
+        }
+        if (out) out[j] = val;
+        if (gz) gz[j] = 0.f;
+      }
+    }
+    if (p.is_new) publish(v, p, key, lane);
+    if (lane == 0) {
+      gslot_out[w] = have ? (uint32_t)p.owner * v.capacity + p.slot : SSB_INVALID_SLOT;
+      if (stats) {
+        if (p.is_new) atomicAdd(stats + 0, 1u);
+        if (valid && !have) atomicAdd(stats + 1, 1u);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+gather_slots_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot, int64_t n,
+                    const uint32_t* __restrict__ n_dev, float* __restrict__ rows_out) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t ne = effective_n(n, n_dev);
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const int D = v.dim;
+  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
+    uint32_t g = __ldg(gslot + w);
+    float* out = rows_out + (size_t)w * D;
+    if (g == SSB_INVALID_SLOT) {
+      for (int j = lane; j < D; j += 32) out[j] = 0.f;
+      continue;
+    }
+    uint32_t o = g / v.capacity, s = g - o * v.capacity;
+    const float* row = v.rows[o] + (size_t)s * D;
+    if ((D & 3) == 0) {
+      for (int j = lane * 4; j < D; j += 128) *reinterpret_cast<float4*>(out + j) = ld_row_f4(row + j);
+    } else {
+      for (int j = lane; j < D; j += 32) out[j] = ld_row_f1(row + j);
+    }
+  }
+}
+
+// ---- push ---------------------------------------------------------------------------------
+template <bool kAdaGrad>
+__global__ void __launch_bounds__(256)
+push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot, float* grads,
+            int64_t n, const uint32_t* __restrict__ n_dev, float lr, float eps, int zero_grads) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t ne = effective_n(n, n_dev);
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const int D = v.dim;
+  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
+    uint32_t g = __ldg(gslot + w);
+    if (g == SSB_INVALID_SLOT) continue;
+    uint32_t o = g / v.capacity, s = g - o * v.capacity;
+    float* row = v.rows[o] + (size_t)s * D;
+    float* st = kAdaGrad ? v.state[o] + (size_t)s * D : nullptr;
+    float* gr = grads + (size_t)w * D;
+    if ((D & 3) == 0) {
+      for (int j = lane * 4; j < D; j += 128) {
+        float4 gv = *reinterpret_cast<const float4*>(gr + j);
+        if (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
+        float4 d;
+        if (kAdaGrad) {
+          float4 g2 = make_float4(gv.x * gv.x, gv.y * gv.y, gv.z * gv.z, gv.w * gv.w);
+          float4 a = atom_add_f4_sys(st + j, g2);
+          d.x = -lr * gv.x * rsqrtf(a.x + g2.x + eps);
+          d.y = -lr * gv.y * rsqrtf(a.y + g2.y + eps);
+          d.z = -lr * gv.z * rsqrtf(a.z + g2.z + eps);
+          d.w = -lr * gv.w * rsqrtf(a.w + g2.w + eps);
+        } else {
+          d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
+        }
+        red_add_f4_sys(row + j, d);
+        if (zero_grads) *reinterpret_cast<float4*>(gr + j) = make_float4(0, 0, 0, 0);
+      }
+    } else {
+      for (int j = lane; j < D; j += 32) {
+        float gv = gr[j];
+        if (gv == 0.f) continue;
+        float d;
+        if (kAdaGrad) {
+          float g2 = gv * gv;
+          float a = atom_add_f1_sys(st + j, g2);
+          d = -lr * gv * rsqrtf(a + g2 + eps);
+        } else {
+          d = -lr * gv;
+        }
+        red_add_f1_sys(row + j, d);
+        if (zero_grads) gr[j] = 0.f;
+      }
+    }
+  }
+}
+
+// ---- bulk load (checkpoint resume; new capability, the reference never reads a dump back) ----
+__global__ void __launch_bounds__(256)
+table_load_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ keys,
+                  const float* __restrict__ rows, const float* __restrict__ state, int64_t n,
+                  uint32_t* __restrict__ stats) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const int D = v.dim;
+  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < (uint32_t)n; w += warps) {
+    const uint32_t key = __ldg(keys + w);
+    if (key >= SSB_LOCKED_KEY) continue;
+    Probe p = probe_insert(v, key, true, lane);
+    if (p.slot == SSB_INVALID_SLOT) { if (lane == 0 && stats) atomicAdd(stats + 1, 1u); continue; }
+    float* row = v.rows[p.owner] + (size_t)p.slot * D;
+    for (int j = lane; j < D; j += 32) row[j] = rows[(size_t)w * D + j];
+    if (state && v.state[p.owner]) {
+      float* st = v.state[p.owner] + (size_t)p.slot * D;
+      for (int j = lane; j < D; j += 32) st[j] = state[(size_t)w * D + j];
+    }
+    if (p.is_new) { publish(v, p, key, lane); if (lane == 0 && stats) atomicAdd(stats + 0, 1u); }
+  }
+}
+
+// ---- dump: compact the live slots of one shard (K11) ----------------------------------------
+// ref: sparsetable.h:49-56,100-104 (text dump key \t value), system/server/init.h:138-149.
+__global__ void __launch_bounds__(256)
+dump_compact_kernel(const uint32_t* __restrict__ keys, const float* __restrict__ rows, uint32_t capacity,
+                    int D, uint32_t* __restrict__ out_keys, float* __restrict__ out_rows,
+                    uint32_t* __restrict__ n_live, uint32_t max_out) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const uint32_t nb = capacity / SSB_BUCKET;
+  for (uint32_t b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < nb; b += warps) {
+    uint32_t k = keys[(size_t)b * SSB_BUCKET + lane];
+    unsigned live = __ballot_sync(0xffffffffu, k < SSB_LOCKED_KEY);
+    if (!live) continue;
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(n_live, (uint32_t)__popc(live));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (k < SSB_LOCKED_KEY) {
+      uint32_t dst = base + __popc(live & ((1u << lane) - 1));
+      if (dst < max_out) out_keys[dst] = k;
+    }
+    if (out_rows) {
+      unsigned m = live;
+      while (m) {
+        int src = __ffs(m) - 1;
+        m &= m - 1;
+        uint32_t dst = base + __popc(live & ((1u << src) - 1));
+        if (dst >= max_out) break;
+        const float* r = rows + ((size_t)b * SSB_BUCKET + src) * D;
+        float* o = out_rows + (size_t)dst * D;
+        for (int j = lane; j < D; j += 32) o[j] = r[j];
+      }
+    }
+  }
+}
+
+inline int row_grid(int64_t n) {
+  // warp per row, 8 warps per block; cap at a few waves of 148 SMs x 8 resident blocks
+  return grid_for(n, 8, kNumSMs * 8);
+}
+
+}  // namespace ssb
+
+extern "C" {
+
+static int check_view(const SsbTableView* v) {
+  if (!v || v->num_shards < 1 || v->num_shards > SSB_MAX_SHARDS || v->dim < 1 ||
+      v->capacity == 0 || v->capacity % SSB_BUCKET != 0 || v->frag_num == 0 || !v->frag_map)
+    return (int)cudaErrorInvalidValue;
+  if ((uint64_t)v->capacity * (uint64_t)v->num_shards >= 0xFFFFFFFFull) return (int)cudaErrorInvalidValue;
+  return 0;
+}
+
+int ssb_pull(const SsbTableView* view, const uint32_t* keys, int64_t n, const uint32_t* n_dev,
+             uint32_t* gslot, float* rows_out, float* grads_zero, int insert, uint32_t* stats,
+             void* stream) {
+  if (int e = check_view(view)) return e;
+  if (n <= 0) return 0;
+  ssb::pull_kernel<<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, keys, n, n_dev, gslot, rows_out,
+                                                                  grads_zero, insert, stats);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_gather_slots(const SsbTableView* view, const uint32_t* gslot, int64_t n, const uint32_t* n_dev,
+                     float* rows_out, void* stream) {
+  if (int e = check_view(view)) return e;
+  if (n <= 0) return 0;
+  ssb::gather_slots_kernel<<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, n, n_dev, rows_out);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_push_sgd(const SsbTableView* view, const uint32_t* gslot, float* grads, int64_t n,
+                 const uint32_t* n_dev, float lr, int zero_grads, void* stream) {
+  if (int e = check_view(view)) return e;
+  if (n <= 0) return 0;
+  ssb::push_kernel<false><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, grads, n, n_dev, lr,
+                                                                         0.f, zero_grads);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_push_adagrad(const SsbTableView* view, const uint32_t* gslot, float* grads, int64_t n,
+                     const uint32_t* n_dev, float lr, float eps, int zero_grads, void* stream) {
+  if (int e = check_view(view)) return e;
+  for (int i = 0; i < view->num_shards; ++i)
+    if (!view->state[i]) return (int)cudaErrorInvalidValue;
+  if (n <= 0) return 0;
+  ssb::push_kernel<true><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, grads, n, n_dev, lr,
+                                                                        eps, zero_grads);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_table_load(const SsbTableView* view, const uint32_t* keys, const float* rows, const float* state,
+                   int64_t n, uint32_t* stats, void* stream) {
+  if (int e = check_view(view)) return e;
+  if (n <= 0) return 0;
+  ssb::table_load_kernel<<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, keys, rows, state, n, stats);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_dump_compact(const uint32_t* keys, const float* rows, uint32_t capacity, int32_t dim,
+                     uint32_t* out_keys, float* out_rows, uint32_t* n_live, uint32_t max_out,
+                     void* stream) {
+  if (capacity == 0 || capacity % SSB_BUCKET != 0) return (int)cudaErrorInvalidValue;
+  cudaError_t e = cudaMemsetAsync(n_live, 0, sizeof(uint32_t), (cudaStream_t)stream);
+  if (e != cudaSuccess) return (int)e;
+  ssb::dump_compact_kernel<<<ssb::row_grid(capacity / SSB_BUCKET), 256, 0, (cudaStream_t)stream>>>(
+      keys, rows, capacity, dim, out_keys, out_rows, n_live, max_out);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

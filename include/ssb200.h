@@ -1,0 +1,131 @@
+/*
+ * ssb200.h — C ABI of the swiftsnails_b200 device library (libssb200_kernels.so).
+ *
+ * Every entry point takes raw device pointers plus a cudaStream_t (passed as void*),
+ * launches on that stream and returns a cudaError_t as int (0 = success); nothing here
+ * synchronises the stream unless the comment says so.  The kernels are written for
+ * sm_100a only.  Citations `ref:` point into /root/reference/src (the CPU reference whose
+ * behaviour the kernel reproduces); see SURVEY.md §8 for the K-numbering.
+ */
+#pragma once
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSB_MAX_SHARDS 16
+#define SSB_EMPTY_KEY 0xFFFFFFFFu  /* ref: core/parameter/sparsetable.h:13 (empty key = max()) */
+#define SSB_LOCKED_KEY 0xFFFFFFFEu /* slot claimed, row being initialised (device-table only)   */
+#define SSB_BUCKET 32              /* keys per probe bucket = one 128-byte line                   */
+#define SSB_INVALID_SLOT 0xFFFFFFFFu
+
+/* A view of the sharded sparse table: one shard per GPU ("server"), every shard mapped into
+ * this process (own HBM or a peer's over NVLink).  Global slot index = shard * capacity + slot.
+ * ref: core/parameter/sparsetable.h:69-121 (SparseTable), hashfrag.h:12-116 (BasicHashFrag). */
+typedef struct SsbTableView {
+  uint32_t *keys[SSB_MAX_SHARDS];  /* [capacity] per shard, SSB_EMPTY_KEY when free          */
+  float *rows[SSB_MAX_SHARDS];     /* [capacity][dim] parameter rows                          */
+  float *state[SSB_MAX_SHARDS];    /* [capacity][dim] AdaGrad accumulators, or NULL           */
+  const uint32_t *frag_map;        /* [frag_num] fragment -> node id (1..num_shards), device  */
+  uint32_t frag_num;
+  uint32_t capacity;               /* slots per shard, multiple of SSB_BUCKET                 */
+  int32_t dim;                     /* floats per row                                          */
+  int32_t num_shards;
+  uint64_t seed;                   /* deterministic lazy init: row = f(key, seed)             */
+  float init_scale;                /* init value = (u01 - 0.5) * init_scale                   */
+  int32_t pad_;
+} SsbTableView;
+
+/* ---- K1: key hashing / routing / bucketing ------------------------------------------------
+ * ref: utils/HashFunction.h:16-24, parameter/hashfrag.h:48-53, global_pull_access.h:58-72 */
+int ssb_fmix64(const uint64_t *in, uint64_t *out, int64_t n, void *stream);
+/* owner[i] = frag_map[fmix64(key) % frag_num] - 1; counts[o] += 1 (counts must be zeroed). */
+int ssb_hash_route(const uint32_t *keys, int64_t n, const uint32_t *frag_map, uint32_t frag_num,
+                   int32_t num_owners, int32_t *owner, uint32_t *counts, void *stream);
+/* Partition keys by owner: offsets[o] = exclusive scan of counts (device, num_owners+1),
+ * cursor[o] zeroed scratch; bucketed[offsets[o] + k] = key, perm[...] = original index. */
+int ssb_bucket_scatter(const uint32_t *keys, const int32_t *owner, int64_t n,
+                       const uint32_t *offsets, uint32_t *cursor, uint32_t *bucketed,
+                       uint32_t *perm, void *stream);
+
+/* ---- K2: de-duplication ------------------------------------------------------------------
+ * ref: parameter/global_param_cache.h:107-108 (grads is a map => unique keys).
+ * Scratch: set[set_cap] uint64 (epoch-tagged, never needs clearing between calls as long as
+ * `epoch` changes; zero-fill once), set_ids[set_cap] uint32.  set_cap must be a power of two
+ * >= 2*n.  Outputs: unique[<=n], inverse[n] (index into unique), *n_unique (device, must be
+ * zeroed by the caller or by passing reset=1). Keys equal to SSB_EMPTY_KEY map to
+ * inverse = SSB_INVALID_SLOT and are not emitted. */
+int ssb_dedup(const uint32_t *keys, int64_t n, uint64_t *set, uint32_t *set_ids, uint32_t set_cap,
+              uint32_t epoch, uint32_t *unique, uint32_t *inverse, uint32_t *n_unique, int reset,
+              void *stream);
+
+/* ---- K3/K4/K10: table probe+insert, pull gather, cache merge -------------------------------
+ * ref: sparsetable.h:142-149 (lazy init_param on miss), global_pull_access.h:40-120,
+ * system/server/init.h:49-69.
+ * n_dev (device uint32, may be NULL) overrides n when smaller (size known only on device).
+ * gslot[i] = shard*capacity + slot.  rows_out [n][dim] may be NULL (resolve only).
+ * insert=0: missing keys return SSB_INVALID_SLOT and the deterministic init row.        */
+int ssb_pull(const SsbTableView *view, const uint32_t *keys, int64_t n, const uint32_t *n_dev,
+             uint32_t *gslot, float *rows_out, float *grads_zero, int insert, uint32_t *stats,
+             void *stream);
+/* Gather by already-resolved global slots (worker-side slot cache hit path). */
+int ssb_gather_slots(const SsbTableView *view, const uint32_t *gslot, int64_t n,
+                     const uint32_t *n_dev, float *rows_out, void *stream);
+
+/* ---- K7/K8: push = scatter-add into the owner shard fused with the server update ----------
+ * ref: global_push_access.h:36-149, sparsetable.h:181-192, sparse_access_method.h:33-46.
+ * SGD:     w -= lr * g                    (one vector `red` per 16 bytes, remote or local)
+ * AdaGrad: acc += g*g; w -= lr*g/sqrt(acc+eps)   (vector `atom` on acc, `red` on w)
+ * zero_grads=1 clears grads after reading (Grad::reset(), global_push_access.h:78).  */
+int ssb_push_sgd(const SsbTableView *view, const uint32_t *gslot, float *grads, int64_t n,
+                 const uint32_t *n_dev, float lr, int zero_grads, void *stream);
+int ssb_push_adagrad(const SsbTableView *view, const uint32_t *gslot, float *grads, int64_t n,
+                     const uint32_t *n_dev, float lr, float eps, int zero_grads, void *stream);
+
+/* ---- K9: negative sampling (alias method, Philox4x32-10 counter RNG) ---------------------- */
+int ssb_neg_sample(const float *prob, const uint32_t *alias, uint32_t vocab, uint64_t seed,
+                   uint64_t offset, uint32_t key_offset, uint32_t *out, int64_t n, void *stream);
+
+/* ---- word2vec SGNS (apps are absent from the reference; SURVEY.md §3.4 hot loop I) --------
+ * Pair generation: tokens[n_tok] in sentences of `sent_len`; dynamic window shrink like
+ * classic word2vec.  inv_in/inv_out map token position -> row index in the worker cache.
+ * pairs_in/out are compacted (order unspecified); *n_pairs device counter (zeroed by reset). */
+int ssb_sgns_make_pairs(const uint32_t *inv_in, const uint32_t *inv_out, int64_t n_tok,
+                        int32_t sent_len, int32_t window, uint64_t seed, uint64_t offset,
+                        uint32_t *pairs_in, uint32_t *pairs_out, uint32_t *n_pairs, void *stream);
+/* CUDA-core tile kernel: tile = 128 pairs sharing n_neg negatives (rows neg_idx[tile*n_neg+..]).
+ * loss_out[0] += sum of losses, loss_out[1] += number of pairs.  neg_weight scales the
+ * negative term (K/n_neg keeps the K-negatives objective in expectation). */
+int ssb_sgns_tiles(const float *params, float *grads, int32_t dim, const uint32_t *pairs_in,
+                   const uint32_t *pairs_out, const uint32_t *n_pairs, int64_t max_pairs,
+                   const uint32_t *neg_idx, int32_t n_neg, float neg_weight, float *loss_out,
+                   void *stream);
+
+/* ---- sparse logistic regression (K6) -------------------------------------------------------
+ * inv[n_ex*n_feat] row index into the cache (dim 1), x values, labels in {0,1}.          */
+int ssb_lr_fwd_bwd(const float *params, float *grads, const uint32_t *inv, const float *x,
+                   const float *labels, int64_t n_ex, int32_t n_feat, float *loss_out,
+                   void *stream);
+
+/* ---- K11: parameter dump -----------------------------------------------------------------
+ * Compacts the live slots of one shard: out_keys[*n_live], out_rows[*n_live][dim].        */
+int ssb_dump_compact(const uint32_t *keys, const float *rows, uint32_t capacity, int32_t dim,
+                     uint32_t *out_keys, float *out_rows, uint32_t *n_live, uint32_t max_out,
+                     void *stream);
+/* Bulk load (new capability: checkpoint resume): insert keys with given rows into the view. */
+int ssb_table_load(const SsbTableView *view, const uint32_t *keys, const float *rows,
+                   const float *state, int64_t n, uint32_t *stats, void *stream);
+
+/* ---- K12: peer bandwidth probe -------------------------------------------------------------
+ * Copies n_bytes from src to dst with a grid of vector loads/stores (either may be a peer). */
+int ssb_p2p_copy(const void *src, void *dst, int64_t n_bytes, int32_t blocks, void *stream);
+
+/* ---- misc ---------------------------------------------------------------------------------- */
+int ssb_fill_u32(uint32_t *p, uint32_t v, int64_t n, void *stream);
+const char *ssb_error_string(int err);
+int ssb_version(void);
+
+#ifdef __cplusplus
+}
+#endif

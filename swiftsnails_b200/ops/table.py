@@ -1,0 +1,167 @@
+"""The HBM-resident sharded sparse table and its pull / push ops (K3, K4, K7, K8, K11).
+
+ref: /root/reference/src/core/parameter/sparsetable.h:69-198 (SparseTable, PullAccessAgent,
+PushAccessAgent), global_pull_access.h:40-120, global_push_access.h:36-149,
+system/server/init.h:49-69,116-149.
+
+One *shard* per GPU ("server"): ``keys[cap]`` / ``rows[cap, D]`` / ``state[cap, D]``.  A
+``ShardedTable`` is one process's view of all shards — its own plus every peer's mapped over
+NVLink (``swiftsnails_b200.parallel.peer``) — and pull/push are single kernels that address the
+owner shard directly.  For tests, several shards may live on one GPU (``local_shards=S``): the
+kernels do not care where a shard pointer points.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from .. import _lib
+from ..parallel.hashfrag import HashFrag
+from ._util import check_cuda
+
+
+def round_capacity(rows_expected: int, load_factor: float = 0.5) -> int:
+    cap = int(rows_expected / load_factor) + _lib.BUCKET
+    return (cap + _lib.BUCKET - 1) // _lib.BUCKET * _lib.BUCKET
+
+
+class DeviceShard:
+    """Storage of one shard on one device."""
+
+    def __init__(self, capacity: int, dim: int, device, with_state: bool, alloc=None):
+        assert capacity % _lib.BUCKET == 0
+        self.capacity, self.dim, self.device = int(capacity), int(dim), device
+        if alloc is None:
+            def alloc(shape, dtype):
+                return torch.empty(shape, dtype=dtype, device=device)
+        self.keys = alloc((capacity,), torch.int32)
+        self.keys.fill_(-1)  # 0xFFFFFFFF = empty
+        self.rows = alloc((capacity, dim), torch.float32)
+        self.state = None
+        if with_state:
+            self.state = alloc((capacity, dim), torch.float32)
+            self.state.zero_()
+
+    def ptrs(self):
+        return (self.keys.data_ptr(), self.rows.data_ptr(), 0 if self.state is None else self.state.data_ptr())
+
+    def nbytes(self):
+        n = self.keys.numel() * 4 + self.rows.numel() * 4
+        return n + (self.state.numel() * 4 if self.state is not None else 0)
+
+
+class ShardedTable:
+    """All shards of the table as seen from one worker process.
+
+    ``shard_ptrs``: list of (keys_ptr, rows_ptr, state_ptr) for every shard, in shard order.
+    Use :meth:`local` for single-process tables (1..16 shards on one GPU)."""
+
+    def __init__(self, hashfrag: HashFrag, capacity: int, dim: int, shard_ptrs, device, seed=0x5EED,
+                 init_scale=None, owned=None, rank=0):
+        if hashfrag.num_nodes != len(shard_ptrs):
+            raise ValueError("hashfrag has %d nodes but %d shards given" % (hashfrag.num_nodes, len(shard_ptrs)))
+        if len(shard_ptrs) > _lib.MAX_SHARDS:
+            raise ValueError("at most %d shards" % _lib.MAX_SHARDS)
+        self.hashfrag, self.capacity, self.dim = hashfrag, int(capacity), int(dim)
+        self.device, self.rank = device, rank
+        self.num_shards = len(shard_ptrs)
+        self.owned = owned or []          # DeviceShard objects this process owns (keeps them alive)
+        self.frag_map_dev = hashfrag.device_map(device)
+        self.init_scale = float(init_scale if init_scale is not None else 1.0 / dim)
+        self.seed = int(seed)
+        v = _lib.SsbTableView()
+        for i, (k, r, s) in enumerate(shard_ptrs):
+            v.keys[i], v.rows[i], v.state[i] = k, r, (s or None)
+        v.frag_map = self.frag_map_dev.data_ptr()
+        v.frag_num = hashfrag.frag_num
+        v.capacity = self.capacity
+        v.dim = self.dim
+        v.num_shards = self.num_shards
+        v.seed = self.seed
+        v.init_scale = self.init_scale
+        self.view = v
+        self.has_state = all(s for (_, _, s) in shard_ptrs)
+        self.stats = torch.zeros(4, dtype=torch.int32, device=device)  # [inserts, misses/full, -, -]
+
+    # -- construction --------------------------------------------------------------------------
+    @classmethod
+    def local(cls, capacity, dim, device, num_shards=1, frag_num=None, with_state=False, **kw):
+        hf = HashFrag(num_shards, frag_num or max(num_shards, 1024 if num_shards > 1 else 1))
+        shards = [DeviceShard(capacity, dim, device, with_state) for _ in range(num_shards)]
+        return cls(hf, capacity, dim, [s.ptrs() for s in shards], device, owned=shards, **kw)
+
+    def _view_ref(self):
+        return C.byref(self.view)
+
+    # -- pull ----------------------------------------------------------------------------------
+    def pull(self, keys, n_dev=None, rows_out=None, gslot_out=None, grads_zero=None, insert=True, n=None):
+        """Route + probe/insert + gather in one kernel. ``keys`` int32 (uint32 bits) [n]."""
+        check_cuda(keys)
+        n = keys.numel() if n is None else n
+        if gslot_out is None:
+            gslot_out = torch.empty(n, dtype=torch.int32, device=keys.device)
+        if rows_out is None:
+            rows_out = torch.empty((n, self.dim), dtype=torch.float32, device=keys.device)
+        _lib.call("ssb_pull", self._view_ref(), keys.data_ptr(), n, _lib.ptr(n_dev), gslot_out.data_ptr(),
+                  rows_out.data_ptr(), _lib.ptr(grads_zero), 1 if insert else 0, self.stats.data_ptr(),
+                  _lib.stream_ptr())
+        return rows_out, gslot_out
+
+    def resolve(self, keys, insert=True):
+        """Keys -> global slots without gathering the rows."""
+        n = keys.numel()
+        gslot = torch.empty(n, dtype=torch.int32, device=keys.device)
+        _lib.call("ssb_pull", self._view_ref(), keys.data_ptr(), n, None, gslot.data_ptr(), None, None,
+                  1 if insert else 0, self.stats.data_ptr(), _lib.stream_ptr())
+        return gslot
+
+    def gather_slots(self, gslot, rows_out=None, n_dev=None, n=None):
+        n = gslot.numel() if n is None else n
+        if rows_out is None:
+            rows_out = torch.empty((n, self.dim), dtype=torch.float32, device=gslot.device)
+        _lib.call("ssb_gather_slots", self._view_ref(), gslot.data_ptr(), n, _lib.ptr(n_dev),
+                  rows_out.data_ptr(), _lib.stream_ptr())
+        return rows_out
+
+    # -- push ----------------------------------------------------------------------------------
+    def push_sgd(self, gslot, grads, lr, n_dev=None, zero_grads=True, n=None):
+        n = gslot.numel() if n is None else n
+        _lib.call("ssb_push_sgd", self._view_ref(), gslot.data_ptr(), grads.data_ptr(), n, _lib.ptr(n_dev),
+                  float(lr), 1 if zero_grads else 0, _lib.stream_ptr())
+
+    def push_adagrad(self, gslot, grads, lr, eps=1e-8, n_dev=None, zero_grads=True, n=None):
+        if not self.has_state:
+            raise ValueError("table was created without AdaGrad state")
+        n = gslot.numel() if n is None else n
+        _lib.call("ssb_push_adagrad", self._view_ref(), gslot.data_ptr(), grads.data_ptr(), n, _lib.ptr(n_dev),
+                  float(lr), float(eps), 1 if zero_grads else 0, _lib.stream_ptr())
+
+    # -- dump / load ---------------------------------------------------------------------------
+    def dump_shard(self, shard: DeviceShard, with_rows=True):
+        """Compact the live entries of an owned shard -> (keys uint32 np, rows float32 np)."""
+        cap = shard.capacity
+        n_live = torch.zeros(1, dtype=torch.int32, device=shard.device)
+        # first pass: count (keys only) so the row buffer is sized exactly
+        out_keys = torch.empty(cap, dtype=torch.int32, device=shard.device)
+        _lib.call("ssb_dump_compact", shard.keys.data_ptr(), shard.rows.data_ptr(), cap, shard.dim,
+                  out_keys.data_ptr(), None, n_live.data_ptr(), cap, _lib.stream_ptr())
+        n = int(n_live.item())
+        if not with_rows:
+            return out_keys[:n].cpu().numpy().view(np.uint32), None
+        out_rows = torch.empty((max(n, 1), shard.dim), dtype=torch.float32, device=shard.device)
+        _lib.call("ssb_dump_compact", shard.keys.data_ptr(), shard.rows.data_ptr(), cap, shard.dim,
+                  out_keys.data_ptr(), out_rows.data_ptr(), n_live.data_ptr(), n, _lib.stream_ptr())
+        torch.cuda.synchronize(shard.device)
+        return out_keys[:n].cpu().numpy().view(np.uint32), out_rows[:n].cpu().numpy()
+
+    def load(self, keys, rows, state=None):
+        """Insert (key,row[,state]) entries (checkpoint resume; not in the reference)."""
+        check_cuda(keys, rows)
+        _lib.call("ssb_table_load", self._view_ref(), keys.data_ptr(), rows.data_ptr(), _lib.ptr(state),
+                  keys.numel(), self.stats.data_ptr(), _lib.stream_ptr())
+
+    def size(self):
+        """Number of live keys across owned shards."""
+        return int(sum(((s.keys != -1) & (s.keys != -2)).sum().item() for s in self.owned))

@@ -1,0 +1,120 @@
+"""Plain NumPy / PyTorch fp32 restatements of the device ops — the numerics oracles the GPU
+tests compare against ("GPU tests comparing every kernel against a CPU oracle").
+Nothing here is on a hot path."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from ..parallel.hashfrag import fmix64
+
+EMPTY = 0xFFFFFFFF
+
+
+def slot_hash(keys):
+    k = np.asarray(keys).astype(np.uint32, copy=True)
+    with np.errstate(over="ignore"):
+        h = k * np.uint32(0x9E3779B1)
+        h ^= h >> np.uint32(16)
+        h *= np.uint32(0x85EBCA6B)
+        h ^= h >> np.uint32(13)
+        h *= np.uint32(0xC2B2AE35)
+        h ^= h >> np.uint32(16)
+    return h
+
+
+def init_rows(keys, dim, seed, scale):
+    """Deterministic lazy-init rows, bit-exact with ``ssb::init_value`` (common.cuh)."""
+    keys = np.asarray(keys).astype(np.uint64)
+    j = np.arange(dim, dtype=np.uint64)[None, :]
+    x = ((keys[:, None] << np.uint64(32)) | j) ^ np.uint64(seed)
+    h = fmix64(x)
+    u = (h >> np.uint64(40)).astype(np.uint32).astype(np.float32) * np.float32(1.0 / 16777216.0)
+    return ((u - np.float32(0.5)) * np.float32(scale)).astype(np.float32)
+
+
+def philox4x32(seed, ctr):
+    """Philox4x32-10 matching ``ssb::Philox::gen``. ctr: uint64 array. Returns uint32 [n,4]."""
+    ctr = np.asarray(ctr, dtype=np.uint64)
+    M0, M1 = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57)
+    W0, W1 = 0x9E3779B9, 0xBB67AE85
+    mask = np.uint64(0xFFFFFFFF)
+    c0 = ctr & mask
+    c1 = ctr >> np.uint64(32)
+    c2 = np.full_like(ctr, 0x5353425F)
+    c3 = np.full_like(ctr, 0x42323030)
+    k0 = seed & 0xFFFFFFFF
+    k1 = (seed >> 32) & 0xFFFFFFFF
+    for _ in range(10):
+        p0 = M0 * c0
+        p1 = M1 * c2
+        hi0, lo0 = p0 >> np.uint64(32), p0 & mask
+        hi1, lo1 = p1 >> np.uint64(32), p1 & mask
+        n0 = hi1 ^ c1 ^ np.uint64(k0)
+        n2 = hi0 ^ c3 ^ np.uint64(k1)
+        c0, c1, c2, c3 = n0, lo1, n2, lo0
+        k0 = (k0 + W0) & 0xFFFFFFFF
+        k1 = (k1 + W1) & 0xFFFFFFFF
+    return np.stack([c0, c1, c2, c3], axis=1).astype(np.uint32)
+
+
+def make_pairs_ref(inv_in, inv_out, sent_len, window, seed, offset):
+    """Reference skip-gram pair generation (dynamic window). Returns sorted list of (in,out)."""
+    n = len(inv_in)
+    r = philox4x32(seed, np.arange(n, dtype=np.uint64) + np.uint64(offset))[:, 0]
+    pairs = []
+    for i in range(n):
+        if inv_in[i] == EMPTY:
+            continue
+        eff = window - int(r[i] % window)
+        pos = i % sent_len
+        lo = -min(eff, pos)
+        hi = min(eff, sent_len - 1 - pos)
+        if i + hi >= n:
+            hi = n - 1 - i
+        for j in range(lo, hi + 1):
+            if j != 0 and inv_out[i + j] != EMPTY:
+                pairs.append((int(inv_in[i]), int(inv_out[i + j])))
+    return pairs
+
+
+def sgns_tiles_ref(params, pairs_in, pairs_out, neg_idx, n_neg, neg_weight, tile=128):
+    """fp32 PyTorch reference of the SGNS tile op. Returns (grads, loss_sum)."""
+    params = params.detach().to(torch.float32)
+    grads = torch.zeros_like(params)
+    n_pairs = pairs_in.numel()
+    loss = torch.zeros((), dtype=torch.float64, device=params.device)
+    for t in range((n_pairs + tile - 1) // tile):
+        sl = slice(t * tile, min((t + 1) * tile, n_pairs))
+        ri, ro = pairs_in[sl].long(), pairs_out[sl].long()
+        nr = neg_idx[t * n_neg:(t + 1) * n_neg].long()
+        a, p, ng = params[ri], params[ro], params[nr]
+        s_pos = (a * p).sum(-1)
+        s_neg = a @ ng.t()
+        mask = (nr[None, :] != ro[:, None]).to(torch.float32)
+        g_pos = torch.sigmoid(s_pos) - 1.0
+        g_neg = neg_weight * torch.sigmoid(s_neg) * mask
+        loss += torch.nn.functional.softplus(-s_pos).double().sum()
+        loss += (neg_weight * torch.nn.functional.softplus(s_neg) * mask).double().sum()
+        grads.index_add_(0, ri, g_pos[:, None] * p + g_neg @ ng)
+        grads.index_add_(0, ro, g_pos[:, None] * a)
+        grads.index_add_(0, nr, g_neg.t() @ a)
+    return grads, float(loss)
+
+
+def lr_ref(params, inv, x, labels):
+    """fp32 PyTorch reference of logistic regression fwd/bwd on a dim-1 cache."""
+    w = params.reshape(-1)[inv.long()]
+    z = (w * x).sum(-1)
+    p = torch.sigmoid(z)
+    loss = torch.nn.functional.binary_cross_entropy_with_logits(z, labels, reduction="sum")
+    g = (p - labels)[:, None] * x
+    grads = torch.zeros_like(params.reshape(-1))
+    grads.index_add_(0, inv.reshape(-1).long(), g.reshape(-1))
+    return grads, float(loss)
+
+
+def adagrad_ref(w, acc, g, lr, eps):
+    acc = acc + g * g
+    w = w - lr * g / torch.sqrt(acc + eps)
+    return w, acc
