@@ -40,9 +40,9 @@ def parse_args():
     ap.add_argument("--negatives", type=int, default=5)
     ap.add_argument("--neg-pool", type=int, default=16)
     ap.add_argument("--tokens-per-step", type=int, default=262144)
-    ap.add_argument("--optimizer", default="sgd", choices=["sgd", "adagrad"])
+    ap.add_argument("--optimizer", default="adagrad", choices=["sgd", "adagrad"])
     ap.add_argument("--tile-impl", default="auto", choices=["auto", "cuda_core", "tcgen05"])
-    ap.add_argument("--lr", type=float, default=0.025)
+    ap.add_argument("--lr", type=float, default=0.05)
     ap.add_argument("--ref-tokens", type=int, default=200_000, help="tokens per worker for the reference arm")
     return ap.parse_args()
 
