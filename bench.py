@@ -77,7 +77,7 @@ def run_ours(args):
 
     tile_impl = args.tile_impl
     if tile_impl == "auto":
-        tile_impl = "tcgen05" if (_lib.has_symbol("ssb_sgns_tiles_tc") and args.dim == 128
+        tile_impl = "tcgen05" if (_lib.has_symbol("ssb_sgns_block_tc") and args.dim == 128
                                   and os.environ.get("SSB200_NO_TC") != "1") else "cuda_core"
     cfg = Word2VecConfig(vocab=args.vocab, dim=args.dim, window=args.window, negatives=args.negatives,
                          neg_pool=args.neg_pool, tokens_per_step=args.tokens_per_step, lr=args.lr,

@@ -17,6 +17,7 @@
 // Probers that see LOCKED in their bucket re-read until it resolves (the holder is a resident
 // warp that never waits, so this cannot deadlock). No deletion, no rehash: capacity is fixed,
 // which is also what makes caching (shard, slot) on the worker legal.
+#include <cuda_bf16.h>
 #include "common.cuh"
 
 namespace ssb {
@@ -74,8 +75,8 @@ __device__ __forceinline__ uint32_t effective_n(int64_t n, const uint32_t* n_dev
 __global__ void __launch_bounds__(256)
 pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ keys, int64_t n,
             const uint32_t* __restrict__ n_dev, uint32_t* __restrict__ gslot_out,
-            float* __restrict__ rows_out, float* __restrict__ grads_zero, int insert,
-            uint32_t* __restrict__ stats) {
+            float* __restrict__ rows_out, __nv_bfloat16* __restrict__ rows_bf16, float* __restrict__ grads_zero,
+            int insert, uint32_t* __restrict__ stats) {
   const int lane = threadIdx.x & 31;
   const uint32_t ne = effective_n(n, n_dev);
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
@@ -90,12 +91,14 @@ pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
     const bool have = p.slot != SSB_INVALID_SLOT;
     float* row = have ? v.rows[p.owner] + (size_t)p.slot * D : nullptr;
     float* out = rows_out ? rows_out + (size_t)w * D : nullptr;
+    __nv_bfloat16* outh = rows_bf16 ? rows_bf16 + (size_t)w * D : nullptr;
     float* gz = grads_zero ? grads_zero + (size_t)w * D : nullptr;
+    const bool want = out || outh;
     if (vec) {
       for (int j = lane * 4; j < D; j += 128) {
         float4 val;
         if (have && !p.is_new) {
-          val = out ? ld_row_f4(row + j) : make_float4(0, 0, 0, 0);
+          val = want ? ld_row_f4(row + j) : make_float4(0, 0, 0, 0);
         } else if (valid) {
           val.x = init_value(key, j, v.seed, v.init_scale);
           val.y = init_value(key, j + 1, v.seed, v.init_scale);
@@ -106,13 +109,20 @@ pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
           val = make_float4(0, 0, 0, 0);
         }
         if (out) *reinterpret_cast<float4*>(out + j) = val;
+        if (outh) {
+          __nv_bfloat162 lo = __floats2bfloat162_rn(val.x, val.y), hi = __floats2bfloat162_rn(val.z, val.w);
+          uint2 pk;
+          pk.x = *reinterpret_cast<uint32_t*>(&lo);
+          pk.y = *reinterpret_cast<uint32_t*>(&hi);
+          *reinterpret_cast<uint2*>(outh + j) = pk;
+        }
         if (gz) *reinterpret_cast<float4*>(gz + j) = make_float4(0, 0, 0, 0);
       }
     } else {
       for (int j = lane; j < D; j += 32) {
         float val;
         if (have && !p.is_new) {
-          val = out ? ld_row_f1(row + j) : 0.f;
+          val = want ? ld_row_f1(row + j) : 0.f;
         } else if (valid) {
           val = init_value(key, j, v.seed, v.init_scale);
           if (p.is_new) row[j] = val;
@@ -120,6 +130,7 @@ pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
           val = 0.f;
         }
         if (out) out[j] = val;
+        if (outh) outh[j] = __float2bfloat16_rn(val);
         if (gz) gz[j] = 0.f;
       }
     }
@@ -287,12 +298,12 @@ static int check_view(const SsbTableView* v) {
 }
 
 int ssb_pull(const SsbTableView* view, const uint32_t* keys, int64_t n, const uint32_t* n_dev,
-             uint32_t* gslot, float* rows_out, float* grads_zero, int insert, uint32_t* stats,
-             void* stream) {
+             uint32_t* gslot, float* rows_out, void* rows_bf16, float* grads_zero, int insert,
+             uint32_t* stats, void* stream) {
   if (int e = check_view(view)) return e;
   if (n <= 0) return 0;
   ssb::pull_kernel<<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, keys, n, n_dev, gslot, rows_out,
-                                                                  grads_zero, insert, stats);
+                                                                  (__nv_bfloat16*)rows_bf16, grads_zero, insert, stats);
   SSB_LAUNCH_CHECK();
   return 0;
 }

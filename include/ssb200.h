@@ -64,11 +64,12 @@ int ssb_dedup(const uint32_t *keys, int64_t n, uint64_t *set, uint32_t *set_ids,
  * ref: sparsetable.h:142-149 (lazy init_param on miss), global_pull_access.h:40-120,
  * system/server/init.h:49-69.
  * n_dev (device uint32, may be NULL) overrides n when smaller (size known only on device).
- * gslot[i] = shard*capacity + slot.  rows_out [n][dim] may be NULL (resolve only).
+ * gslot[i] = shard*capacity + slot.  rows_out [n][dim] fp32 and/or rows_bf16 [n][dim] bf16 (the
+ * tensor-core cache) may be NULL.  grads_zero [n][dim] (may be NULL) is cleared in the same pass.
  * insert=0: missing keys return SSB_INVALID_SLOT and the deterministic init row.        */
 int ssb_pull(const SsbTableView *view, const uint32_t *keys, int64_t n, const uint32_t *n_dev,
-             uint32_t *gslot, float *rows_out, float *grads_zero, int insert, uint32_t *stats,
-             void *stream);
+             uint32_t *gslot, float *rows_out, void *rows_bf16, float *grads_zero, int insert,
+             uint32_t *stats, void *stream);
 /* Gather by already-resolved global slots (worker-side slot cache hit path). */
 int ssb_gather_slots(const SsbTableView *view, const uint32_t *gslot, int64_t n,
                      const uint32_t *n_dev, float *rows_out, void *stream);

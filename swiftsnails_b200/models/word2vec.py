@@ -82,8 +82,16 @@ class Word2VecWorker:
         assert table.dim == cfg.dim
         self.cfg, self.table, self.device = cfg, table, device
         B, w = cfg.tokens_per_step, cfg.window
-        self.max_pairs = B * 2 * w
-        self.max_tiles = (self.max_pairs + 127) // 128
+        self.tc = cfg.tile_impl == "tcgen05"
+        if self.tc:
+            # block formulation (csrc/kernels/sgns_tc.cu): a tile = 128 consecutive centre tokens
+            # sharing 16 negatives; no pair list is materialised
+            assert cfg.dim == 128 and cfg.window <= 8 and cfg.neg_pool == 16
+            self.max_pairs = 0
+            self.max_tiles = (B + 127) // 128
+        else:
+            self.max_pairs = B * 2 * w
+            self.max_tiles = (self.max_pairs + 127) // 128
         self.n_negs = self.max_tiles * cfg.neg_pool
         self.n_keys = 2 * B + self.n_negs
         if sampler is None:
@@ -95,10 +103,12 @@ class Word2VecWorker:
         self.inverse = torch.empty(self.n_keys, **i32)
         self.n_unique = torch.zeros(1, **i32)
         self.gslot = torch.empty(self.n_keys, **i32)
-        self.params = torch.empty((self.n_keys, cfg.dim), dtype=torch.float32, device=device)
+        self.params = None if self.tc else torch.empty((self.n_keys, cfg.dim), dtype=torch.float32, device=device)
+        self.params_bf16 = torch.empty((self.n_keys, cfg.dim), dtype=torch.bfloat16, device=device) if self.tc else None
         self.grads = torch.zeros((self.n_keys, cfg.dim), dtype=torch.float32, device=device)
-        self.pairs_in = torch.empty(self.max_pairs, **i32)
-        self.pairs_out = torch.empty(self.max_pairs, **i32)
+        self.pairs_in = torch.empty(max(self.max_pairs, 1), **i32)
+        self.pairs_out = torch.empty(max(self.max_pairs, 1), **i32)
+        self.tma_mode = 1
         self.n_pairs = torch.zeros(1, **i32)
         self.loss = torch.zeros(2, dtype=torch.float32, device=device)
         self.dedup = Deduper(self.n_keys, device)
@@ -117,16 +127,19 @@ class Word2VecWorker:
         # K2: unique keys + inverse index (the cache has one entry per key)
         self.dedup(ka, unique=self.unique, inverse=self.inverse, n_unique=self.n_unique)
         # K1+K3+K4: route, probe/insert, gather into the cache; grads zeroed in the same pass
-        self.table.pull(self.unique, n_dev=self.n_unique, rows_out=self.params, gslot_out=self.gslot,
-                        grads_zero=self.grads, n=self.n_keys)
-        # pairs over cache row indices
-        sgns_ops.make_pairs(self.inverse[:B], self.inverse[B:2 * B], cfg.sent_len, cfg.window,
-                            cfg.seed, self.step_idx * B, self.pairs_in, self.pairs_out, self.n_pairs)
-        # K5: SGNS forward/backward on the cache
-        impl = "cuda_core" if cfg.tile_impl == "cuda_core" else "tc"
-        sgns_ops.sgns_tiles(self.params, self.grads, self.pairs_in, self.pairs_out, self.n_pairs,
-                            self.max_pairs, self.inverse[2 * B:], cfg.neg_pool, self.neg_weight, self.loss,
-                            impl=impl)
+        self.table.pull(self.unique, n_dev=self.n_unique, rows_out=self.params, rows_bf16=self.params_bf16,
+                        want_fp32=not self.tc, gslot_out=self.gslot, grads_zero=self.grads, n=self.n_keys)
+        if self.tc:
+            # K5 on tensor cores: TMA gather4 -> tcgen05.mma (bf16) -> TMEM epilogue -> red
+            sgns_ops.sgns_block_tc(self.params_bf16, self.grads, self.inverse[:B], self.inverse[B:2 * B],
+                                   cfg.sent_len, cfg.window, cfg.seed, self.step_idx * B, self.inverse[2 * B:],
+                                   float(cfg.negatives), self.loss, mode=self.tma_mode)
+        else:
+            # pairs over cache row indices, then the CUDA-core tile kernel
+            sgns_ops.make_pairs(self.inverse[:B], self.inverse[B:2 * B], cfg.sent_len, cfg.window,
+                                cfg.seed, self.step_idx * B, self.pairs_in, self.pairs_out, self.n_pairs)
+            sgns_ops.sgns_tiles(self.params, self.grads, self.pairs_in, self.pairs_out, self.n_pairs,
+                                self.max_pairs, self.inverse[2 * B:], cfg.neg_pool, self.neg_weight, self.loss)
         # K7/K8: scatter-add fused with the server update
         if cfg.optimizer == "adagrad":
             self.table.push_adagrad(self.gslot, self.grads, cfg.lr, cfg.adagrad_eps, n_dev=self.n_unique,

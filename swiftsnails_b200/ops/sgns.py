@@ -16,10 +16,29 @@ def make_pairs(inv_in, inv_out, sent_len, window, seed, offset, pairs_in, pairs_
               offset, pairs_in.data_ptr(), pairs_out.data_ptr(), n_pairs.data_ptr(), _lib.stream_ptr())
 
 
-def sgns_tiles(params, grads, pairs_in, pairs_out, n_pairs, max_pairs, neg_idx, n_neg, neg_weight, loss_out,
-               impl="cuda_core"):
+def sgns_tiles(params, grads, pairs_in, pairs_out, n_pairs, max_pairs, neg_idx, n_neg, neg_weight, loss_out):
     dim = params.shape[-1]
-    name = "ssb_sgns_tiles" if impl == "cuda_core" else "ssb_sgns_tiles_tc"
-    _lib.call(name, params.data_ptr(), grads.data_ptr(), dim, pairs_in.data_ptr(), pairs_out.data_ptr(),
+    _lib.call("ssb_sgns_tiles", params.data_ptr(), grads.data_ptr(), dim, pairs_in.data_ptr(), pairs_out.data_ptr(),
               n_pairs.data_ptr(), max_pairs, neg_idx.data_ptr(), n_neg, neg_weight, loss_out.data_ptr(),
+              _lib.stream_ptr())
+
+
+def sgns_block_tc(params, grads, inv_in, inv_out, sent_len, window, seed, offset, neg_idx, neg_k, loss_out,
+                  mode=1, box_rows=1, debug=None):
+    """Block-formulation SGNS step on tcgen05 tensor cores (csrc/kernels/sgns_tc.cu).
+    params: bf16 cache [n_rows, 128]; grads: fp32.  mode 0 = vector-load gather, 1 = TMA tile::gather4."""
+    import torch
+
+    assert params.dtype == torch.bfloat16 and grads.dtype == torch.float32
+    import ctypes as C
+
+    if "ssb_sgns_block_tc" not in _lib._KERNEL_SIGS:
+        vp, i64, i32, u64, f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint64, C.c_float
+        _lib.register_sig("ssb_sgns_block_tc", [vp, vp, i64, i32, vp, vp, i64, i32, i32, u64, u64, vp, f32, vp,
+                                                 i32, i32, vp, vp])
+    n_rows, dim = params.shape
+    n_tok = inv_in.numel()
+    _lib.call("ssb_sgns_block_tc", params.data_ptr(), grads.data_ptr(), n_rows, dim, inv_in.data_ptr(),
+              inv_out.data_ptr(), n_tok, sent_len, window, seed, offset, neg_idx.data_ptr(), float(neg_k),
+              loss_out.data_ptr(), mode, box_rows, None if debug is None else debug.data_ptr(),
               _lib.stream_ptr())

@@ -96,24 +96,25 @@ class ShardedTable:
         return C.byref(self.view)
 
     # -- pull ----------------------------------------------------------------------------------
-    def pull(self, keys, n_dev=None, rows_out=None, gslot_out=None, grads_zero=None, insert=True, n=None):
+    def pull(self, keys, n_dev=None, rows_out=None, gslot_out=None, grads_zero=None, insert=True, n=None,
+             rows_bf16=None, want_fp32=True):
         """Route + probe/insert + gather in one kernel. ``keys`` int32 (uint32 bits) [n]."""
         check_cuda(keys)
         n = keys.numel() if n is None else n
         if gslot_out is None:
             gslot_out = torch.empty(n, dtype=torch.int32, device=keys.device)
-        if rows_out is None:
+        if rows_out is None and want_fp32:
             rows_out = torch.empty((n, self.dim), dtype=torch.float32, device=keys.device)
         _lib.call("ssb_pull", self._view_ref(), keys.data_ptr(), n, _lib.ptr(n_dev), gslot_out.data_ptr(),
-                  rows_out.data_ptr(), _lib.ptr(grads_zero), 1 if insert else 0, self.stats.data_ptr(),
-                  _lib.stream_ptr())
+                  _lib.ptr(rows_out), _lib.ptr(rows_bf16), _lib.ptr(grads_zero), 1 if insert else 0,
+                  self.stats.data_ptr(), _lib.stream_ptr())
         return rows_out, gslot_out
 
     def resolve(self, keys, insert=True):
         """Keys -> global slots without gathering the rows."""
         n = keys.numel()
         gslot = torch.empty(n, dtype=torch.int32, device=keys.device)
-        _lib.call("ssb_pull", self._view_ref(), keys.data_ptr(), n, None, gslot.data_ptr(), None, None,
+        _lib.call("ssb_pull", self._view_ref(), keys.data_ptr(), n, None, gslot.data_ptr(), None, None, None,
                   1 if insert else 0, self.stats.data_ptr(), _lib.stream_ptr())
         return gslot
 

@@ -118,3 +118,56 @@ def adagrad_ref(w, acc, g, lr, eps):
     acc = acc + g * g
     w = w - lr * g / torch.sqrt(acc + eps)
     return w, acc
+
+
+def sgns_block_ref(params, inv_in, inv_out, neg_idx, sent_len, window, seed, offset, neg_k, tile=128, halo=8,
+                   n_neg=16):
+    """fp32 PyTorch reference of the block-formulation SGNS step (csrc/kernels/sgns_tc.cu):
+    every token is a centre, contexts are the tokens within its (shrunk) window in the same
+    sentence, each tile of 128 centres shares 16 negatives weighted m_i*K/16.
+    inv_* / neg_idx: int64 numpy arrays of cache rows (EMPTY = invalid).  Returns
+    (grads, loss_sum, n_pairs)."""
+    dev = params.device
+    params = params.detach().to(torch.float32)
+    n_tok = len(inv_in)
+    grads = torch.zeros_like(params)
+    r0 = philox4x32(seed, np.arange(n_tok, dtype=np.uint64) + np.uint64(offset))[:, 0]
+    eff_all = window - (r0 % np.uint32(window)).astype(np.int64)
+    loss = 0.0
+    n_pairs = 0
+    for t in range((n_tok + tile - 1) // tile):
+        t0 = t * tile
+        rows = np.arange(t0, min(t0 + tile, n_tok))
+        ctx_tok = np.arange(t0 - halo, t0 + tile + halo)
+        in_rows = inv_in[rows]
+        ctx_ok = (ctx_tok >= 0) & (ctx_tok < n_tok)
+        ctx_rows = np.where(ctx_ok, inv_out[np.clip(ctx_tok, 0, n_tok - 1)], EMPTY)
+        ctx_ok &= ctx_rows != EMPTY
+        rel = ctx_tok[None, :] - rows[:, None]
+        mask = (rel != 0) & (np.abs(rel) <= eff_all[rows][:, None]) & ctx_ok[None, :] & \
+               ((ctx_tok[None, :] // sent_len) == (rows[:, None] // sent_len)) & (in_rows != EMPTY)[:, None]
+        negs = neg_idx[t * n_neg:(t + 1) * n_neg]
+        neg_ok = negs != EMPTY
+        mt = torch.from_numpy(mask).to(dev).float()
+        a = params[torch.from_numpy(np.where(in_rows == EMPTY, 0, in_rows)).to(dev).long()]
+        c = params[torch.from_numpy(np.where(ctx_rows == EMPTY, 0, ctx_rows)).to(dev).long()]
+        ng = params[torch.from_numpy(np.where(neg_ok, negs, 0)).to(dev).long()]
+        s_pos = a @ c.t()
+        s_neg = a @ ng.t()
+        m_i = mt.sum(1)
+        w = (m_i * neg_k / n_neg)[:, None] * torch.from_numpy(neg_ok).to(dev).float()[None, :]
+        g_pos = (torch.sigmoid(s_pos) - 1.0) * mt
+        g_neg = w * torch.sigmoid(s_neg)
+        loss += float((torch.nn.functional.softplus(-s_pos) * mt).double().sum())
+        loss += float((w * torch.nn.functional.softplus(s_neg)).double().sum())
+        n_pairs += int(mask.sum())
+        d_in = g_pos @ c + g_neg @ ng
+        d_ctx = g_pos.t() @ a
+        d_neg = g_neg.t() @ a
+        ok_in = torch.from_numpy(in_rows != EMPTY).to(dev)
+        grads.index_add_(0, torch.from_numpy(np.where(in_rows == EMPTY, 0, in_rows)).to(dev).long()[ok_in], d_in[ok_in])
+        ok_c = torch.from_numpy(ctx_ok).to(dev)
+        grads.index_add_(0, torch.from_numpy(np.where(ctx_rows == EMPTY, 0, ctx_rows)).to(dev).long()[ok_c], d_ctx[ok_c])
+        ok_n = torch.from_numpy(neg_ok).to(dev)
+        grads.index_add_(0, torch.from_numpy(np.where(neg_ok, negs, 0)).to(dev).long()[ok_n], d_neg[ok_n])
+    return grads, loss, n_pairs

@@ -276,3 +276,25 @@ def test_word2vec_loss_decreases(device):
         losses.append(w.mean_loss())
     assert all(np.isfinite(losses))
     assert np.mean(losses[-5:]) < 0.9 * np.mean(losses[:3]), losses
+
+
+def test_word2vec_tcgen05_loss_decreases(device):
+    from swiftsnails_b200.models.word2vec import Word2VecConfig, Word2VecWorker, synthetic_corpus
+    from swiftsnails_b200.ops._util import u32_tensor
+    from swiftsnails_b200.ops.table import ShardedTable, round_capacity
+
+    cfg = Word2VecConfig(vocab=2000, dim=128, window=3, negatives=5, neg_pool=16, sent_len=50,
+                         tokens_per_step=4096, lr=0.05, optimizer="adagrad", tile_impl="tcgen05")
+    table = ShardedTable.local(round_capacity(2 * cfg.vocab), cfg.dim, device, num_shards=2, frag_num=16,
+                               with_state=True, init_scale=1.0 / cfg.dim)
+    w = Word2VecWorker(cfg, table, device)
+    base = synthetic_corpus(cfg.vocab, cfg.tokens_per_step * 30, seed=3)
+    base[1::2] = (base[0::2] * 7 + 1) % cfg.vocab
+    losses = []
+    for s in range(30):
+        tok = u32_tensor(base[s * cfg.tokens_per_step:(s + 1) * cfg.tokens_per_step], device)
+        w.reset_loss()
+        w.step(tok)
+        losses.append(w.mean_loss())
+    assert all(np.isfinite(losses))
+    assert np.mean(losses[-5:]) < 0.9 * np.mean(losses[:3]), losses
