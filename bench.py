@@ -43,6 +43,8 @@ def parse_args():
     ap.add_argument("--optimizer", default="adagrad", choices=["sgd", "adagrad"])
     ap.add_argument("--tile-impl", default="auto", choices=["auto", "cuda_core", "tcgen05"])
     ap.add_argument("--lr", type=float, default=0.05)
+    ap.add_argument("--zipf-s", type=float, default=1.0)
+    ap.add_argument("--tc-mode", type=int, default=1, help="tcgen05 kernel mode bits (1 = TMA gather4; 2 = perf experiment: skip gradient reds)")
     ap.add_argument("--ref-tokens", type=int, default=200_000, help="tokens per worker for the reference arm")
     return ap.parse_args()
 
@@ -81,7 +83,7 @@ def run_ours(args):
                                   and os.environ.get("SSB200_NO_TC") != "1") else "cuda_core"
     cfg = Word2VecConfig(vocab=args.vocab, dim=args.dim, window=args.window, negatives=args.negatives,
                          neg_pool=args.neg_pool, tokens_per_step=args.tokens_per_step, lr=args.lr,
-                         optimizer=args.optimizer, seed=1 + rank, tile_impl=tile_impl)
+                         optimizer=args.optimizer, seed=1 + rank, tile_impl=tile_impl, zipf_s=args.zipf_s)
     # 2*vocab keys (input + output vectors) spread over `world` shards at load factor 0.5
     rows_per_shard = (2 * cfg.vocab + world - 1) // world
     table = make_table(rows_per_shard, cfg.dim, dev, with_state=(cfg.optimizer == "adagrad"),
@@ -104,6 +106,7 @@ def run_ours(args):
 
     # ---------------- device-timed arm: batches already on the device -------------------------
     worker = Word2VecWorker(cfg, table, dev)
+    worker.tma_mode = args.tc_mode
     dev_tokens = host.to(dev)
     for s in range(W):
         worker.step(dev_tokens[s])

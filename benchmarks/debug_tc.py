@@ -42,22 +42,22 @@ for name, lo, hi in (("in", 0, U1), ("ctx", U1, U2), ("neg", U2, U3)):
               " sum ref %.4f got %.4f" % (r[i].sum().item(), g[i].sum().item()))
 
 # ---- raw dump of tile 0: G (swizzled smem image), TMEM S | dIn | dON^T ----
-dbg = torch.zeros(24576 + 128 * 448, device=dev)
+dbg = torch.zeros(32768 + 128 * 416, device=dev)
 grads.zero_(); loss.zero_()
 sgns.sgns_block_tc(params_bf16, grads, u32_tensor(inv_in, dev), u32_tensor(inv_out, dev), sent_len, window, 7, 123,
                    u32_tensor(neg, dev), 5.0, loss, mode=mode, box_rows=box, debug=dbg)
 torch.cuda.synchronize()
 d = dbg.cpu().numpy()
-Gs = d[:24576].reshape(3, 128, 64)   # [col block][row][64 bf16 swizzled in 16B chunks]
-Gf = np.zeros((128, 192), np.float32)
-for cb in range(3):
+Gs = d[:32768].reshape(4, 128, 64)   # [col block][row][64 bf16 swizzled in 16B chunks]
+Gf = np.zeros((128, 256), np.float32)
+for cb in range(4):
     for r in range(128):
         row = Gs[cb, r].reshape(8, 8)
         for ch in range(8):
             Gf[r, cb * 64 + ch * 8: cb * 64 + ch * 8 + 8] = row[ch ^ (r & 7)]
 G = Gf[:, :160]
-T = d[24576:].reshape(128, 448)
-S, dIn, dOnT = T[:, :160], T[:, 160:288], T[:, 288:448]
+T = d[32768:].reshape(128, 416)
+dOnB, dIn, dOnA = T[:, :128], T[:, 160:288], T[:, 288:416]
 P = params.cpu().numpy()
 A = P[inv_in[:128]]
 ctx_tok = np.arange(-8, 136)
@@ -65,11 +65,13 @@ ON = np.zeros((160, 128), np.float32)
 ok = (ctx_tok >= 0) & (ctx_tok < n_tok)
 ON[:144][ok] = P[inv_out[ctx_tok[ok]]]
 ON[144:] = P[neg[:16]]
-S_ref = A @ ON.T
-print("S err", np.abs(S - S_ref).max(), "G nnz", int((G != 0).sum()), "G absmax", np.abs(G).max())
+print("G nnz", int((G != 0).sum()), "G absmax", np.abs(G).max())
 dIn_ref = G @ ON
-dOnT_ref = A.T @ G
+dOn_ref = G.T @ A
+dOnT_ref = dOn_ref[:128]
+dOnT = dOnA
+print("dOnB err", np.abs(dOnB[:32] - dOn_ref[128:160]).max())
 print("dIn  max|ref| %.4f max|got| %.4f err %.4f" % (np.abs(dIn_ref).max(), np.abs(dIn).max(), np.abs(dIn - dIn_ref).max()))
 print("dOnT max|ref| %.4f max|got| %.4f err %.4f" % (np.abs(dOnT_ref).max(), np.abs(dOnT).max(), np.abs(dOnT - dOnT_ref).max()))
 print("dIn got[0,:6]", dIn[0, :6], "ref", dIn_ref[0, :6])
-print("dOnT got[0,8:14]", dOnT[0, 8:14], "ref", dOnT_ref[0, 8:14])
+print("dOnA got[9,:6]", dOnT[9, :6], "ref", dOnT_ref[9, :6])

@@ -30,38 +30,46 @@
 namespace ssb {
 namespace tc {
 
-constexpr int kD = 128;          // embedding dim (floats)
+constexpr int kD = 128;          // embedding dim
 constexpr int kM = 128;          // centre tokens per tile
 constexpr int kHalo = 8;         // max window
 constexpr int kCtx = kM + 2 * kHalo;   // 144 context rows
 constexpr int kNeg = 16;
 constexpr int kN = kCtx + kNeg;  // 160
-constexpr int kThreads = 256;
+constexpr int kConsumerWarps = 16;
+constexpr int kConsumers = kConsumerWarps * 32;   // 512 epilogue / MMA-issue threads
+constexpr int kThreads = kConsumers + 32;         // + 1 producer warp (TMA)
 
 // bf16 operands: a "column block" is 64 elements = 128 bytes wide.
 constexpr uint32_t kInBlk = kM * 128;   // bytes of one [128 rows x 128 B] column block of In / G
 constexpr uint32_t kOnBlk = kN * 128;   // bytes of one [160 rows x 128 B] column block of ON
 constexpr int kInBlks = kD / 64;        // 2
-constexpr int kGBlks = (kN + 63) / 64;  // 3 (the last block is half used)
-constexpr uint32_t kOffIn = 0;
-constexpr uint32_t kOffOn = kOffIn + kInBlks * kInBlk;    // 32768
-constexpr uint32_t kOffG = kOffOn + kInBlks * kOnBlk;     // 73728
-constexpr uint32_t kOffMisc = kOffG + kGBlks * kInBlk;    // 122880
-constexpr uint32_t kSmemBytes = kOffMisc + 2048;
+constexpr int kGBlks = 4;               // 160 columns used; padded to 256 so the second dON MMA stays in bounds
+constexpr uint32_t kInBytes = kInBlks * kInBlk;   // 32768
+constexpr uint32_t kOnBytes = kInBlks * kOnBlk;   // 40960
+constexpr uint32_t kOffIn = 0;                               // 2 stages
+constexpr uint32_t kOffOn = kOffIn + 2 * kInBytes;           // 65536, 2 stages
+constexpr uint32_t kOffG = kOffOn + 2 * kOnBytes;            // 147456
+constexpr uint32_t kOffMisc = kOffG + kGBlks * kInBlk;       // 212992
+constexpr uint32_t kSmemBytes = kOffMisc + 6144;
 
-constexpr uint32_t kTmemS = 0, kTmemDIn = 160, kTmemDOn = 288, kTmemCols = 512;
+// TMEM columns: S (160) | dIn (128) | dON rows 0..127 (128); dON rows 128..255 aliases S.
+constexpr uint32_t kTmemS = 0, kTmemDIn = 160, kTmemDOnA = 288, kTmemDOnB = 0, kTmemCols = 512;
 
 struct Misc {
-  uint32_t in_row[kM];
-  uint32_t on_row[kN];
-  uint32_t col_used[kN];
-  unsigned long long tma_bar;
+  uint32_t in_row[2][kM];
+  uint32_t on_row[2][kN];
+  uint32_t out_rows[kM + kN];   // gradient destination rows of the current tile (INVALID = skip)
+  uint8_t lead_in[2][kM];       // first position in the tile holding the same row (tile-local dedup)
+  uint8_t lead_on[2][kN];
+  unsigned long long full_bar[2];
+  unsigned long long empty_bar[2];
   unsigned long long mma_bar;
   uint32_t tmem_base;
-  float loss[8];
-  float pairs[8];
+  float loss[kConsumerWarps];
+  float pairs[kConsumerWarps];
 };
-static_assert(sizeof(Misc) <= 2048, "misc region too large");
+static_assert(sizeof(Misc) <= 6144, "misc region too large");
 
 // ---- PTX wrappers -----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -75,10 +83,10 @@ __device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t
 // Bounded wait: a lost arrival traps (reported as a launch failure) instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
   uint32_t done = 0;
-  for (uint32_t it = 0; it < (1u << 22); ++it) {
+  for (uint32_t it = 0; it < (1u << 26); ++it) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 1000000;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(done)
         : "r"(smem_u32(bar)), "r"(parity)
@@ -156,21 +164,32 @@ __device__ __forceinline__ uint32_t swz_off(uint32_t r, uint32_t c, uint32_t blk
 }
 
 // ---- the kernel -------------------------------------------------------------------------------
-// mode 0: rows loaded with vector loads + swizzled st.shared; mode 1: TMA tile::gather4.
+// Warp roles: warps 0..15 = consumers (thread 0 issues the MMAs, all 512 threads run the TMEM
+// epilogues: warp w owns TMEM lanes 32*(w%4).. and column part w/4), warp 16 = producer
+// (row indices + TMA gather4 of the NEXT tile while the current one is computed; 2 stages).
+// mode 0: producer copies rows with vector loads + swizzled st.shared; mode 1: TMA tile::gather4.
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory"); }
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict__ grads,
                      const uint32_t* __restrict__ inv_in, const uint32_t* __restrict__ inv_out,
-                     int64_t n_tok, int sent_len, int window, uint64_t seed, uint64_t offset,
+                     int n_tok, int sent_len, int window, uint64_t seed, uint64_t offset,
                      const uint32_t* __restrict__ neg_idx, float neg_k, float* __restrict__ loss_out,
                      const __grid_constant__ CUtensorMap tmap, int mode, float* __restrict__ debug) {
   extern __shared__ __align__(1024) uint8_t smem[];
   Misc* misc = reinterpret_cast<Misc*>(smem + kOffMisc);
   const uint32_t sbase = smem_u32(smem);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int64_t n_tiles = (n_tok + kM - 1) / kM;
+  const int n_tiles = (n_tok + kM - 1) / kM;
 
   if (tid == 0) {
-    mbar_init(&misc->tma_bar, 1);
+    mbar_init(&misc->full_bar[0], 1);
+    mbar_init(&misc->full_bar[1], 1);
+    mbar_init(&misc->empty_bar[0], 1);
+    mbar_init(&misc->empty_bar[1], 1);
     mbar_init(&misc->mma_bar, 1);
     fence_barrier_init();
   }
@@ -178,231 +197,286 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
   // G starts all-zero; each tile rewrites only the band windows and the negative columns
   for (uint32_t i = tid; i < kGBlks * kInBlk / 16; i += kThreads)
     reinterpret_cast<float4*>(smem + kOffG)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = misc->tmem_base;
 
-  uint32_t tma_phase = 0, mma_phase = 0;
-  float loss_acc = 0.f, pair_acc = 0.f;
-
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const int64_t t0 = tile * kM;
-    // ---- 1. row indices -------------------------------------------------------------------
-    if (tid < kM) {
-      int64_t g = t0 + tid;
-      misc->in_row[tid] = (g < n_tok) ? inv_in[g] : SSB_INVALID_SLOT;
-    }
-    if (tid < kN) {
-      uint32_t r;
-      if (tid < kCtx) {
-        int64_t g = t0 - kHalo + tid;
-        r = (g >= 0 && g < n_tok) ? inv_out[g] : SSB_INVALID_SLOT;
-      } else {
-        r = neg_idx[tile * kNeg + (tid - kCtx)];
+  if (warp == kConsumerWarps) {
+    // =========================== producer warp ===========================================
+    uint32_t it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int b = it & 1;
+      const int t0 = tile * kM;
+      if (it >= 2) mbar_wait(&misc->empty_bar[b], ((it >> 1) - 1) & 1);   // stage freed by the MMAs of tile it-2
+      for (int r = lane; r < kM; r += 32) {
+        int g = t0 + r;
+        misc->in_row[b][r] = (g < n_tok) ? inv_in[g] : SSB_INVALID_SLOT;
       }
-      misc->on_row[tid] = r;
-      misc->col_used[tid] = 0;
-    }
-    __syncthreads();
-
-    // ---- 2. gather rows into swizzled smem -------------------------------------------------
-    if (mode == 1) {
-      if (tid == 0) {
-        mbar_expect_tx(&misc->tma_bar, (kM + kN) * kD * 2);
-        for (int r = 0; r < kM; r += 4) {
-          uint32_t i0 = misc->in_row[r], i1 = misc->in_row[r + 1], i2 = misc->in_row[r + 2], i3 = misc->in_row[r + 3];
-          i0 = i0 == SSB_INVALID_SLOT ? 0 : i0; i1 = i1 == SSB_INVALID_SLOT ? 0 : i1;
-          i2 = i2 == SSB_INVALID_SLOT ? 0 : i2; i3 = i3 == SSB_INVALID_SLOT ? 0 : i3;
-#pragma unroll
-          for (int cb = 0; cb < kInBlks; ++cb)
-            tma_gather4(sbase + kOffIn + cb * kInBlk + r * 128, &tmap, &misc->tma_bar, cb * 64, i0, i1, i2, i3);
+      for (int r = lane; r < kN; r += 32) {
+        uint32_t v;
+        if (r < kCtx) {
+          int g = t0 - kHalo + r;
+          v = (g >= 0 && g < n_tok) ? inv_out[g] : SSB_INVALID_SLOT;
+        } else {
+          v = neg_idx[(size_t)tile * kNeg + (r - kCtx)];
         }
-        for (int r = 0; r < kN; r += 4) {
-          uint32_t i0 = misc->on_row[r], i1 = misc->on_row[r + 1], i2 = misc->on_row[r + 2], i3 = misc->on_row[r + 3];
-          i0 = i0 == SSB_INVALID_SLOT ? 0 : i0; i1 = i1 == SSB_INVALID_SLOT ? 0 : i1;
-          i2 = i2 == SSB_INVALID_SLOT ? 0 : i2; i3 = i3 == SSB_INVALID_SLOT ? 0 : i3;
-#pragma unroll
-          for (int cb = 0; cb < kInBlks; ++cb)
-            tma_gather4(sbase + kOffOn + cb * kOnBlk + r * 128, &tmap, &misc->tma_bar, cb * 64, i0, i1, i2, i3);
-        }
+        misc->on_row[b][r] = v;
       }
-      mbar_wait(&misc->tma_bar, tma_phase);
-      tma_phase ^= 1;
-    } else {
-      // half a warp per row: 16 lanes x 16 B = 256 B of bf16
-      for (int r = warp * 2 + (lane >> 4); r < kM + kN; r += kThreads / 16) {
-        const bool is_in = r < kM;
-        const uint32_t rr = is_in ? r : r - kM;
-        const int l16 = lane & 15;
-        uint32_t row = is_in ? misc->in_row[rr] : misc->on_row[rr];
-        uint4 v = make_uint4(0u, 0u, 0u, 0u);
-        if (row != SSB_INVALID_SLOT) v = *reinterpret_cast<const uint4*>(params + (size_t)row * kD + l16 * 8);
-        uint32_t off = (is_in ? kOffIn : kOffOn) + swz_off(rr, l16 * 8, is_in ? kInBlk : kOnBlk);
-        *reinterpret_cast<uint4*>(smem + off) = v;
-      }
-      fence_proxy_async();
-    }
-    __syncthreads();
-
-    // ---- 3. S = In . ON^T ------------------------------------------------------------------
-    if (tid == 0) {
-      tc_fence_after();
-      constexpr uint32_t idesc = make_idesc(kM, kN, 0, 0);
-#pragma unroll
-      for (int s = 0; s < kD / 16; ++s) {
-        uint64_t a = make_desc(sbase + kOffIn + (s >> 2) * kInBlk + (s & 3) * 32, 16, 1024);
-        uint64_t b = make_desc(sbase + kOffOn + (s >> 2) * kOnBlk + (s & 3) * 32, 16, 1024);
-        umma_bf16(tmem + kTmemS, a, b, idesc, s > 0);
-      }
-      umma_commit(&misc->mma_bar);
-    }
-    mbar_wait(&misc->mma_bar, mma_phase);
-    mma_phase ^= 1;
-    tc_fence_after();
-
-    // ---- 4. epilogue 1: logits -> loss and dL/dS (band + negatives) --------------------------
-    if (warp < 4) {
-      const int i = tid;                       // tile row = TMEM lane
-      const int64_t gi = t0 + i;
-      const uint32_t my_in = misc->in_row[i];
-      const bool row_ok = my_in != SSB_INVALID_SLOT;
-      int eff = 0;
-      if (row_ok) {
-        uint32_t r4[4];
-        Philox::gen(seed, offset + (uint64_t)gi, r4);
-        eff = window - (int)(r4[0] % (uint32_t)window);
-      }
-      const int64_t sent = gi / sent_len;
-      const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
-      float m_i = 0.f;
-      // band window: columns [32*warp, 32*warp + 48)
-#pragma unroll
-      for (int blk = 0; blk < 3; ++blk) {
-        float v[16];
-        const int c0 = warp * 32 + blk * 16;
-        tmem_ld16(lane_base + kTmemS + c0, v);
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int c = c0 + j;
-          const int rel = c - (i + kHalo);
-          const int64_t tok = t0 - kHalo + c;
-          bool ok = row_ok && rel != 0 && rel >= -eff && rel <= eff && tok >= 0 && tok < n_tok &&
-                    (tok / sent_len) == sent && misc->on_row[c] != SSB_INVALID_SLOT;
-          float g = 0.f;
-          if (ok) {
-            g = fast_sigmoid(v[j]) - 1.0f;
-            loss_acc += neg_log_sigmoid(v[j]);
-            m_i += 1.f;
-            misc->col_used[c] = 1;
-          }
-          *reinterpret_cast<__nv_bfloat16*>(smem + kOffG + swz_off(i, c, kInBlk)) = __float2bfloat16_rn(g);
-        }
-      }
-      pair_acc += m_i;
-      // negatives: weight m_i * K / 16 each (K negatives per pair in expectation)
+      __syncwarp();
+      // tile-local dedup: lead[p] = first position with the same row id. Duplicate positions fold
+      // their dL/dS entries into the leader's row/column of G, so every distinct row gets ONE
+      // gradient reduction per tile (hot words would otherwise serialise on the same address).
       {
-        float v[16];
-        tmem_ld16(lane_base + kTmemS + kCtx, v);
-        const float w = m_i * neg_k * (1.0f / kNeg);
+        uint32_t v[5];
+        int ld[5];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const uint32_t nr = misc->on_row[kCtx + j];
-          float g = 0.f;
-          if (m_i > 0.f && nr != SSB_INVALID_SLOT) {
-            g = w * fast_sigmoid(v[j]);
-            loss_acc += w * neg_log_sigmoid(-v[j]);
-            misc->col_used[kCtx + j] = 1;
-          }
-          *reinterpret_cast<__nv_bfloat16*>(smem + kOffG + swz_off(i, kCtx + j, kInBlk)) = __float2bfloat16_rn(g);
+        for (int k = 0; k < 4; ++k) { v[k] = misc->in_row[b][lane + 32 * k]; ld[k] = lane + 32 * k; }
+        for (int j = 0; j < kM; ++j) {
+          const uint32_t x = misc->in_row[b][j];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) if (v[k] == x) ld[k] = min(ld[k], j);
         }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) misc->lead_in[b][lane + 32 * k] = (uint8_t)ld[k];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) { v[k] = misc->on_row[b][lane + 32 * k]; ld[k] = lane + 32 * k; }
+        for (int j = 0; j < kN; ++j) {
+          const uint32_t x = misc->on_row[b][j];
+#pragma unroll
+          for (int k = 0; k < 5; ++k) if (v[k] == x) ld[k] = min(ld[k], j);
+        }
+#pragma unroll
+        for (int k = 0; k < 5; ++k) misc->lead_on[b][lane + 32 * k] = (uint8_t)ld[k];
       }
-      fence_proxy_async();
-      tc_fence_before();
+      __syncwarp();
+      const uint32_t in_base = kOffIn + b * kInBytes, on_base = kOffOn + b * kOnBytes;
+      if (mode & 1) {
+        if (lane == 0) mbar_expect_tx(&misc->full_bar[b], (kM + kN) * kD * 2);
+        __syncwarp();
+        // 72 groups of 4 rows (32 In + 40 ON), each 2 column blocks; spread over the lanes
+        for (int g = lane; g < (kM + kN) / 4; g += 32) {
+          const bool is_in = g < kM / 4;
+          const int r = is_in ? g * 4 : (g - kM / 4) * 4;
+          const uint32_t* rows = is_in ? &misc->in_row[b][r] : &misc->on_row[b][r];
+          uint32_t i0 = rows[0], i1 = rows[1], i2 = rows[2], i3 = rows[3];
+          i0 = i0 == SSB_INVALID_SLOT ? 0 : i0; i1 = i1 == SSB_INVALID_SLOT ? 0 : i1;
+          i2 = i2 == SSB_INVALID_SLOT ? 0 : i2; i3 = i3 == SSB_INVALID_SLOT ? 0 : i3;
+          const uint32_t dst = sbase + (is_in ? in_base : on_base) + r * 128;
+          const uint32_t blk = is_in ? kInBlk : kOnBlk;
+          tma_gather4(dst, &tmap, &misc->full_bar[b], 0, i0, i1, i2, i3);
+          tma_gather4(dst + blk, &tmap, &misc->full_bar[b], 64, i0, i1, i2, i3);
+        }
+      } else {
+        // half a warp per row: 16 lanes x 16 B = 256 B of bf16
+        for (int r = lane >> 4; r < kM + kN; r += 2) {
+          const bool is_in = r < kM;
+          const uint32_t rr = is_in ? r : r - kM;
+          const int l16 = lane & 15;
+          uint32_t row = is_in ? misc->in_row[b][rr] : misc->on_row[b][rr];
+          uint4 v = make_uint4(0u, 0u, 0u, 0u);
+          if (row != SSB_INVALID_SLOT) v = *reinterpret_cast<const uint4*>(params + (size_t)row * kD + l16 * 8);
+          uint32_t off = (is_in ? in_base : on_base) + swz_off(rr, l16 * 8, is_in ? kInBlk : kOnBlk);
+          *reinterpret_cast<uint4*>(smem + off) = v;
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&misc->full_bar[b]);
+      }
     }
-    __syncthreads();
-    if (debug && tile == 0)
-      for (uint32_t i = tid; i < kGBlks * kInBlk / 2; i += kThreads)
-        debug[i] = __bfloat162float(reinterpret_cast<__nv_bfloat16*>(smem + kOffG)[i]);
+  } else {
+    // =========================== consumer warps ==========================================
+    const int q = warp & 3, part = warp >> 2;       // TMEM lane quarter, column part
+    const int i = q * 32 + lane;                    // tile row = TMEM lane
+    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+    uint32_t mma_phase = 0, it = 0;
+    float loss_acc = 0.f, pair_acc = 0.f;
 
-    // ---- 5. dIn = G . ON ;  dON^T = In^T . G ------------------------------------------------
-    if (tid == 0) {
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+      const int b = it & 1;
+      const int t0 = tile * kM;
+      const uint32_t in_s = sbase + kOffIn + b * kInBytes, on_s = sbase + kOffOn + b * kOnBytes;
+      mbar_wait(&misc->full_bar[b], (it >> 1) & 1);
+
+      // ---- S = In . ON^T --------------------------------------------------------------------
+      if (tid == 0) {
+        tc_fence_after();
+        constexpr uint32_t idesc = make_idesc(kM, kN, 0, 0);
+#pragma unroll
+        for (int s = 0; s < kD / 16; ++s) {
+          uint64_t a = make_desc(in_s + (s >> 2) * kInBlk + (s & 3) * 32, 16, 1024);
+          uint64_t bd = make_desc(on_s + (s >> 2) * kOnBlk + (s & 3) * 32, 16, 1024);
+          umma_bf16(tmem + kTmemS, a, bd, idesc, s > 0);
+        }
+        umma_commit(&misc->mma_bar);
+      }
+      mbar_wait(&misc->mma_bar, mma_phase);
+      mma_phase ^= 1;
       tc_fence_after();
-      constexpr uint32_t idesc2 = make_idesc(kM, kD, 0, 1);
-#pragma unroll
-      for (int s = 0; s < kN / 16; ++s) {     // K = 160 context/negative rows, 16 per step
-        uint64_t a = make_desc(sbase + kOffG + (s >> 2) * kInBlk + (s & 3) * 32, 16, 1024);
-        uint64_t b = make_desc(sbase + kOffOn + s * 2048, kOnBlk, 1024);
-        umma_bf16(tmem + kTmemDIn, a, b, idesc2, s > 0);
-      }
-      constexpr uint32_t idesc3 = make_idesc(kD, kN, 1, 1);
-#pragma unroll
-      for (int s = 0; s < kM / 16; ++s) {     // K = 128 centre tokens, 16 per step
-        uint64_t a = make_desc(sbase + kOffIn + s * 2048, kInBlk, 1024);
-        uint64_t b = make_desc(sbase + kOffG + s * 2048, kInBlk, 1024);
-        umma_bf16(tmem + kTmemDOn, a, b, idesc3, s > 0);
-      }
-      umma_commit(&misc->mma_bar);
-    }
-    mbar_wait(&misc->mma_bar, mma_phase);
-    mma_phase ^= 1;
-    tc_fence_after();
 
-    // ---- 6. epilogue 2: gradients out through vector red -------------------------------------
-    if (warp < 4) {
-      const int i = tid;
-      const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
-      const uint32_t my_in = misc->in_row[i];
-      if (debug && tile == 0) {
-        float* d1 = debug + kGBlks * kInBlk / 2;
-        for (int blk = 0; blk < 28; ++blk) {   // all 448 used columns: S | dIn | dON^T
-          float v[16];
-          tmem_ld16(lane_base + blk * 16, v);
-          for (int j = 0; j < 16; ++j) d1[(size_t)i * 448 + blk * 16 + j] = v[j];
-        }
+      // Gradient destination rows for epilogue 2, copied out of the stage's index arrays now (the
+      // producer may refill them as soon as the gradient MMAs retire). Non-leaders are skipped:
+      // their contribution has been folded into the leader's row / column of G.
+      if (tid < kM) {
+        misc->out_rows[tid] = (misc->lead_in[b][tid] == tid) ? misc->in_row[b][tid] : SSB_INVALID_SLOT;
+      } else if (tid < kM + kN) {
+        const int c = tid - kM;
+        misc->out_rows[tid] = (misc->lead_on[b][c] == c) ? misc->on_row[b][c] : SSB_INVALID_SLOT;
       }
-      // dIn row i -> grads[in_row[i]]
-#pragma unroll
-      for (int blk = 0; blk < kD / 16; ++blk) {
+
+      // ---- epilogue 1: logits -> loss and dL/dS (band + negatives) ---------------------------
+      {
+        const int gi = t0 + i;
+        const uint32_t my_in = misc->in_row[b][i];
+        const bool row_ok = my_in != SSB_INVALID_SLOT;
+        const uint32_t li = misc->lead_in[b][i];
+        int eff = 0;
+        if (row_ok) {
+          uint32_t r4[4];
+          Philox::gen(seed, offset + (uint64_t)gi, r4);
+          eff = window - (int)(r4[0] % (uint32_t)window);
+        }
+        const int s_lo = (gi / sent_len) * sent_len;
+        const int tok_lo = max(s_lo, 0), tok_hi = min(s_lo + sent_len, n_tok);
+        // column c <-> token t0 - 8 + c ; centre i <-> column i + 8
+        auto col_ok = [&](int c) -> bool {
+          const int rel = c - (i + kHalo);
+          const int tok = t0 - kHalo + c;
+          return row_ok && rel != 0 && rel >= -eff && rel <= eff && tok >= tok_lo && tok < tok_hi &&
+                 misc->on_row[b][c] != SSB_INVALID_SLOT;
+        };
+        // G[lead(i)][lead(c)] += g   (bf16x2 shared-memory reduction; G was zeroed by the previous tile)
+        auto g_add = [&](int c, float g) {
+          const uint32_t lc = misc->lead_on[b][c];
+          __nv_bfloat162 pk = (lc & 1) ? __floats2bfloat162_rn(0.f, g) : __floats2bfloat162_rn(g, 0.f);
+          const uint32_t addr = sbase + kOffG + swz_off(li, lc & ~1u, kInBlk);
+          asm volatile("red.shared::cta.add.noftz.bf16x2 [%0], %1;" ::"r"(addr), "r"(*reinterpret_cast<uint32_t*>(&pk)) : "memory");
+        };
         float v[16];
-        tmem_ld16(lane_base + kTmemDIn + blk * 16, v);
-        if (my_in != SSB_INVALID_SLOT) {
-          float* dst = grads + (size_t)my_in * kD + blk * 16;
+        if (part < 3) {
+          const int c0 = q * 32 + part * 16;          // band window of this lane quarter: [32q, 32q+48)
+          tmem_ld16(lane_base + kTmemS + c0, v);
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            float4 x = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-            if (x.x != 0.f || x.y != 0.f || x.z != 0.f || x.w != 0.f) red_add_f4_gpu(dst + 4 * q, x);
+          for (int j = 0; j < 16; ++j) {
+            if (col_ok(c0 + j)) {
+              g_add(c0 + j, fast_sigmoid(v[j]) - 1.0f);
+              loss_acc += neg_log_sigmoid(v[j]);
+              pair_acc += 1.f;
+            }
+          }
+        } else {
+          // negatives: weight m_i * K / 16 each, m_i = number of valid contexts of centre i
+          float m_i = 0.f;
+#pragma unroll
+          for (int c = 0; c <= 2 * kHalo; ++c) m_i += col_ok(i + c) ? 1.f : 0.f;
+          tmem_ld16(lane_base + kTmemS + kCtx, v);
+          const float w = m_i * neg_k * (1.0f / kNeg);
+          if (m_i > 0.f) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              if (misc->on_row[b][kCtx + j] != SSB_INVALID_SLOT) {
+                g_add(kCtx + j, w * fast_sigmoid(v[j]));
+                loss_acc += w * neg_log_sigmoid(-v[j]);
+              }
+            }
           }
         }
+        fence_proxy_async();
+        tc_fence_before();
       }
-      // dON^T: lane = d, columns = context/negative row j -> grads[on_row[j]][d]
+      consumer_sync();
+      if (debug && tile == 0)
+        for (uint32_t k = tid; k < kGBlks * kInBlk / 2; k += kConsumers)
+          debug[k] = __bfloat162float(reinterpret_cast<__nv_bfloat16*>(smem + kOffG)[k]);
+
+      // ---- dIn = G . ON ;  dON = G^T . In (rows 0..127 and 128..255) ---------------------------
+      if (tid == 0) {
+        tc_fence_after();
+        constexpr uint32_t idesc2 = make_idesc(kM, kD, 0, 1);
 #pragma unroll
-      for (int blk = 0; blk < kN / 16; ++blk) {
-        float v[16];
-        tmem_ld16(lane_base + kTmemDOn + blk * 16, v);
+        for (int s = 0; s < kN / 16; ++s) {     // K = 160 context/negative rows, 16 per step
+          uint64_t a = make_desc(sbase + kOffG + (s >> 2) * kInBlk + (s & 3) * 32, 16, 1024);
+          uint64_t bd = make_desc(on_s + s * 2048, kOnBlk, 1024);
+          umma_bf16(tmem + kTmemDIn, a, bd, idesc2, s > 0);
+        }
+        constexpr uint32_t idesc3 = make_idesc(128, kD, 1, 1);
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int c = blk * 16 + j;
-          const uint32_t row = misc->on_row[c];
-          if (misc->col_used[c] && row != SSB_INVALID_SLOT) atomicAdd(grads + (size_t)row * kD + i, v[j]);
+        for (int s = 0; s < kM / 16; ++s) {     // K = 128 centre tokens, 16 per step
+          uint64_t bd = make_desc(in_s + s * 2048, kInBlk, 1024);
+          uint64_t a0 = make_desc(sbase + kOffG + s * 2048, kInBlk, 1024);
+          uint64_t a1 = make_desc(sbase + kOffG + 2 * kInBlk + s * 2048, kInBlk, 1024);
+          umma_bf16(tmem + kTmemDOnA, a0, bd, idesc3, s > 0);
+          umma_bf16(tmem + kTmemDOnB, a1, bd, idesc3, s > 0);
+        }
+        umma_commit(&misc->empty_bar[b]);   // the stage's In / ON are free once these MMAs retire
+        umma_commit(&misc->mma_bar);
+      }
+      mbar_wait(&misc->mma_bar, mma_phase);
+      mma_phase ^= 1;
+      tc_fence_after();
+
+      if (debug && tile == 0 && part == 0) {
+        float* d1 = debug + kGBlks * kInBlk / 2;
+        for (int blk = 0; blk < 26; ++blk) {   // 416 columns: dONb | pad | dIn | dONa
+          float vv[16];
+          tmem_ld16(lane_base + blk * 16, vv);
+          for (int j = 0; j < 16; ++j) d1[(size_t)i * 416 + blk * 16 + j] = vv[j];
         }
       }
-      tc_fence_before();
-    }
-    __syncthreads();
-  }
 
-  // ---- teardown -------------------------------------------------------------------------------
-  if (warp < 4) {
+      // ---- epilogue 2: TMEM -> fp32 staging in shared memory (the G region is dead now) -> one
+      //      coalesced 512-byte vector red per gradient row. TMEM holds a row per lane; staging
+      //      transposes that into a row per warp so 32 lanes reduce 32 x 16 contiguous bytes.
+      {
+        float* stage = reinterpret_cast<float*>(smem + kOffG);      // [128 rows][128 fp32], 16 B chunks swizzled by row
+        const uint32_t tcol[3] = {kTmemDIn, kTmemDOnA, kTmemDOnB};
+        const int nrows[3] = {kM, kM, kN - kM};
+        const int row_base[3] = {0, kM, 2 * kM};                    // into misc->out_rows
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          if (k < 2 || q == 0) {                                    // dON rows 128..159 live in lanes 0..31 only
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              float v[16];
+              tmem_ld16(lane_base + tcol[k] + part * 32 + h * 16, v);
+#pragma unroll
+              for (int x4 = 0; x4 < 4; ++x4) {
+                const int chunk = part * 8 + h * 4 + x4;
+                *reinterpret_cast<float4*>(stage + i * kD + ((chunk ^ (i & 7)) << 2)) =
+                    make_float4(v[4 * x4], v[4 * x4 + 1], v[4 * x4 + 2], v[4 * x4 + 3]);
+              }
+            }
+          }
+          tc_fence_before();
+          consumer_sync();
+          for (int r = warp; r < nrows[k]; r += kConsumerWarps) {
+            const uint32_t row = misc->out_rows[row_base[k] + r];
+            if (row == SSB_INVALID_SLOT) continue;
+            const float4 x = *reinterpret_cast<const float4*>(stage + r * kD + ((lane ^ (r & 7)) << 2));
+            if ((x.x != 0.f || x.y != 0.f || x.z != 0.f || x.w != 0.f) && !(mode & 2))
+              red_add_f4_gpu(grads + (size_t)row * kD + lane * 4, x);
+          }
+          consumer_sync();
+        }
+        // leave G zeroed for the next tile (columns 0..191; block 3 is never read back)
+        for (uint32_t z = tid; z < 3 * kInBlk / 16; z += kConsumers)
+          reinterpret_cast<float4*>(smem + kOffG)[z] = make_float4(0.f, 0.f, 0.f, 0.f);
+        fence_proxy_async();
+      }
+      consumer_sync();
+    }
     loss_acc = warp_sum(loss_acc);
     pair_acc = warp_sum(pair_acc);
     if (lane == 0) { misc->loss[warp] = loss_acc; misc->pairs[warp] = pair_acc; }
   }
+
+  // ---- teardown -------------------------------------------------------------------------------
   tc_fence_before();
   __syncthreads();
   if (tid == 0) {
-    float l = misc->loss[0] + misc->loss[1] + misc->loss[2] + misc->loss[3];
-    float p = misc->pairs[0] + misc->pairs[1] + misc->pairs[2] + misc->pairs[3];
+    float l = 0.f, p = 0.f;
+    for (int w = 0; w < kConsumerWarps; ++w) { l += misc->loss[w]; p += misc->pairs[w]; }
     if (l != 0.f) atomicAdd(loss_out, l);
     if (p != 0.f) atomicAdd(loss_out + 1, p);
   }
@@ -457,10 +531,11 @@ int ssb_sgns_block_tc(const void* params, float* grads, int64_t n_rows, int32_t 
                       int32_t box_rows, float* debug, void* stream) {
   using namespace ssb::tc;
   if (n_tok <= 0) return 0;
+  if (n_tok >= (1ll << 31) - 4096) return (int)cudaErrorInvalidValue;
   if (dim != kD || window < 1 || window > kHalo || sent_len < 1) return (int)cudaErrorInvalidValue;
   CUtensorMap tmap;
   memset(&tmap, 0, sizeof(tmap));
-  if (mode == 1) {
+  if (mode & 1) {
     int e = make_row_tmap(&tmap, params, (uint64_t)n_rows, box_rows > 0 ? (uint32_t)box_rows : 1u);
     if (e) return e;
   }
@@ -473,7 +548,7 @@ int ssb_sgns_block_tc(const void* params, float* grads, int64_t n_rows, int32_t 
   int64_t tiles = (n_tok + kM - 1) / kM;
   int blocks = (int)(tiles < ssb::kNumSMs ? tiles : ssb::kNumSMs);
   sgns_block_tc_kernel<<<blocks, kThreads, kSmemBytes, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)params, grads, inv_in, inv_out, n_tok, sent_len, window, seed, offset, neg_idx, neg_k,
+      (const __nv_bfloat16*)params, grads, inv_in, inv_out, (int)n_tok, sent_len, window, seed, offset, neg_idx, neg_k,
       loss_out, tmap, mode, debug);
   SSB_LAUNCH_CHECK();
   return 0;
