@@ -1,0 +1,181 @@
+// core_capi.cc — C ABI of the host core for the Python layer (declared in include/ssb200_core.h).
+#include <fstream>
+#include "../../include/ssb200_core.h"
+#include "../apps/algorithms.h"
+
+using namespace ssb;
+
+extern "C" {
+
+int ssb_core_version(void) { return 100; }
+
+// ---- config ---------------------------------------------------------------------------------
+void ssb_config_clear(void) { global_config().clear(); }
+int ssb_config_load(const char* path) {
+  std::ifstream probe(path);
+  if (!probe.good()) return -1;
+  global_config().load_conf(path);
+  global_config().parse();
+  return 0;
+}
+void ssb_config_set(const char* key, const char* value) { global_config().set(key, value); }
+int ssb_config_parse_line(const char* line) { return global_config().parse_line(line) ? 1 : 0; }
+int ssb_config_get(const char* key, char* out, int out_len) {
+  if (!global_config().has(key)) return -1;
+  const std::string& v = global_config().get_config(key).to_string();
+  if ((int)v.size() + 1 > out_len) return -2;
+  std::memcpy(out, v.c_str(), v.size() + 1);
+  return (int)v.size();
+}
+int ssb_config_keys(char* out, int out_len) {
+  std::string all;
+  for (auto& kv : global_config().items()) { all += kv.first; all += '\n'; }
+  if ((int)all.size() + 1 > out_len) return -2;
+  std::memcpy(out, all.c_str(), all.size() + 1);
+  return (int)all.size();
+}
+
+// ---- hashing / hash fragments ----------------------------------------------------------------
+uint64_t ssb_hash_code(uint64_t x) { return get_hash_code(x); }
+int ssb_hashfrag_build(int num_nodes, int frag_num, uint32_t* map_out) {
+  if (num_nodes < 1 || frag_num < num_nodes) return -1;
+  BasicHashFrag<uint32_t> h;
+  h.init(num_nodes, frag_num);
+  std::memcpy(map_out, h.map_table().data(), sizeof(uint32_t) * frag_num);
+  return 0;
+}
+void ssb_hashfrag_route(const uint32_t* keys, int64_t n, const uint32_t* map, int frag_num, int32_t* node_out) {
+  for (int64_t i = 0; i < n; ++i) node_out[i] = (int32_t)map[get_hash_code((uint64_t)keys[i]) % (uint64_t)frag_num];
+}
+
+// ---- binary buffer round trip (used by the wire-format tests) ----------------------------------
+int ssb_buffer_selftest(void) {
+  BinaryBuffer bb;
+  bb << (int32_t)-7 << (uint64_t)1234567890123ull << 3.5f << 2.25 << true << (uint8_t)9;
+  for (int i = 0; i < 1000; ++i) bb << (int32_t)i;  // grows past the 1 KiB initial capacity
+  int32_t a; uint64_t b; float c; double d; bool e; uint8_t f;
+  bb >> a >> b >> c >> d >> e >> f;
+  if (a != -7 || b != 1234567890123ull || c != 3.5f || d != 2.25 || !e || f != 9) return 1;
+  for (int i = 0; i < 1000; ++i) { int32_t v; bb >> v; if (v != i) return 2; }
+  return bb.read_finished() ? 0 : 3;
+}
+
+// ---- text parameter dump (the reference's checkpoint format) + loader ----------------------------
+// line = "<key>\t<value>\n"; a row of dim > 1 prints like the reference's Vec: "Vec:\t v0 v1 … "
+// (ref: parameter/sparsetable.h:49-56, utils/vec1.h:106-112); dim 1 prints the scalar.
+int64_t ssb_dump_write_text(const char* path, const uint32_t* keys, const float* rows, int64_t n, int dim, int append) {
+  FILE* f = std::fopen(path, append ? "a" : "w");
+  if (!f) return -1;
+  std::vector<char> buf(1 << 20);
+  std::setvbuf(f, buf.data(), _IOFBF, buf.size());
+  for (int64_t i = 0; i < n; ++i) {
+    const float* r = rows + i * dim;
+    if (dim == 1) {
+      std::fprintf(f, "%u\t%g\n", keys[i], r[0]);
+    } else {
+      std::fprintf(f, "%u\tVec:\t", keys[i]);
+      for (int j = 0; j < dim; ++j) std::fprintf(f, "%g ", r[j]);
+      std::fputc('\n', f);
+    }
+  }
+  std::fclose(f);
+  return n;
+}
+// returns the number of rows read (<= max_n); rows shorter than dim are zero-padded
+int64_t ssb_dump_read_text(const char* path, uint32_t* keys, float* rows, int64_t max_n, int dim) {
+  FILE* f = std::fopen(path, "r");
+  if (!f) return -1;
+  LineFileReader reader;
+  int64_t n = 0;
+  while (n < max_n) {
+    char* line = reader.getline(f);
+    if (!line) break;
+    char* tab = std::strchr(line, '\t');
+    if (!tab) continue;
+    keys[n] = (uint32_t)std::strtoul(line, nullptr, 10);
+    char* p = tab + 1;
+    if (std::strncmp(p, "Vec:", 4) == 0) p += 4;
+    float* r = rows + n * dim;
+    for (int j = 0; j < dim; ++j) {
+      char* end = nullptr;
+      r[j] = std::strtof(p, &end);
+      if (end == p) { for (; j < dim; ++j) r[j] = 0.f; break; }
+      p = end;
+    }
+    ++n;
+  }
+  std::fclose(f);
+  return n;
+}
+
+// ---- CPU sparse table (oracle for the HBM table; SGD / AdaGrad access methods) -------------------
+struct CpuTable {
+  table_t_ table;
+  RowPullMethod<table_t_> pull;
+  SgdPushMethod<table_t_> sgd;
+  AdaGradPushMethod<table_t_> adagrad;
+  int dim;
+  bool use_adagrad;
+  CpuTable(int shards, int dim_, bool ada, float lr, float eps, uint64_t seed, float scale)
+      : table(shards), pull(dim_, ada, seed, scale), sgd(lr), adagrad(lr, eps), dim(dim_), use_adagrad(ada) {}
+};
+void* ssb_cpu_table_new(int shard_num, int dim, int adagrad, float lr, float eps, uint64_t seed, float init_scale) {
+  return new CpuTable(shard_num, dim, adagrad != 0, lr, eps, seed, init_scale);
+}
+void ssb_cpu_table_free(void* t) { delete static_cast<CpuTable*>(t); }
+void ssb_cpu_table_pull(void* tp, const uint32_t* keys, int64_t n, float* rows_out) {
+  auto* t = static_cast<CpuTable*>(tp);
+  PullAccessAgent<table_t_, RowPullMethod<table_t_>> agent(t->table, t->pull);
+  VecF val;
+  for (int64_t i = 0; i < n; ++i) {
+    agent.get_pull_value(keys[i], val);
+    std::memcpy(rows_out + i * t->dim, val.data(), sizeof(float) * t->dim);
+  }
+}
+int64_t ssb_cpu_table_push(void* tp, const uint32_t* keys, const float* grads, int64_t n) {
+  auto* t = static_cast<CpuTable*>(tp);
+  int64_t missing = 0;
+  VecF g((size_t)t->dim);
+  for (int64_t i = 0; i < n; ++i) {
+    std::memcpy(g.data(), grads + i * t->dim, sizeof(float) * t->dim);
+    bool ok;
+    if (t->use_adagrad) {
+      PushAccessAgent<table_t_, AdaGradPushMethod<table_t_>> agent(t->table, t->adagrad);
+      ok = agent.apply_push_value(keys[i], g);
+    } else {
+      PushAccessAgent<table_t_, SgdPushMethod<table_t_>> agent(t->table, t->sgd);
+      ok = agent.apply_push_value(keys[i], g);
+    }
+    if (!ok) ++missing;
+  }
+  return missing;
+}
+int64_t ssb_cpu_table_size(void* tp) { return (int64_t) static_cast<CpuTable*>(tp)->table.size(); }
+int ssb_cpu_table_dump(void* tp, const char* path) {
+  std::ofstream out(path);
+  if (!out.good()) return -1;
+  static_cast<CpuTable*>(tp)->table.output(out);
+  return 0;
+}
+
+// ---- roles (one role per process; they use the process-wide transfer) ----------------------------
+int ssb_run_master(const char* config_path) {
+  if (ssb_config_load(config_path) != 0) return -1;
+  run_master();
+  ps_transfer().shutdown();
+  return 0;
+}
+int ssb_run_server(const char* config_path) {
+  if (ssb_config_load(config_path) != 0) return -1;
+  run_server();
+  ps_transfer().shutdown();
+  return 0;
+}
+int ssb_run_worker(const char* config_path, const char* app, const char* data_path) {
+  if (ssb_config_load(config_path) != 0) return -1;
+  int rc = run_worker(app, data_path ? data_path : "");
+  if (global_config().get_config("local_train", "0").to_int32() == 0) ps_transfer().shutdown();
+  return rc;
+}
+
+}  // extern "C"

@@ -9,7 +9,11 @@ namespace ssb {
 
 class Listener : public VirtualObject {
  public:
-  explicit Listener(void* zmq_ctx) : zmq_ctx_(zmq_ctx) {
+  explicit Listener(void* zmq_ctx = nullptr) { if (zmq_ctx) init_receiver(zmq_ctx); }
+  // create the inbox socket on `zmq_ctx` (the route owns the context, ref: Route.h:23)
+  void init_receiver(void* zmq_ctx) {
+    CHECK(receiver_ == nullptr);
+    zmq_ctx_ = zmq_ctx;
     receiver_ = zmq_socket(zmq_ctx_, ZMQ_PULL);
     PCHECK(receiver_ != nullptr) << "zmq_socket(PULL)";
     int hwm = 0;  // unbounded: a PS inbox must never drop or block senders on HWM

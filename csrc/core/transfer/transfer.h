@@ -55,11 +55,7 @@ class Transfer : public Listener {
 
   Transfer() : Listener(nullptr), route_(new Route) {
     // the route owns the zmq context (ref: Route.h:23); the inbox socket is created on it
-    zmq_ctx_ = route_->zmq_ctx();
-    receiver_ = zmq_socket(zmq_ctx_, ZMQ_PULL);
-    PCHECK(receiver_ != nullptr);
-    int hwm = 0;
-    zmq_setsockopt(receiver_, ZMQ_RCVHWM, &hwm, sizeof(hwm));
+    init_receiver(route_->zmq_ctx());
   }
   ~Transfer() override { shutdown(); }
 

@@ -1,0 +1,53 @@
+/*
+ * ssb200_core.h — C ABI of the C++17 host core (libssb200_core.so): config parser, hash
+ * fragments, the reference-format text dump, the CPU sparse table, and the master / server /
+ * worker roles over ZeroMQ.  `ref:` citations point into /root/reference/src.
+ */
+#pragma once
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int ssb_core_version(void);
+
+/* config — ref: utils/ConfigParser.h:25-129 */
+void ssb_config_clear(void);
+int ssb_config_load(const char *path);                      /* 0 ok, -1 cannot open          */
+void ssb_config_set(const char *key, const char *value);
+int ssb_config_parse_line(const char *line);
+int ssb_config_get(const char *key, char *out, int out_len); /* length, -1 missing, -2 too small */
+int ssb_config_keys(char *out, int out_len);                /* newline-separated key list     */
+
+/* hashing — ref: utils/HashFunction.h:16-24, parameter/hashfrag.h:36-53 */
+uint64_t ssb_hash_code(uint64_t x);
+int ssb_hashfrag_build(int num_nodes, int frag_num, uint32_t *map_out);
+void ssb_hashfrag_route(const uint32_t *keys, int64_t n, const uint32_t *map, int frag_num,
+                        int32_t *node_out);
+
+/* BinaryBuffer self test — ref: utils/Buffer.h:174-234 */
+int ssb_buffer_selftest(void);
+
+/* text parameter dump (`key \t value \n`) and its loader — ref: parameter/sparsetable.h:49-56,
+ * utils/vec1.h:106-112; the loader has no counterpart in the reference (it never reads a dump). */
+int64_t ssb_dump_write_text(const char *path, const uint32_t *keys, const float *rows, int64_t n,
+                            int dim, int append);
+int64_t ssb_dump_read_text(const char *path, uint32_t *keys, float *rows, int64_t max_n, int dim);
+
+/* CPU sparse table with the stock SGD / AdaGrad access methods — ref: parameter/sparsetable.h */
+void *ssb_cpu_table_new(int shard_num, int dim, int adagrad, float lr, float eps, uint64_t seed,
+                        float init_scale);
+void ssb_cpu_table_free(void *t);
+void ssb_cpu_table_pull(void *t, const uint32_t *keys, int64_t n, float *rows_out);
+int64_t ssb_cpu_table_push(void *t, const uint32_t *keys, const float *grads, int64_t n);
+int64_t ssb_cpu_table_size(void *t);
+int ssb_cpu_table_dump(void *t, const char *path);
+
+/* roles — ref: core/framework/SwiftMaster.h, SwiftServer.h, SwiftWorker.h. One role per process. */
+int ssb_run_master(const char *config_path);
+int ssb_run_server(const char *config_path);
+int ssb_run_worker(const char *config_path, const char *app, const char *data_path);
+
+#ifdef __cplusplus
+}
+#endif

@@ -109,7 +109,10 @@ def build_core(verbose=False):
     srcs = sorted(glob.glob(os.path.join(core_dir, "*.cc")))
     if not srcs:
         return None
-    hdrs = glob.glob(os.path.join(core_dir, "*.h")) + glob.glob(os.path.join(ROOT, "include", "*.h"))
+    hdrs = (glob.glob(os.path.join(core_dir, "**", "*.h"), recursive=True)
+            + glob.glob(os.path.join(ROOT, "csrc", "apps", "*.h"))
+            + glob.glob(os.path.join(ROOT, "csrc", "tests", "*.h"))
+            + glob.glob(os.path.join(ROOT, "include", "*.h")))
     libzmq = find_libzmq()
     if libzmq is None:
         raise RuntimeError("libzmq not found (pyzmq.libs); set SSB200_LIBZMQ")

@@ -1,0 +1,178 @@
+"""CPU tests of the C++ host core: unit-test binary, C-ABI bindings, and the automated localhost
+cluster (1 master + 2 servers + 2 workers over ZeroMQ — BASELINE config 1)."""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "swiftsnails_b200", "bin")
+
+
+def test_cpp_unit_tests(native_built):
+    r = subprocess.run([os.path.join(BIN, "unit_tests")], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "0 failed expectations" in r.stdout
+
+
+def test_config_python_matches_native(native_built, tmp_path):
+    from swiftsnails_b200 import _lib
+    from swiftsnails_b200.utils.config import ConfigParser
+
+    (tmp_path / "common.conf").write_text("# c\nfrag_num: 100\nmaster_addr: tcp://127.0.0.1:16831\nfrag_num: 3\n")
+    (tmp_path / "node.conf").write_text("import common.conf\nlisten_addr:\nshard_num: 8 # x\n")
+    py = ConfigParser(str(tmp_path / "node.conf"))
+    assert py.to_int32("frag_num") == 100 and py.get("master_addr") == "tcp://127.0.0.1:16831"
+    assert py.get("listen_addr") == "" and py.to_int32("shard_num") == 8
+    with pytest.raises(KeyError):
+        py.get("nope")
+    lib = _lib.core()
+    lib.ssb_config_clear()
+    assert lib.ssb_config_load(str(tmp_path / "node.conf").encode()) == 0
+    buf = C.create_string_buffer(256)
+    for k, v in py.items.items():
+        n = lib.ssb_config_get(k.encode(), buf, 256)
+        assert n >= 0 and buf.value.decode() == v
+    assert lib.ssb_config_get(b"nope", buf, 256) == -1
+    lib.ssb_config_clear()
+
+
+def test_hashfrag_native_matches_python(native_built):
+    from swiftsnails_b200 import _lib
+    from swiftsnails_b200.parallel.hashfrag import HashFrag, fmix64
+
+    lib = _lib.core()
+    lib.ssb_hash_code.restype = C.c_uint64
+    lib.ssb_hash_code.argtypes = [C.c_uint64]
+    for x in (0, 1, 12345, 2 ** 40 + 7):
+        assert lib.ssb_hash_code(x) == int(fmix64(np.array([x], dtype=np.uint64))[0])
+    for nodes, frags in ((2, 100), (7, 100), (8, 1024)):
+        hf = HashFrag(nodes, frags)
+        m = np.zeros(frags, dtype=np.uint32)
+        assert lib.ssb_hashfrag_build(nodes, frags, m.ctypes.data_as(C.c_void_p)) == 0
+        assert np.array_equal(m, hf.map)
+        keys = np.random.default_rng(0).integers(0, 2 ** 32, 5000, dtype=np.uint64).astype(np.uint32)
+        out = np.zeros(len(keys), dtype=np.int32)
+        lib.ssb_hashfrag_route(keys.ctypes.data_as(C.c_void_p), C.c_int64(len(keys)), m.ctypes.data_as(C.c_void_p),
+                               frags, out.ctypes.data_as(C.c_void_p))
+        assert np.array_equal(out, hf.to_node_id(keys))
+    assert lib.ssb_hashfrag_build(8, 4, m.ctypes.data_as(C.c_void_p)) == -1
+    assert lib.ssb_buffer_selftest() == 0
+
+
+def test_text_dump_roundtrip(native_built, tmp_path):
+    from swiftsnails_b200.utils import dump
+
+    keys = np.array([5, 4220827, 4000000000], dtype=np.uint32)
+    rows = np.array([[0.5, -1.25, 3.0], [0.012402, 1e-5, 7], [1, 2, 3]], dtype=np.float32)
+    p = str(tmp_path / "param.txt")
+    assert dump.write_text(p, keys, rows) == 3
+    text = open(p).read().splitlines()
+    assert text[0] == "5\tVec:\t0.5 -1.25 3 "          # the reference's Vec print form
+    k2, r2 = dump.read_text(p, 3)
+    assert np.array_equal(k2, keys) and np.allclose(r2, rows, rtol=1e-5)
+    dump.write_text(p, keys[:1], rows[:1, :1].copy())
+    assert open(p).read() == "5\t0.5\n"                  # scalar param: `key \t value`
+
+
+@pytest.mark.parametrize("opt", ["sgd", "adagrad"])
+def test_cpu_table_matches_reference_math(native_built, opt):
+    from swiftsnails_b200.ops.cpu_table import CpuSparseTable
+    from swiftsnails_b200.utils.reference import init_rows
+
+    t = CpuSparseTable(16, shard_num=4, optimizer=opt, lr=0.1, eps=1e-8, seed=77, init_scale=0.5)
+    keys = np.arange(100, 400, dtype=np.uint32)
+    w = t.pull(keys)
+    assert np.array_equal(w, init_rows(keys, 16, 77, 0.5))   # same lazy init as the HBM table
+    acc = np.zeros_like(w)
+    rng = np.random.default_rng(1)
+    for _ in range(3):
+        g = rng.standard_normal(w.shape).astype(np.float32)
+        assert t.push(keys, g) == 0
+        if opt == "sgd":
+            w = w - 0.1 * g
+        else:
+            acc += g * g
+            w = w - 0.1 * g / np.sqrt(acc + 1e-8)
+    assert np.allclose(t.pull(keys), w, rtol=1e-5, atol=1e-6)
+    assert t.push(np.array([999999], dtype=np.uint32), np.zeros((1, 16), np.float32)) == 1  # never pulled
+    assert t.size() == 300
+
+
+def test_localhost_cluster_1_master_2_servers_2_workers(native_built):
+    """BASELINE config 1: synthetic sparse-key pull/push SGD over ZeroMQ, then check the final
+    parameter dump against the closed form (init - lr * sum of pushed grads)."""
+    from swiftsnails_b200.parallel.hashfrag import HashFrag
+    from swiftsnails_b200.parallel.launcher import launch_local_cluster, parse_dump, parse_result_line
+    from swiftsnails_b200.utils.reference import init_rows
+
+    dim, iters, lr = 8, 3, 0.05
+    r = launch_local_cluster("bench", 2, 2, overrides={"dim": dim, "bench_keys": 3000, "num_iters": iters,
+                                                        "learning_rate": lr, "bench_key_space": 20000,
+                                                        "frag_num": 100, "table_seed": 24301}, timeout=120)
+    assert r["master"][0] == 0, r["master"][2]
+    assert "Master terminated normally" in r["master"][2]
+    for w in r["workers"]:
+        assert w[0] == 0, w[2]
+        res = parse_result_line(w[1], "BENCH")
+        assert res and res["pull_keys_per_s"] > 0 and res["push_keys_per_s"] > 0
+    dumps = [parse_dump(s[1]) for s in r["servers"]]
+    assert all(s[0] == 0 for s in r["servers"])
+    assert len(set(dumps[0]) & set(dumps[1])) == 0            # every key lives on exactly one server
+    hf = HashFrag(2, 100)
+    for sid, d in enumerate(dumps):
+        ks = np.array(sorted(d), dtype=np.uint32)
+        assert len(ks) > 500
+        assert np.all(hf.to_node_id(ks) == sid + 1)           # same key -> server rule as the reference
+        init = init_rows(ks, dim, 24301, 1.0 / dim)
+        got = np.array([d[int(k)] for k in ks], dtype=np.float32)
+        delta = (init - got) / (lr * 0.001)                   # = number of pushes that hit the key
+        n_push = np.rint(delta[:, 0])
+        assert np.all((n_push == iters) | (n_push == 2 * iters))  # pushed by one or by both workers
+        assert np.allclose(delta, n_push[:, None], atol=0.02)
+
+
+def test_cluster_word2vec_and_local_train(native_built, tmp_path):
+    from swiftsnails_b200.parallel.launcher import launch_local_cluster, parse_result_line
+
+    data = str(tmp_path / "data.txt")
+    subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gen_word2vec_data.py"), "--lines", "1500", "--vocab",
+                    "301", "--out", data], check=True)
+    ov = {"dim": 16, "vocab": 301, "window": 3, "negative": 3, "minibatch_lines": 32, "learning_rate": 0.05,
+          "update": "adagrad", "num_iters": 2}
+    r = launch_local_cluster("word2vec", 2, 2, overrides=ov, data_files=[data], timeout=240)
+    assert r["master"][0] == 0, r["master"][2]
+    for w in r["workers"]:
+        assert w[0] == 0, w[2]
+        res = parse_result_line(w[1])
+        assert res["words"] > 10000 and res["words_per_s"] > 0 and 0 < res["mean_loss"] < 5.0
+    # single-process mode (local_train=1): no servers, same algorithm
+    conf = tmp_path / "local.conf"
+    conf.write_text("".join("%s: %s\n" % kv for kv in dict(ov, local_train=1, num_iters=1).items()))
+    p = subprocess.run([os.path.join(BIN, "swift_worker"), "-config", str(conf), "-data", data, "-app", "word2vec"],
+                       capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stderr
+    assert parse_result_line(p.stdout)["words"] > 10000
+
+
+def test_lr_app_local(native_built, tmp_path):
+    from swiftsnails_b200.parallel.launcher import parse_result_line
+
+    rng = np.random.default_rng(0)
+    w_true = rng.standard_normal(50)
+    lines = []
+    for _ in range(3000):
+        f = rng.choice(50, 5, replace=False)
+        y = 1 if w_true[f].sum() > 0 else 0
+        lines.append("%d %s" % (y, " ".join("%d:1" % k for k in f)))
+    data = tmp_path / "lr.txt"
+    data.write_text("\n".join(lines) + "\n")
+    conf = tmp_path / "lr.conf"
+    conf.write_text("local_train: 1\nnum_iters: 5\nlearning_rate: 0.05\nminibatch_lines: 32\n")
+    p = subprocess.run([os.path.join(BIN, "swift_worker"), "-config", str(conf), "-data", str(data), "-app", "lr"],
+                       capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stderr
+    assert parse_result_line(p.stdout)["mean_loss"] < 0.55   # below log(2): it learned
