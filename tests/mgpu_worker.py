@@ -1,0 +1,122 @@
+"""Multi-GPU checks, run under torchrun (one process per GPU) by tests/test_multigpu.py.
+Every rank hosts server shard `rank` and worker `rank`; shards are peer-mapped over NVLink."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    from swiftsnails_b200 import _lib
+    from swiftsnails_b200.models.word2vec import Word2VecConfig, Word2VecWorker, synthetic_corpus
+    from swiftsnails_b200.ops._util import to_u32_numpy, u32_tensor
+    from swiftsnails_b200.parallel.cluster import make_table
+    from swiftsnails_b200.utils.reference import init_rows
+
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    out = {"world": world}
+
+    # ---- 1. pull: every rank pulls an overlapping key set; all ranks must see identical rows/slots
+    dim = 64
+    table = make_table(50_000, dim, dev, with_state=True, init_scale=0.5, frag_num=64, seed=11)
+    rng = np.random.default_rng(5)
+    common = np.unique(rng.integers(0, 2 ** 31, 30_000, dtype=np.int64).astype(np.uint32))
+    own = np.unique(np.random.default_rng(100 + rank).integers(0, 2 ** 31, 10_000, dtype=np.int64).astype(np.uint32))
+    keys = np.concatenate([common, own])
+    rows, gslot = table.pull(u32_tensor(keys, dev))
+    torch.cuda.synchronize()
+    dist.barrier()
+    assert np.array_equal(rows.cpu().numpy(), init_rows(keys, dim, 11, 0.5)), "lazy-init rows differ"
+    g = to_u32_numpy(gslot)
+    assert np.array_equal(g // table.capacity, table.hashfrag.to_shard(keys)), "owner != hashfrag"
+    gs = [torch.empty_like(gslot[:len(common)]) for _ in range(world)]
+    dist.all_gather(gs, gslot[:len(common)].contiguous())
+    for o in gs:
+        assert torch.equal(o, gs[0]), "ranks resolved the same key to different slots"
+    live = torch.tensor([table.size()], device=dev)
+    dist.all_reduce(live)
+    all_own = [None] * world
+    dist.all_gather_object(all_own, own)
+    n_unique = len(np.unique(np.concatenate([common] + all_own)))
+    assert int(live.item()) == n_unique, (int(live.item()), n_unique)
+    out["pull_ok"] = True
+
+    # ---- 2. push: all ranks push to the common keys; SGD deltas must add up across ranks
+    dist.barrier()
+    before, cslot = table.pull(u32_tensor(common, dev))
+    torch.cuda.synchronize()
+    dist.barrier()
+    grads = torch.full((len(common), dim), float(rank + 1), device=dev)
+    table.push_sgd(cslot, grads, lr=0.5, zero_grads=False)
+    torch.cuda.synchronize()
+    dist.barrier()
+    after, _ = table.pull(u32_tensor(common, dev))
+    expect = before - 0.5 * sum(range(1, world + 1))
+    assert torch.allclose(after, expect, rtol=1e-6, atol=1e-6), "remote red deltas did not add up"
+    # AdaGrad over NVLink: one rank at a time so the oracle is deterministic
+    acc = torch.zeros_like(after)
+    w = after.clone()
+    for r in range(world):
+        gr = torch.full((len(common), dim), 0.25 * (r + 1), device=dev)
+        if r == rank:
+            table.push_adagrad(cslot, gr.clone(), lr=0.1, eps=1e-8, zero_grads=False)
+            torch.cuda.synchronize()
+        dist.barrier()
+        acc = acc + gr * gr
+        w = w - 0.1 * gr / torch.sqrt(acc + 1e-8)
+    final, _ = table.pull(u32_tensor(common, dev))
+    assert torch.allclose(final, w, rtol=1e-4, atol=1e-6), "AdaGrad over peer memory differs"
+    out["push_ok"] = True
+
+    # ---- 3. NVLink copy probe (kernel ld/st on a peer mapping), timed on the device
+    pm = table.peer_memory
+    nbytes = min(pm.stride, 256 << 20) // 16 * 16
+    peer = (rank + 1) % world
+    dst = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    for _ in range(2):
+        _lib.call("ssb_p2p_copy", pm.segment_ptr(peer), dst.data_ptr(), nbytes, 0, _lib.stream_ptr())
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        _lib.call("ssb_p2p_copy", pm.segment_ptr(peer), dst.data_ptr(), nbytes, 0, _lib.stream_ptr())
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / 5], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out["p2p_read_gbs"] = nbytes / (t.item() * 1e-3) / 1e9
+
+    # ---- 4. word2vec over the peer-mapped table: loss must fall on every rank
+    dist.barrier()
+    cfg = Word2VecConfig(vocab=3000, dim=128, window=3, negatives=5, neg_pool=16, sent_len=50, tokens_per_step=4096,
+                         lr=0.05, optimizer="adagrad", tile_impl="tcgen05", seed=1 + rank)
+    t2 = make_table(2 * cfg.vocab, cfg.dim, dev, with_state=True, init_scale=1.0 / cfg.dim, frag_num=64)
+    wk = Word2VecWorker(cfg, t2, dev)
+    base = synthetic_corpus(cfg.vocab, cfg.tokens_per_step * 25, seed=3 + rank)
+    base[1::2] = (base[0::2] * 7 + 1) % cfg.vocab
+    losses = []
+    for s in range(25):
+        wk.reset_loss()
+        wk.step(u32_tensor(base[s * cfg.tokens_per_step:(s + 1) * cfg.tokens_per_step], dev))
+        losses.append(wk.mean_loss())
+    assert all(np.isfinite(losses)) and np.mean(losses[-5:]) < 0.9 * np.mean(losses[:3]), losses
+    out["w2v_loss_first_last"] = [losses[0], losses[-1]]
+    torch.cuda.synchronize()
+    dist.barrier()
+    if rank == 0:
+        print("MGPU_RESULT " + json.dumps(out))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
