@@ -45,7 +45,7 @@ def parse_args():
     ap.add_argument("--lr", type=float, default=0.05)
     ap.add_argument("--zipf-s", type=float, default=1.0)
     ap.add_argument("--tc-mode", type=int, default=1, help="tcgen05 kernel mode bits (1 = TMA gather4; 2 = perf experiment: skip gradient reds)")
-    ap.add_argument("--ref-tokens", type=int, default=200_000, help="tokens per worker for the reference arm")
+    ap.add_argument("--ref-tokens", type=int, default=60_000, help="tokens per worker for the reference arm")
     return ap.parse_args()
 
 
