@@ -4,6 +4,7 @@
 // GPU form: an open-addressing hash *set* in scratch memory. Entries are 64-bit
 // (epoch << 32 | key); an entry whose epoch differs from the current call's epoch counts as
 // empty, so the scratch never needs clearing between calls.
+#include <cstdio>
 #include "common.cuh"
 
 namespace ssb {
@@ -78,6 +79,85 @@ extern "C" int ssb_dedup(const uint32_t* keys, int64_t n, uint64_t* set, uint32_
                                                   set_cap - 1, epoch, unique, inverse, n_unique);
   SSB_LAUNCH_CHECK();
   ssb::dedup_resolve_kernel<<<blocks, 256, 0, s>>>(set_ids, inverse, n);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+// -------------------------------------------------------------------------------------------
+// ssb_dedup_static — the same de-duplication for callers that must not allocate.
+//
+// ssb_dedup above needs a scratch hash set that somebody has to allocate on the device. Two kinds
+// of caller cannot do that: code embedded in a process whose device memory is entirely owned and
+// accounted for by its own arena or pool (a serving process, or a framework whose caching allocator
+// must not be bypassed, hands this library raw buffers and forbids any further cudaMalloc so its
+// memory budget stays exact), and code on a latency-critical path, where cudaMalloc/cudaFree would
+// stall the whole device. For them the scratch lives in the library image itself: a file-scope
+// __device__ array of fixed size. Every GPU that loads the library carries its own copy of that
+// array (1.5 MiB) from load until the process exits.
+//
+// Limits and rules:
+//   * at most SSB_DEDUP_STATIC_MAX_KEYS (65 536) keys per call; larger batches are refused with
+//     cudaErrorInvalidValue and a message on stderr — use ssb_dedup with your own scratch instead;
+//   * the array's name is only a host-side handle, not a device address, so the first call on each
+//     device (with that device current) asks the runtime for the real address with
+//     cudaGetSymbolAddress and remembers it; make that first call outside any stream capture;
+//   * nothing here calls cudaMalloc, cudaFree or any allocating library routine: the only runtime
+//     calls are the address query, two cudaMemsetAsync on the caller's stream and the launches;
+//   * all calls on a device share the one array and it keeps whatever the previous call left in
+//     it; each call therefore clears the hash-set part (and the output counter) on the caller's
+//     stream before inserting. Two calls that overlap on the GPU — different streams, or different
+//     host threads — race on the shared scratch: serialise them.
+#include <mutex>
+
+namespace ssb {
+constexpr uint32_t kStaticDedupMaxKeys = 65536;
+constexpr uint32_t kStaticDedupCap = 2 * kStaticDedupMaxKeys;  // hash-set slots (power of two)
+// [0, kStaticDedupCap) 64-bit set entries, then kStaticDedupCap 32-bit ids packed into 64-bit words
+static __device__ __align__(256) unsigned long long g_static_dedup_scratch[kStaticDedupCap + kStaticDedupCap / 2];
+
+static std::mutex g_static_dedup_mutex;
+static unsigned long long* g_static_dedup_ptr[64] = {nullptr};  // per device ordinal
+}  // namespace ssb
+
+extern "C" int ssb_dedup_static(const uint32_t* keys, int64_t n, uint32_t* unique, uint32_t* inverse,
+                                uint32_t* n_unique, void* stream) {
+  using namespace ssb;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n < 0 || n > (int64_t)kStaticDedupMaxKeys) {
+    fprintf(stderr, "ssb_dedup_static: n = %lld exceeds the built-in scratch (max %u keys per call); "
+                    "use ssb_dedup with caller-provided scratch\n", (long long)n, kStaticDedupMaxKeys);
+    return (int)cudaErrorInvalidValue;
+  }
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+  unsigned long long* scratch = nullptr;
+  {
+    // one-time set-up per device: turn the symbol into this device's address
+    std::lock_guard<std::mutex> lk(g_static_dedup_mutex);
+    if (g_static_dedup_ptr[dev] == nullptr) {
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_static_dedup_scratch);
+      if (e != cudaSuccess) return (int)e;
+      g_static_dedup_ptr[dev] = static_cast<unsigned long long*>(p);
+    }
+    scratch = g_static_dedup_ptr[dev];
+  }
+  unsigned long long* set = scratch;
+  uint32_t* set_ids = reinterpret_cast<uint32_t*>(scratch + kStaticDedupCap);
+  // the set must start empty (epoch 0 everywhere) and the counter at zero; set_ids needs no
+  // clearing: an id is only read for a slot whose set entry was written by this call
+  e = cudaMemsetAsync(set, 0, sizeof(unsigned long long) * kStaticDedupCap, s);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaMemsetAsync(n_unique, 0, sizeof(uint32_t), s);
+  if (e != cudaSuccess) return (int)e;
+  if (n == 0) return 0;
+  int blocks = grid_for(n, 256 * 2);
+  dedup_insert_kernel<<<blocks, 256, 0, s>>>(keys, n, set, set_ids, kStaticDedupCap - 1, /*epoch=*/1u, unique,
+                                             inverse, n_unique);
+  SSB_LAUNCH_CHECK();
+  dedup_resolve_kernel<<<blocks, 256, 0, s>>>(set_ids, inverse, n);
   SSB_LAUNCH_CHECK();
   return 0;
 }

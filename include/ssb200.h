@@ -60,6 +60,19 @@ int ssb_dedup(const uint32_t *keys, int64_t n, uint64_t *set, uint32_t *set_ids,
               uint32_t epoch, uint32_t *unique, uint32_t *inverse, uint32_t *n_unique, int reset,
               void *stream);
 
+/* Allocation-free variant of ssb_dedup (no counterpart in the reference, which has no device
+ * code): the scratch hash set is a fixed 1.5 MiB __device__ array inside the library, one copy per
+ * GPU that loads it, held until the process exits. For callers that may not allocate device
+ * memory — hosts that own all of it through their own arena/pool, and latency-critical paths
+ * where cudaMalloc would stall the device. At most SSB_DEDUP_STATIC_MAX_KEYS keys per call (more
+ * is refused with cudaErrorInvalidValue and a message on stderr). The first call on each device
+ * resolves the array's address (cudaGetSymbolAddress); make it outside any stream capture. Calls
+ * share the array and each one clears it on the caller's stream first; calls that overlap on
+ * the GPU race. Same outputs as ssb_dedup (the order of `unique` is unspecified in both). */
+#define SSB_DEDUP_STATIC_MAX_KEYS 65536
+int ssb_dedup_static(const uint32_t *keys, int64_t n, uint32_t *unique, uint32_t *inverse,
+                     uint32_t *n_unique, void *stream);
+
 /* ---- K3/K4/K10: table probe+insert, pull gather, cache merge -------------------------------
  * ref: sparsetable.h:142-149 (lazy init_param on miss), global_pull_access.h:40-120,
  * system/server/init.h:49-69.
