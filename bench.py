@@ -88,6 +88,10 @@ def run_ours(args):
     rows_per_shard = (2 * cfg.vocab + world - 1) // world
     table = make_table(rows_per_shard, cfg.dim, dev, with_state=(cfg.optimizer == "adagrad"),
                        init_scale=1.0 / cfg.dim, frag_num=max(1024, world))
+    if args.impl == "nccl":
+        from swiftsnails_b200.parallel.nccl_baseline import NcclShardedTable
+
+        table = NcclShardedTable(table)
     K, W, B = args.steps, args.warmup, cfg.tokens_per_step
     corpus = synthetic_corpus(cfg.vocab, (K + W) * B, s=cfg.zipf_s, seed=100 + rank)
     host = torch.from_numpy(corpus.view(np.int32)).reshape(K + W, B).pin_memory()
@@ -154,14 +158,15 @@ def run_ours(args):
         out = {
             "metric": METRIC, "value": value, "unit": "words/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "fp32 table, tf32 tensor-core tiles" if tile_impl == "tcgen05" else "fp32",
-            "data": "synthetic Zipf(s=1) corpus, random-init table", "impl": "ours",
+            "dtype": "bf16" if tile_impl == "tcgen05" else "fp32",
+            "data": "synthetic Zipf(s=1) corpus, random-init table", "impl": args.impl,
             "config": {"model": "word2vec skip-gram negative sampling", "vocab": cfg.vocab, "dim": cfg.dim,
                        "window": cfg.window, "negatives": cfg.negatives,
                        "neg_pool_per_128_pair_tile": cfg.neg_pool, "global_batch": B * world,
                        "tokens_per_step_per_gpu": B, "seq_len": cfg.sent_len, "optimizer": cfg.optimizer,
-                       "parallelism": "ps%d (1 server shard + 1 worker per GPU, P2P pull/push)" % world,
+                       "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if args.impl == "nccl" else "P2P"),
                        "tile_impl": tile_impl, "pairs_per_step_per_gpu": n_pairs / K,
+                       "precision": "bf16 tensor-core operands (tcgen05), fp32 accumulate, fp32 master table / AdaGrad state / gradients",
                        "l2": "no flush: table (%.2f GiB/shard) and caches exceed the 126 MB L2"
                              % (table.owned[0].nbytes() / 2 ** 30)},
             "clocks": clocks,

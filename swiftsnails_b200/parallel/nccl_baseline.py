@@ -1,0 +1,105 @@
+"""NCCL all-to-all pull / push — the GPU *baseline* the P2P kernels have to beat (BASELINE.json:
+"an NCCL all-to-all pull/push implementation as the GPU baseline. A path that only calls NCCL is
+the baseline, not the product").
+
+It is the straightforward translation of the reference's RPC
+(/root/reference/src/core/parameter/global_pull_access.h:40-120, global_push_access.h:36-149)
+onto collectives: bucket keys per owner → exchange counts (host sync for the split sizes) →
+``all_to_all_single`` of keys → owner-side lookup on its own shard → ``all_to_all_single`` of the
+rows back → un-permute.  Push mirrors it with (key, grad) going out and the owner applying the
+update.  Same table memory, same owner rule and same owner-side kernels as the P2P path (through a
+one-shard local view), so the two paths are interchangeable and comparable.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from ..ops import hashing
+from ..ops.table import ShardedTable
+from .hashfrag import HashFrag
+
+
+class NcclShardedTable:
+    """Wraps a (peer-mapped or local) ``ShardedTable`` but never touches a peer pointer."""
+
+    def __init__(self, table: ShardedTable):
+        self.table = table
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.dim, self.device, self.capacity = table.dim, table.device, table.capacity
+        self.hashfrag = table.hashfrag
+        self.has_state = table.has_state
+        self.owned = table.owned
+        shard = table.owned[0]
+        # one-shard view of my own shard: every key routes to shard 0 = my memory
+        self.local = ShardedTable(HashFrag(1, 1), table.capacity, table.dim, [shard.ptrs()], table.device,
+                                  seed=table.seed, init_scale=table.init_scale, owned=[shard])
+        self.stats = self.local.stats
+        self._plan = None
+
+    # ---- exchange plan for a key set ---------------------------------------------------------
+    def _route(self, keys):
+        bucketed, perm, counts, offsets = hashing.bucket_by_owner(keys, self.table.frag_map_dev, self.world)
+        send_counts = counts.to(torch.int64)
+        recv_counts = torch.empty_like(send_counts)
+        if self.world > 1:
+            dist.all_to_all_single(recv_counts, send_counts)
+        else:
+            recv_counts.copy_(send_counts)
+        sc = send_counts.tolist()      # host sync: NCCL needs the split sizes on the host
+        rc = recv_counts.tolist()
+        recv_keys = torch.empty(sum(rc), dtype=torch.int32, device=keys.device)
+        if self.world > 1:
+            dist.all_to_all_single(recv_keys, bucketed, rc, sc)
+        else:
+            recv_keys.copy_(bucketed)
+        return {"perm": perm.long(), "sc": sc, "rc": rc, "recv_keys": recv_keys}
+
+    def pull(self, keys, n_dev=None, rows_out=None, gslot_out=None, grads_zero=None, insert=True, n=None,
+             rows_bf16=None, want_fp32=True):
+        n = keys.numel() if n is None else n
+        if n_dev is not None:
+            n = min(n, int(n_dev.item()))
+        k = keys[:n]
+        plan = self._route(k)
+        rows_owner, _ = self.local.pull(plan["recv_keys"], insert=insert)
+        back = torch.empty((n, self.dim), dtype=torch.float32, device=keys.device)
+        if self.world > 1:
+            dist.all_to_all_single(back, rows_owner, plan["sc"], plan["rc"])
+        else:
+            back.copy_(rows_owner)
+        if rows_out is None and want_fp32:
+            rows_out = torch.empty((n, self.dim), dtype=torch.float32, device=keys.device)
+        if rows_out is not None:
+            rows_out[:n].index_copy_(0, plan["perm"], back)
+        if rows_bf16 is not None:
+            rows_bf16[:n].index_copy_(0, plan["perm"], back.to(torch.bfloat16))
+        if grads_zero is not None:
+            grads_zero[:n].zero_()
+        self._plan = (plan, n)
+        return rows_out, gslot_out
+
+    def _push(self, grads, n, apply):
+        plan, n_plan = self._plan
+        assert n_plan == n, "push must follow the pull of the same key set"
+        g = grads[:n].index_select(0, plan["perm"])
+        recv = torch.empty((sum(plan["rc"]), self.dim), dtype=torch.float32, device=grads.device)
+        if self.world > 1:
+            dist.all_to_all_single(recv, g, plan["rc"], plan["sc"])
+        else:
+            recv.copy_(g)
+        gslot = self.local.resolve(plan["recv_keys"], insert=True)
+        apply(gslot, recv)
+
+    def push_sgd(self, gslot, grads, lr, n_dev=None, zero_grads=True, n=None):
+        n = self._plan[1]
+        self._push(grads, n, lambda s, g: self.local.push_sgd(s, g, lr, zero_grads=False))
+        if zero_grads:
+            grads[:n].zero_()
+
+    def push_adagrad(self, gslot, grads, lr, eps=1e-8, n_dev=None, zero_grads=True, n=None):
+        n = self._plan[1]
+        self._push(grads, n, lambda s, g: self.local.push_adagrad(s, g, lr, eps, zero_grads=False))
+        if zero_grads:
+            grads[:n].zero_()

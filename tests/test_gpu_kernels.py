@@ -298,3 +298,39 @@ def test_word2vec_tcgen05_loss_decreases(device):
         losses.append(w.mean_loss())
     assert all(np.isfinite(losses))
     assert np.mean(losses[-5:]) < 0.9 * np.mean(losses[:3]), losses
+
+
+def test_lr_worker_learns(device):
+    from swiftsnails_b200.models.logistic_regression import LRConfig, LRWorker, criteo_like_batch
+    from swiftsnails_b200.ops._util import u32_tensor
+    from swiftsnails_b200.ops.table import ShardedTable
+
+    cfg = LRConfig(feature_bits=20, batch_size=4096, lr=0.1)
+    table = ShardedTable.local(1 << 19, 1, device, num_shards=2, frag_num=16, with_state=True, init_scale=0.0)
+    w = LRWorker(cfg, table, device)
+    losses = []
+    for s in range(40):
+        k, v, y = criteo_like_batch(cfg, cfg.batch_size, seed=s)
+        w.reset_loss()
+        w.step(u32_tensor(k, device), torch.from_numpy(v).to(device), torch.from_numpy(y).to(device))
+        losses.append(w.mean_loss())
+    assert abs(losses[0] - np.log(2)) < 1e-3          # zero-initialised weights
+    assert np.mean(losses[-5:]) < 0.97 * losses[0], losses
+
+
+def test_nccl_baseline_single_rank_matches_p2p(device):
+    from swiftsnails_b200.ops._util import u32_tensor
+    from swiftsnails_b200.ops.table import ShardedTable
+    from swiftsnails_b200.parallel.nccl_baseline import NcclShardedTable
+
+    t = ShardedTable.local(8192, 32, device, num_shards=1, with_state=True)
+    nt = NcclShardedTable(t)
+    keys = np.unique(_keys(3000, seed=21))
+    kd = u32_tensor(keys, device)
+    rows_p2p, gslot = t.pull(kd)
+    rows_nccl, _ = nt.pull(kd)
+    assert torch.equal(rows_p2p, rows_nccl)
+    g = torch.randn(len(keys), 32, device=device)
+    nt.push_sgd(None, g.clone(), lr=0.1)
+    rows2, _ = t.pull(kd)
+    assert torch.allclose(rows2, rows_p2p - 0.1 * g, rtol=1e-6, atol=1e-7)
