@@ -131,6 +131,7 @@ def run_ours(args):
     ms = max_over_ranks(e0.elapsed_time(e1))
     loss_dev = worker.mean_loss()
     n_pairs = float(worker.loss[1].item())
+    n_unique_last = int(worker.n_unique.item())
     sampler.stop()
     clocks = sampler.summary(t0, t1)
     del dev_tokens
@@ -165,7 +166,7 @@ def run_ours(args):
                        "neg_pool_per_128_pair_tile": cfg.neg_pool, "global_batch": B * world,
                        "tokens_per_step_per_gpu": B, "seq_len": cfg.sent_len, "optimizer": cfg.optimizer,
                        "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if args.impl == "nccl" else "P2P"),
-                       "tile_impl": tile_impl, "pairs_per_step_per_gpu": n_pairs / K,
+                       "tile_impl": tile_impl, "pairs_per_step_per_gpu": n_pairs / K, "unique_keys_last_step": n_unique_last,
                        "precision": "bf16 tensor-core operands (tcgen05), fp32 accumulate, fp32 master table / AdaGrad state / gradients",
                        "l2": "no flush: table (%.2f GiB/shard) and caches exceed the 126 MB L2"
                              % (table.owned[0].nbytes() / 2 ** 30)},

@@ -72,6 +72,76 @@ __device__ __forceinline__ uint32_t effective_n(int64_t n, const uint32_t* n_dev
 }
 
 // ---- pull ---------------------------------------------------------------------------------
+// A warp works on kPullK keys at a time so that kPullK bucket probes, then kPullK row reads, are
+// in flight together (one key at a time leaves HBM / NVLink latency exposed twice per key).
+// Fast path: the first bucket is probed with relaxed system-scope loads and, on a hit, the row
+// is read through an address that depends on the loaded key word; rows are only ever written
+// before their key is published (st.release.sys) and are read with strong .sys loads that bypass
+// L1, so the dependent read observes the initialised row. Anything else — miss in the first
+// bucket, LOCKED slot, insert — takes the acquire-based probe_insert() slow path.
+constexpr int kPullK = 4;
+
+__device__ __forceinline__ void pull_emit(const SsbTableView& v, uint32_t key, bool valid, const Probe& p, uint32_t w,
+                                          int lane, float* __restrict__ rows_out, __nv_bfloat16* __restrict__ rows_bf16,
+                                          float* __restrict__ grads_zero, uint32_t* __restrict__ gslot_out,
+                                          uint32_t* __restrict__ stats, bool have_pre, float4 preloaded) {
+  const int D = v.dim;
+  const bool have = p.slot != SSB_INVALID_SLOT;
+  float* row = have ? v.rows[p.owner] + (size_t)p.slot * D : nullptr;
+  float* out = rows_out ? rows_out + (size_t)w * D : nullptr;
+  __nv_bfloat16* outh = rows_bf16 ? rows_bf16 + (size_t)w * D : nullptr;
+  float* gz = grads_zero ? grads_zero + (size_t)w * D : nullptr;
+  const bool want = out || outh;
+  if ((D & 3) == 0) {
+    for (int j = lane * 4; j < D; j += 128) {
+      float4 val;
+      if (have && !p.is_new) {
+        val = (have_pre && j < 128) ? preloaded : (want ? ld_row_f4(row + j) : make_float4(0, 0, 0, 0));
+      } else if (valid) {
+        val.x = init_value(key, j, v.seed, v.init_scale);
+        val.y = init_value(key, j + 1, v.seed, v.init_scale);
+        val.z = init_value(key, j + 2, v.seed, v.init_scale);
+        val.w = init_value(key, j + 3, v.seed, v.init_scale);
+        if (p.is_new) *reinterpret_cast<float4*>(row + j) = val;
+      } else {
+        val = make_float4(0, 0, 0, 0);
+      }
+      if (out) *reinterpret_cast<float4*>(out + j) = val;
+      if (outh) {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(val.x, val.y), hi = __floats2bfloat162_rn(val.z, val.w);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t*>(&lo);
+        pk.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(outh + j) = pk;
+      }
+      if (gz) *reinterpret_cast<float4*>(gz + j) = make_float4(0, 0, 0, 0);
+    }
+  } else {
+    for (int j = lane; j < D; j += 32) {
+      float val;
+      if (have && !p.is_new) {
+        val = want ? ld_row_f1(row + j) : 0.f;
+      } else if (valid) {
+        val = init_value(key, j, v.seed, v.init_scale);
+        if (p.is_new) row[j] = val;
+      } else {
+        val = 0.f;
+      }
+      if (out) out[j] = val;
+      if (outh) outh[j] = __float2bfloat16_rn(val);
+      if (gz) gz[j] = 0.f;
+    }
+  }
+  if (p.is_new) publish(v, p, key, lane);
+  if (lane == 0) {
+    gslot_out[w] = have ? (uint32_t)p.owner * v.capacity + p.slot : SSB_INVALID_SLOT;
+    if (stats) {
+      if (p.is_new) atomicAdd(stats + 0, 1u);
+      if (valid && !have) atomicAdd(stats + 1, 1u);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256)
 pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ keys, int64_t n,
             const uint32_t* __restrict__ n_dev, uint32_t* __restrict__ gslot_out,
@@ -81,66 +151,48 @@ pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
   const uint32_t ne = effective_n(n, n_dev);
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
   const int D = v.dim;
-  const bool vec = (D & 3) == 0;
-  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
-    const uint32_t key = __ldg(keys + w);
-    Probe p;
-    p.owner = 0; p.slot = SSB_INVALID_SLOT; p.is_new = false;
-    const bool valid = key < SSB_LOCKED_KEY;
-    if (valid) p = probe_insert(v, key, insert != 0, lane);
-    const bool have = p.slot != SSB_INVALID_SLOT;
-    float* row = have ? v.rows[p.owner] + (size_t)p.slot * D : nullptr;
-    float* out = rows_out ? rows_out + (size_t)w * D : nullptr;
-    __nv_bfloat16* outh = rows_bf16 ? rows_bf16 + (size_t)w * D : nullptr;
-    float* gz = grads_zero ? grads_zero + (size_t)w * D : nullptr;
-    const bool want = out || outh;
-    if (vec) {
-      for (int j = lane * 4; j < D; j += 128) {
-        float4 val;
-        if (have && !p.is_new) {
-          val = want ? ld_row_f4(row + j) : make_float4(0, 0, 0, 0);
-        } else if (valid) {
-          val.x = init_value(key, j, v.seed, v.init_scale);
-          val.y = init_value(key, j + 1, v.seed, v.init_scale);
-          val.z = init_value(key, j + 2, v.seed, v.init_scale);
-          val.w = init_value(key, j + 3, v.seed, v.init_scale);
-          if (p.is_new) *reinterpret_cast<float4*>(row + j) = val;
-        } else {
-          val = make_float4(0, 0, 0, 0);
-        }
-        if (out) *reinterpret_cast<float4*>(out + j) = val;
-        if (outh) {
-          __nv_bfloat162 lo = __floats2bfloat162_rn(val.x, val.y), hi = __floats2bfloat162_rn(val.z, val.w);
-          uint2 pk;
-          pk.x = *reinterpret_cast<uint32_t*>(&lo);
-          pk.y = *reinterpret_cast<uint32_t*>(&hi);
-          *reinterpret_cast<uint2*>(outh + j) = pk;
-        }
-        if (gz) *reinterpret_cast<float4*>(gz + j) = make_float4(0, 0, 0, 0);
-      }
-    } else {
-      for (int j = lane; j < D; j += 32) {
-        float val;
-        if (have && !p.is_new) {
-          val = want ? ld_row_f1(row + j) : 0.f;
-        } else if (valid) {
-          val = init_value(key, j, v.seed, v.init_scale);
-          if (p.is_new) row[j] = val;
-        } else {
-          val = 0.f;
-        }
-        if (out) out[j] = val;
-        if (outh) outh[j] = __float2bfloat16_rn(val);
-        if (gz) gz[j] = 0.f;
+  const bool want = rows_out || rows_bf16;
+  const bool fast_rows = want && (D & 3) == 0;
+  const uint32_t nb = v.capacity / SSB_BUCKET;
+  for (uint32_t w0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * kPullK; w0 < ne; w0 += warps * kPullK) {
+    uint32_t key[kPullK], kv[kPullK], bucket[kPullK];
+    int owner[kPullK];
+    bool valid[kPullK];
+    // phase 1: kPullK independent first-bucket probes
+#pragma unroll
+    for (int k = 0; k < kPullK; ++k) {
+      const uint32_t w = w0 + k;
+      key[k] = (w < ne) ? __ldg(keys + w) : SSB_EMPTY_KEY;
+      valid[k] = key[k] < SSB_LOCKED_KEY;
+      owner[k] = valid[k] ? owner_of(key[k], v.frag_map, v.frag_num) : 0;
+      if (owner[k] < 0 || owner[k] >= v.num_shards) { owner[k] = 0; valid[k] = valid[k] && false; }
+      bucket[k] = reduce_range(slot_hash(key[k]), nb);
+      kv[k] = valid[k] ? ld_relaxed_sys(v.keys[owner[k]] + (size_t)bucket[k] * SSB_BUCKET + lane) : SSB_EMPTY_KEY;
+    }
+    // phase 2: resolve hits, issue their row reads together
+    Probe p[kPullK];
+    float4 pre[kPullK];
+#pragma unroll
+    for (int k = 0; k < kPullK; ++k) pre[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    bool fast[kPullK];
+#pragma unroll
+    for (int k = 0; k < kPullK; ++k) {
+      p[k].owner = owner[k]; p[k].slot = SSB_INVALID_SLOT; p[k].is_new = false;
+      unsigned m = __ballot_sync(0xffffffffu, valid[k] && kv[k] == key[k]);
+      fast[k] = m != 0;
+      if (fast[k]) {
+        p[k].slot = bucket[k] * SSB_BUCKET + (__ffs(m) - 1);
+        if (fast_rows && lane * 4 < D) pre[k] = ld_row_f4(v.rows[owner[k]] + (size_t)p[k].slot * D + lane * 4);
       }
     }
-    if (p.is_new) publish(v, p, key, lane);
-    if (lane == 0) {
-      gslot_out[w] = have ? (uint32_t)p.owner * v.capacity + p.slot : SSB_INVALID_SLOT;
-      if (stats) {
-        if (p.is_new) atomicAdd(stats + 0, 1u);
-        if (valid && !have) atomicAdd(stats + 1, 1u);
-      }
+    // phase 3: slow path for the rest (miss in first bucket, locked slot, insert), then emit
+#pragma unroll
+    for (int k = 0; k < kPullK; ++k) {
+      const uint32_t w = w0 + k;
+      if (w >= ne) break;
+      if (!fast[k] && valid[k]) p[k] = probe_insert(v, key[k], insert != 0, lane);
+      pull_emit(v, key[k], valid[k], p[k], w, lane, rows_out, rows_bf16, grads_zero, gslot_out, stats,
+                fast[k] && fast_rows, pre[k]);
     }
   }
 }
