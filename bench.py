@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--tile-impl", default="auto", choices=["auto", "cuda_core", "tcgen05"])
     ap.add_argument("--lr", type=float, default=0.05)
     ap.add_argument("--zipf-s", type=float, default=1.0)
+    ap.add_argument("--pipeline", type=int, default=1, help="overlap dedup+pull of step i+1 with SGNS+push of step i (2 streams)")
     ap.add_argument("--tc-mode", type=int, default=1, help="tcgen05 kernel mode bits (1 = TMA gather4; 2 = perf experiment: skip gradient reds)")
     ap.add_argument("--ref-tokens", type=int, default=60_000, help="tokens per worker for the reference arm")
     return ap.parse_args()
@@ -109,11 +110,12 @@ def run_ours(args):
         return float(t.item())
 
     # ---------------- device-timed arm: batches already on the device -------------------------
-    worker = Word2VecWorker(cfg, table, dev)
+    worker = Word2VecWorker(cfg, table, dev, pipeline=bool(args.pipeline) and args.impl == "ours")
     worker.tma_mode = args.tc_mode
     dev_tokens = host.to(dev)
     for s in range(W):
         worker.step(dev_tokens[s])
+    worker.flush()
     barrier()
     sampler = ClockSampler(gpu_index=local).start()
     time.sleep(0.3)
@@ -124,6 +126,7 @@ def run_ours(args):
     e0.record()
     for s in range(W, W + K):
         worker.step(dev_tokens[s])
+    worker.flush()
     e1.record()
     barrier()
     t1 = time.time()
@@ -137,7 +140,8 @@ def run_ours(args):
     del dev_tokens
 
     # ---------------- end-to-end arm: public API, H2D tokens + D2H loss every step -------------
-    trainer = Word2VecTrainer(cfg, table, dev)
+    trainer = Word2VecTrainer(cfg, table, dev, pipeline=bool(args.pipeline) and args.impl == "ours")
+    trainer.worker.tma_mode = args.tc_mode
     trainer.worker.step_idx = worker.step_idx
     for s in range(W):
         trainer.train_step(host[s])
@@ -148,6 +152,7 @@ def run_ours(args):
     for s in range(W, W + K):
         trainer.train_step(host[s])
     last_loss = trainer.finish()
+    trainer.worker.flush()
     f1.record()
     barrier()
     ms_e2e = max_over_ranks(f0.elapsed_time(f1))
@@ -166,6 +171,7 @@ def run_ours(args):
                        "neg_pool_per_128_pair_tile": cfg.neg_pool, "global_batch": B * world,
                        "tokens_per_step_per_gpu": B, "seq_len": cfg.sent_len, "optimizer": cfg.optimizer,
                        "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if args.impl == "nccl" else "P2P"),
+                       "pipeline": "2-stream, pull one step ahead (staleness <= 1 step)" if worker.pipeline else "off",
                        "tile_impl": tile_impl, "pairs_per_step_per_gpu": n_pairs / K, "unique_keys_last_step": n_unique_last,
                        "precision": "bf16 tensor-core operands (tcgen05), fp32 accumulate, fp32 master table / AdaGrad state / gradients",
                        "l2": "no flush: table (%.2f GiB/shard) and caches exceed the 126 MB L2"

@@ -64,6 +64,8 @@ struct Misc {
   uint8_t lead_on[2][kN];
   unsigned long long full_bar[2];
   unsigned long long empty_bar[2];
+  unsigned long long lead_bar[2];
+  uint32_t ctx_has_invalid[2];  // a context row inside the batch is INVALID (padding key): count m_i the slow way
   unsigned long long mma_bar;
   uint32_t tmem_base;
   float loss[kConsumerWarps];
@@ -130,6 +132,14 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float (&v)[4]) {
+  uint32_t r[4];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v[i] = __uint_as_float(r[i]);
+}
 __device__ __forceinline__ void tma_gather4(uint32_t dst_smem, const CUtensorMap* map, unsigned long long* bar,
                                             int col, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3) {
   asm volatile(
@@ -190,6 +200,8 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
     mbar_init(&misc->full_bar[1], 1);
     mbar_init(&misc->empty_bar[0], 1);
     mbar_init(&misc->empty_bar[1], 1);
+    mbar_init(&misc->lead_bar[0], 1);
+    mbar_init(&misc->lead_bar[1], 1);
     mbar_init(&misc->mma_bar, 1);
     fence_barrier_init();
   }
@@ -205,51 +217,50 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
 
   if (warp == kConsumerWarps) {
     // =========================== producer warp ===========================================
+    // Per tile: (wait for the stage) -> publish the row indices -> start the gather (TMA) ->
+    // prefetch the NEXT tile's indices into registers -> tile-local dedup -> signal lead_bar.
+    // The dedup and the index prefetch run while the TMA engine fills the stage.
+    uint32_t ri[4], ro[5];
+    auto load_idx = [&](int tile) {
+      const int t0 = tile * kM;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int g = t0 + lane + 32 * k;
+        ri[k] = (tile < n_tiles && g < n_tok) ? __ldg(inv_in + g) : SSB_INVALID_SLOT;
+      }
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const int r = lane + 32 * k;
+        uint32_t v = SSB_INVALID_SLOT;
+        if (tile < n_tiles) {
+          if (r < kCtx) {
+            const int g = t0 - kHalo + r;
+            if (g >= 0 && g < n_tok) v = __ldg(inv_out + g);
+          } else {
+            v = __ldg(neg_idx + (size_t)tile * kNeg + (r - kCtx));
+          }
+        }
+        ro[k] = v;
+      }
+    };
+    load_idx(blockIdx.x);
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
       const int b = it & 1;
       const int t0 = tile * kM;
       if (it >= 2) mbar_wait(&misc->empty_bar[b], ((it >> 1) - 1) & 1);   // stage freed by the MMAs of tile it-2
-      for (int r = lane; r < kM; r += 32) {
-        int g = t0 + r;
-        misc->in_row[b][r] = (g < n_tok) ? inv_in[g] : SSB_INVALID_SLOT;
+      bool bad = false;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) misc->in_row[b][lane + 32 * k] = ri[k];
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const int r = lane + 32 * k;
+        misc->on_row[b][r] = ro[k];
+        const int g = t0 - kHalo + r;
+        bad = bad || (r < kCtx && g >= 0 && g < n_tok && ro[k] == SSB_INVALID_SLOT);
       }
-      for (int r = lane; r < kN; r += 32) {
-        uint32_t v;
-        if (r < kCtx) {
-          int g = t0 - kHalo + r;
-          v = (g >= 0 && g < n_tok) ? inv_out[g] : SSB_INVALID_SLOT;
-        } else {
-          v = neg_idx[(size_t)tile * kNeg + (r - kCtx)];
-        }
-        misc->on_row[b][r] = v;
-      }
-      __syncwarp();
-      // tile-local dedup: lead[p] = first position with the same row id. Duplicate positions fold
-      // their dL/dS entries into the leader's row/column of G, so every distinct row gets ONE
-      // gradient reduction per tile (hot words would otherwise serialise on the same address).
-      {
-        uint32_t v[5];
-        int ld[5];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { v[k] = misc->in_row[b][lane + 32 * k]; ld[k] = lane + 32 * k; }
-        for (int j = 0; j < kM; ++j) {
-          const uint32_t x = misc->in_row[b][j];
-#pragma unroll
-          for (int k = 0; k < 4; ++k) if (v[k] == x) ld[k] = min(ld[k], j);
-        }
-#pragma unroll
-        for (int k = 0; k < 4; ++k) misc->lead_in[b][lane + 32 * k] = (uint8_t)ld[k];
-#pragma unroll
-        for (int k = 0; k < 5; ++k) { v[k] = misc->on_row[b][lane + 32 * k]; ld[k] = lane + 32 * k; }
-        for (int j = 0; j < kN; ++j) {
-          const uint32_t x = misc->on_row[b][j];
-#pragma unroll
-          for (int k = 0; k < 5; ++k) if (v[k] == x) ld[k] = min(ld[k], j);
-        }
-#pragma unroll
-        for (int k = 0; k < 5; ++k) misc->lead_on[b][lane + 32 * k] = (uint8_t)ld[k];
-      }
+      const unsigned any_bad = __ballot_sync(0xffffffffu, bad);
+      if (lane == 0) misc->ctx_has_invalid[b] = any_bad ? 1u : 0u;
       __syncwarp();
       const uint32_t in_base = kOffIn + b * kInBytes, on_base = kOffOn + b * kOnBytes;
       if (mode & 1) {
@@ -284,6 +295,33 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
         __syncwarp();
         if (lane == 0) mbar_arrive(&misc->full_bar[b]);
       }
+      // tile-local dedup: lead[p] = first position with the same row id. Duplicate positions fold
+      // their dL/dS entries into the leader's row/column of G, so every distinct row gets ONE
+      // gradient reduction per tile (hot words would otherwise serialise on the same address).
+      {
+        int ld[5];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) ld[k] = lane + 32 * k;
+        for (int j = 0; j < kM; ++j) {
+          const uint32_t x = misc->in_row[b][j];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) if (ri[k] == x) ld[k] = min(ld[k], j);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) misc->lead_in[b][lane + 32 * k] = (uint8_t)ld[k];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) ld[k] = lane + 32 * k;
+        for (int j = 0; j < kN; ++j) {
+          const uint32_t x = misc->on_row[b][j];
+#pragma unroll
+          for (int k = 0; k < 5; ++k) if (ro[k] == x) ld[k] = min(ld[k], j);
+        }
+#pragma unroll
+        for (int k = 0; k < 5; ++k) misc->lead_on[b][lane + 32 * k] = (uint8_t)ld[k];
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&misc->lead_bar[b]);
+      load_idx(tile + gridDim.x);   // next tile's indices, in flight while the consumers work
     }
   } else {
     // =========================== consumer warps ==========================================
@@ -318,6 +356,7 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
       // Gradient destination rows for epilogue 2, copied out of the stage's index arrays now (the
       // producer may refill them as soon as the gradient MMAs retire). Non-leaders are skipped:
       // their contribution has been folded into the leader's row / column of G.
+      mbar_wait(&misc->lead_bar[b], (it >> 1) & 1);
       if (tid < kM) {
         misc->out_rows[tid] = (misc->lead_in[b][tid] == tid) ? misc->in_row[b][tid] : SSB_INVALID_SLOT;
       } else if (tid < kM + kN) {
@@ -325,7 +364,8 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
         misc->out_rows[tid] = (misc->lead_on[b][c] == c) ? misc->on_row[b][c] : SSB_INVALID_SLOT;
       }
 
-      // ---- epilogue 1: logits -> loss and dL/dS (band + negatives) ---------------------------
+      // ---- epilogue 1: logits -> loss and dL/dS. Column part p owns band block p (16 of the 48
+      //      window columns; part 3 has none) and negatives [4p, 4p+4) -------------------------
       {
         const int gi = t0 + i;
         const uint32_t my_in = misc->in_row[b][i];
@@ -353,31 +393,52 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
           const uint32_t addr = sbase + kOffG + swz_off(li, lc & ~1u, kInBlk);
           asm volatile("red.shared::cta.add.noftz.bf16x2 [%0], %1;" ::"r"(addr), "r"(*reinterpret_cast<uint32_t*>(&pk)) : "memory");
         };
-        float v[16];
+        // one exp per logit: t = 1 + e^-x ; sigmoid = 1/t ; -log sigmoid(x) = log t ; softplus(x) = x + log t
+        auto sig_logt = [](float x, float& sig, float& logt) {
+          x = fminf(fmaxf(x, -30.f), 30.f);
+          const float t = 1.0f + exp2f(-1.4426950408889634f * x);
+          sig = __frcp_rn(t);
+          logt = 0.6931471805599453f * __log2f(t);
+        };
         if (part < 3) {
+          float v[16];
           const int c0 = q * 32 + part * 16;          // band window of this lane quarter: [32q, 32q+48)
           tmem_ld16(lane_base + kTmemS + c0, v);
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             if (col_ok(c0 + j)) {
-              g_add(c0 + j, fast_sigmoid(v[j]) - 1.0f);
-              loss_acc += neg_log_sigmoid(v[j]);
+              float sg, lt;
+              sig_logt(v[j], sg, lt);
+              g_add(c0 + j, sg - 1.0f);
+              loss_acc += lt;
               pair_acc += 1.f;
             }
           }
-        } else {
+        }
+        {
           // negatives: weight m_i * K / 16 each, m_i = number of valid contexts of centre i
           float m_i = 0.f;
+          if (row_ok) {
+            if (misc->ctx_has_invalid[b]) {
 #pragma unroll
-          for (int c = 0; c <= 2 * kHalo; ++c) m_i += col_ok(i + c) ? 1.f : 0.f;
-          tmem_ld16(lane_base + kTmemS + kCtx, v);
+              for (int c = 0; c <= 2 * kHalo; ++c) m_i += col_ok(i + c) ? 1.f : 0.f;
+            } else {
+              const int lo = max(gi - eff, tok_lo), hi = min(gi + eff, tok_hi - 1);
+              m_i = (float)max(hi - lo, 0);
+            }
+          }
+          float v4[4];
+          tmem_ld4(lane_base + kTmemS + kCtx + 4 * part, v4);
           const float w = m_i * neg_k * (1.0f / kNeg);
           if (m_i > 0.f) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              if (misc->on_row[b][kCtx + j] != SSB_INVALID_SLOT) {
-                g_add(kCtx + j, w * fast_sigmoid(v[j]));
-                loss_acc += w * neg_log_sigmoid(-v[j]);
+            for (int j = 0; j < 4; ++j) {
+              const int c = kCtx + 4 * part + j;
+              if (misc->on_row[b][c] != SSB_INVALID_SLOT) {
+                float sg, lt;
+                sig_logt(v4[j], sg, lt);
+                g_add(c, w * sg);
+                loss_acc += w * (v4[j] + lt);
               }
             }
           }

@@ -75,10 +75,39 @@ def unigram_weights_from_zipf(vocab: int, s: float = 1.0, power: float = 0.75, p
     return w
 
 
-class Word2VecWorker:
-    """The worker-side algorithm (``BaseAlgorithm`` analogue) for one GPU."""
+class _StepBuffers:
+    """One set of per-step device buffers (the worker cache for one minibatch)."""
 
-    def __init__(self, cfg: Word2VecConfig, table: ShardedTable, device, sampler: AliasSampler | None = None):
+    def __init__(self, n_keys, dim, max_pairs, device, tc):
+        i32 = dict(dtype=torch.int32, device=device)
+        self.keys_all = torch.empty(n_keys, **i32)
+        self.unique = torch.empty(n_keys, **i32)
+        self.inverse = torch.empty(n_keys, **i32)
+        self.n_unique = torch.zeros(1, **i32)
+        self.gslot = torch.empty(n_keys, **i32)
+        self.params = None if tc else torch.empty((n_keys, dim), dtype=torch.float32, device=device)
+        self.params_bf16 = torch.empty((n_keys, dim), dtype=torch.bfloat16, device=device) if tc else None
+        self.grads = torch.zeros((n_keys, dim), dtype=torch.float32, device=device)
+        self.pairs_in = torch.empty(max(max_pairs, 1), **i32)
+        self.pairs_out = torch.empty(max(max_pairs, 1), **i32)
+        self.n_pairs = torch.zeros(1, **i32)
+        self.dedup = Deduper(n_keys, device)
+        self.pulled = torch.cuda.Event()
+        self.freed = torch.cuda.Event()
+        self.step_idx = 0
+
+
+class Word2VecWorker:
+    """The worker-side algorithm (``BaseAlgorithm`` analogue) for one GPU.
+
+    ``pipeline=True`` runs the communication half of a step (key build, negative sampling, dedup,
+    pull — the part that crosses NVLink) on its own stream, one step ahead of the compute half
+    (SGNS tiles + push), with two buffer sets.  A pull may then read a row before the previous
+    step's push has landed: bounded staleness of one step, well inside what the reference's
+    fully asynchronous workers already allow (no cross-worker synchronisation)."""
+
+    def __init__(self, cfg: Word2VecConfig, table: ShardedTable, device, sampler: AliasSampler | None = None,
+                 pipeline: bool = False):
         assert table.dim == cfg.dim
         self.cfg, self.table, self.device = cfg, table, device
         B, w = cfg.tokens_per_step, cfg.window
@@ -97,63 +126,96 @@ class Word2VecWorker:
         if sampler is None:
             sampler = AliasSampler(unigram_weights_from_zipf(cfg.vocab, cfg.zipf_s), device, seed=cfg.seed + 77)
         self.sampler = sampler
-        i32 = dict(dtype=torch.int32, device=device)
-        self.keys_all = torch.empty(self.n_keys, **i32)
-        self.unique = torch.empty(self.n_keys, **i32)
-        self.inverse = torch.empty(self.n_keys, **i32)
-        self.n_unique = torch.zeros(1, **i32)
-        self.gslot = torch.empty(self.n_keys, **i32)
-        self.params = None if self.tc else torch.empty((self.n_keys, cfg.dim), dtype=torch.float32, device=device)
-        self.params_bf16 = torch.empty((self.n_keys, cfg.dim), dtype=torch.bfloat16, device=device) if self.tc else None
-        self.grads = torch.zeros((self.n_keys, cfg.dim), dtype=torch.float32, device=device)
-        self.pairs_in = torch.empty(max(self.max_pairs, 1), **i32)
-        self.pairs_out = torch.empty(max(self.max_pairs, 1), **i32)
-        self.tma_mode = 1
-        self.n_pairs = torch.zeros(1, **i32)
+        self.pipeline = bool(pipeline)
+        self.sets = [_StepBuffers(self.n_keys, cfg.dim, self.max_pairs, device, self.tc)
+                     for _ in range(2 if self.pipeline else 1)]
         self.loss = torch.zeros(2, dtype=torch.float32, device=device)
-        self.dedup = Deduper(self.n_keys, device)
         self.step_idx = 0
         self.neg_weight = float(cfg.negatives) / float(cfg.neg_pool)
+        self.tma_mode = 1
+        if self.pipeline:
+            lo, hi = torch.cuda.Stream.priority_range()
+            self.comm_stream = torch.cuda.Stream(device=device, priority=lo)
+            self.comp_stream = torch.cuda.Stream(device=device, priority=hi)
+        # aliases for the non-pipelined path / introspection
+        self.n_unique = self.sets[0].n_unique
+        self.grads = self.sets[0].grads
+        self.params = self.sets[0].params
+        self.params_bf16 = self.sets[0].params_bf16
 
-    def step(self, tokens: torch.Tensor):
-        """One minibatch: tokens int32 [tokens_per_step] on the device. Returns the loss tensor
-        [sum_loss, n_pairs] (device, accumulated since the last ``reset_loss``)."""
+    # ---- the two halves of a step ----------------------------------------------------------
+    def _comm(self, s, tokens):
         cfg, B = self.cfg, self.cfg.tokens_per_step
-        assert tokens.numel() == B
-        ka = self.keys_all
+        ka = s.keys_all
         ka[:B].copy_(tokens)                               # input keys  = w
         torch.add(tokens, cfg.vocab, out=ka[B:2 * B])      # output keys = w + vocab
         self.sampler.sample(self.n_negs, out=ka[2 * B:], key_offset=cfg.vocab)
         # K2: unique keys + inverse index (the cache has one entry per key)
-        self.dedup(ka, unique=self.unique, inverse=self.inverse, n_unique=self.n_unique)
+        s.dedup(ka, unique=s.unique, inverse=s.inverse, n_unique=s.n_unique)
         # K1+K3+K4: route, probe/insert, gather into the cache; grads zeroed in the same pass
-        self.table.pull(self.unique, n_dev=self.n_unique, rows_out=self.params, rows_bf16=self.params_bf16,
-                        want_fp32=not self.tc, gslot_out=self.gslot, grads_zero=self.grads, n=self.n_keys)
+        self.table.pull(s.unique, n_dev=s.n_unique, rows_out=s.params, rows_bf16=s.params_bf16,
+                        want_fp32=not self.tc, gslot_out=s.gslot, grads_zero=s.grads, n=self.n_keys)
+
+    def _compute(self, s):
+        cfg, B = self.cfg, self.cfg.tokens_per_step
         if self.tc:
             # K5 on tensor cores: TMA gather4 -> tcgen05.mma (bf16) -> TMEM epilogue -> red
-            sgns_ops.sgns_block_tc(self.params_bf16, self.grads, self.inverse[:B], self.inverse[B:2 * B],
-                                   cfg.sent_len, cfg.window, cfg.seed, self.step_idx * B, self.inverse[2 * B:],
+            sgns_ops.sgns_block_tc(s.params_bf16, s.grads, s.inverse[:B], s.inverse[B:2 * B],
+                                   cfg.sent_len, cfg.window, cfg.seed, s.step_idx * B, s.inverse[2 * B:],
                                    float(cfg.negatives), self.loss, mode=self.tma_mode)
         else:
             # pairs over cache row indices, then the CUDA-core tile kernel
-            sgns_ops.make_pairs(self.inverse[:B], self.inverse[B:2 * B], cfg.sent_len, cfg.window,
-                                cfg.seed, self.step_idx * B, self.pairs_in, self.pairs_out, self.n_pairs)
-            sgns_ops.sgns_tiles(self.params, self.grads, self.pairs_in, self.pairs_out, self.n_pairs,
-                                self.max_pairs, self.inverse[2 * B:], cfg.neg_pool, self.neg_weight, self.loss)
+            sgns_ops.make_pairs(s.inverse[:B], s.inverse[B:2 * B], cfg.sent_len, cfg.window,
+                                cfg.seed, s.step_idx * B, s.pairs_in, s.pairs_out, s.n_pairs)
+            sgns_ops.sgns_tiles(s.params, s.grads, s.pairs_in, s.pairs_out, s.n_pairs,
+                                self.max_pairs, s.inverse[2 * B:], cfg.neg_pool, self.neg_weight, self.loss)
         # K7/K8: scatter-add fused with the server update
         if cfg.optimizer == "adagrad":
-            self.table.push_adagrad(self.gslot, self.grads, cfg.lr, cfg.adagrad_eps, n_dev=self.n_unique,
+            self.table.push_adagrad(s.gslot, s.grads, cfg.lr, cfg.adagrad_eps, n_dev=s.n_unique,
                                     zero_grads=False, n=self.n_keys)
         else:
-            self.table.push_sgd(self.gslot, self.grads, cfg.lr, n_dev=self.n_unique, zero_grads=False,
-                                n=self.n_keys)
+            self.table.push_sgd(s.gslot, s.grads, cfg.lr, n_dev=s.n_unique, zero_grads=False, n=self.n_keys)
+
+    def step(self, tokens: torch.Tensor):
+        """One minibatch: tokens int32 [tokens_per_step] on the device. Returns the loss tensor
+        [sum_loss, n_pairs] (device, accumulated since the last ``reset_loss``)."""
+        assert tokens.numel() == self.cfg.tokens_per_step
+        s = self.sets[self.step_idx % len(self.sets)]
+        s.step_idx = self.step_idx
+        if not self.pipeline:
+            self._comm(s, tokens)
+            self._compute(s)
+        else:
+            cur = torch.cuda.current_stream()
+            self.comm_stream.wait_stream(cur)              # tokens were produced on the caller's stream
+            with torch.cuda.stream(self.comm_stream):
+                self.comm_stream.wait_event(s.freed)        # this buffer set's previous push has finished
+                self._comm(s, tokens)
+                s.pulled.record(self.comm_stream)
+            with torch.cuda.stream(self.comp_stream):
+                self.comp_stream.wait_event(s.pulled)
+                self._compute(s)
+                s.freed.record(self.comp_stream)
+            tokens.record_stream(self.comm_stream)
         self.step_idx += 1
         return self.loss
 
+    def flush(self):
+        """Make the caller's stream wait for everything enqueued so far (pipelined mode)."""
+        if self.pipeline:
+            cur = torch.cuda.current_stream()
+            cur.wait_stream(self.comm_stream)
+            cur.wait_stream(self.comp_stream)
+
     def reset_loss(self):
-        self.loss.zero_()
+        if self.pipeline:
+            with torch.cuda.stream(self.comp_stream):
+                self.loss.zero_()
+        else:
+            self.loss.zero_()
 
     def mean_loss(self):
+        self.flush()
         s, n = self.loss.tolist()
         return s / max(n, 1.0)
 
@@ -167,8 +229,8 @@ class Word2VecTrainer:
     stalls the GPU.  ``finish()`` returns the last loss.  Bytes per step: ``h2d_bytes`` /
     ``d2h_bytes``."""
 
-    def __init__(self, cfg: Word2VecConfig, table: ShardedTable, device):
-        self.worker = Word2VecWorker(cfg, table, device)
+    def __init__(self, cfg: Word2VecConfig, table: ShardedTable, device, pipeline: bool = False):
+        self.worker = Word2VecWorker(cfg, table, device, pipeline=pipeline)
         self.cfg, self.device = cfg, device
         self.tok_dev = [torch.empty(cfg.tokens_per_step, dtype=torch.int32, device=device) for _ in range(2)]
         self.loss_host = torch.zeros((2, 2), dtype=torch.float32).pin_memory()
@@ -180,10 +242,19 @@ class Word2VecTrainer:
     def train_step(self, tokens_host: torch.Tensor):
         i = self._i & 1
         self.tok_dev[i].copy_(tokens_host, non_blocking=True)
-        self.worker.reset_loss()
-        loss = self.worker.step(self.tok_dev[i])
-        self.loss_host[i].copy_(loss, non_blocking=True)
-        self.events[i].record()
+        w = self.worker
+        if w.pipeline:
+            # per-step loss: snapshot-and-clear on the compute stream right after the step's kernels
+            w.step(self.tok_dev[i])
+            with torch.cuda.stream(w.comp_stream):
+                self.loss_host[i].copy_(w.loss, non_blocking=True)
+                w.loss.zero_()
+                self.events[i].record(w.comp_stream)
+        else:
+            w.reset_loss()
+            loss = w.step(self.tok_dev[i])
+            self.loss_host[i].copy_(loss, non_blocking=True)
+            self.events[i].record()
         prev = None
         if self._i > 0:
             j = 1 - i

@@ -334,3 +334,29 @@ def test_nccl_baseline_single_rank_matches_p2p(device):
     nt.push_sgd(None, g.clone(), lr=0.1)
     rows2, _ = t.pull(kd)
     assert torch.allclose(rows2, rows_p2p - 0.1 * g, rtol=1e-6, atol=1e-7)
+
+
+def test_word2vec_pipelined_two_streams(device):
+    """dedup+pull one step ahead of SGNS+push on a second stream: still learns, nothing races on
+    the double-buffered caches, and flush() makes the caller's stream see the result."""
+    from swiftsnails_b200.models.word2vec import Word2VecConfig, Word2VecWorker, synthetic_corpus
+    from swiftsnails_b200.ops._util import u32_tensor
+    from swiftsnails_b200.ops.table import ShardedTable, round_capacity
+
+    cfg = Word2VecConfig(vocab=2000, dim=128, window=3, negatives=5, neg_pool=16, sent_len=50,
+                         tokens_per_step=4096, lr=0.05, optimizer="adagrad", tile_impl="tcgen05")
+    table = ShardedTable.local(round_capacity(2 * cfg.vocab), cfg.dim, device, num_shards=2, frag_num=16,
+                               with_state=True, init_scale=1.0 / cfg.dim)
+    w = Word2VecWorker(cfg, table, device, pipeline=True)
+    base = synthetic_corpus(cfg.vocab, cfg.tokens_per_step * 40, seed=3)
+    base[1::2] = (base[0::2] * 7 + 1) % cfg.vocab
+    toks = [u32_tensor(base[s * cfg.tokens_per_step:(s + 1) * cfg.tokens_per_step], device) for s in range(40)]
+    losses = []
+    for blk in range(8):
+        w.reset_loss()
+        for s in range(5):
+            w.step(toks[blk * 5 + s])
+        losses.append(w.mean_loss())
+    assert all(np.isfinite(losses))
+    assert losses[-1] < 0.9 * losses[0], losses
+    assert float(w.loss[1]) > 0
