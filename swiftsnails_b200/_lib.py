@@ -88,6 +88,14 @@ def kernels():
             return _kernels
         path = kernels_path()
         if not os.path.exists(path):
+            # in-tree build on first use (nvcc is part of the image); never a PyTorch fallback
+            try:
+                from . import build as _build
+
+                _build.build_kernels()
+            except Exception as e:  # noqa: BLE001
+                raise NativeError("native kernel library missing and the in-tree build failed: %s" % (e,))
+        if not os.path.exists(path):
             raise NativeError(
                 "native kernel library missing: %s — run `python -m swiftsnails_b200.build` "
                 "(there is no PyTorch fallback for the hot ops)" % path)
@@ -141,6 +149,13 @@ def core():
         if _core is not None:
             return _core
         path = core_path()
+        if not os.path.exists(path):
+            try:
+                from . import build as _build
+
+                _build.build_core()
+            except Exception as e:  # noqa: BLE001
+                raise NativeError("host core library missing and the in-tree build failed: %s" % (e,))
         if not os.path.exists(path):
             raise NativeError("host core library missing: %s — run `python -m swiftsnails_b200.build`" % path)
         _core = C.CDLL(path, mode=C.RTLD_GLOBAL)
