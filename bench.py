@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--tile-impl", default="auto", choices=["auto", "cuda_core", "tcgen05"])
     ap.add_argument("--lr", type=float, default=0.05)
     ap.add_argument("--zipf-s", type=float, default=1.0)
+    ap.add_argument("--inbox", type=int, default=1, help="multi-GPU AdaGrad push through owner inboxes (one-way) instead of remote atomics")
     ap.add_argument("--prepopulate", type=int, default=1, help="create all 2*vocab rows before timing (steady-state table)")
     ap.add_argument("--pipeline", type=int, default=1, help="overlap dedup+pull of step i+1 with SGNS+push of step i (2 streams)")
     ap.add_argument("--tc-mode", type=int, default=1, help="tcgen05 kernel mode bits (1 = TMA gather4; 2 = perf experiment: skip gradient reds)")
@@ -90,6 +91,11 @@ def run_ours(args):
     rows_per_shard = (2 * cfg.vocab + world - 1) // world
     table = make_table(rows_per_shard, cfg.dim, dev, with_state=(cfg.optimizer == "adagrad"),
                        init_scale=1.0 / cfg.dim, frag_num=max(1024, world))
+    if args.impl == "ours" and args.inbox and world > 1 and cfg.optimizer == "adagrad":
+        from swiftsnails_b200.parallel.cluster import attach_inbox
+
+        n_keys_max = 2 * cfg.tokens_per_step + ((cfg.tokens_per_step + 127) // 128) * cfg.neg_pool
+        attach_inbox(table, 2 * n_keys_max)
     if args.impl == "nccl":
         from swiftsnails_b200.parallel.nccl_baseline import NcclShardedTable
 

@@ -274,6 +274,81 @@ push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
   }
 }
 
+// ---- inbox push: one-way gradient shipment, owner applies the update --------------------------------
+// The AdaGrad update is not a pure reduction (it reads the accumulator), so pushing it with remote
+// `atom` moves every row three times across NVLink (operand out, old value back, `red` out). Here a
+// worker ships (slot, grad row) ONCE into the owner's inbox with plain peer stores; after a barrier
+// the owner applies its inbox with the ordinary push kernel on local memory (full HBM speed).
+// Rows the worker owns itself skip the inbox. Space in an owner's inbox is claimed with one remote
+// atomicAdd per (block, owner). ref: the reference's push is exactly "send (key, grad)* to the owner,
+// the owner applies" (global_push_access.h:123-149, server/init.h:116-132) — this is its NVLink form.
+constexpr int kSendRows = 64;   // rows per block
+
+template <bool kAdaGrad>
+__global__ void __launch_bounds__(256)
+push_send_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__ SsbInboxView ib,
+                 const uint32_t* __restrict__ gslot, const float* __restrict__ grads, int64_t n,
+                 const uint32_t* __restrict__ n_dev, int self_shard, float lr, float eps, uint32_t* __restrict__ overflow) {
+  __shared__ uint32_t cnt[SSB_MAX_SHARDS], base[SSB_MAX_SHARDS];
+  __shared__ uint32_t row_slot[kSendRows];
+  __shared__ uint16_t row_owner[kSendRows], row_rank[kSendRows];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t ne = effective_n(n, n_dev);
+  const int D = v.dim;
+  for (uint32_t r0 = blockIdx.x * kSendRows; r0 < ne; r0 += gridDim.x * kSendRows) {
+    if (threadIdx.x < SSB_MAX_SHARDS) cnt[threadIdx.x] = 0;
+    __syncthreads();
+    if (threadIdx.x < kSendRows) {
+      const uint32_t r = r0 + threadIdx.x;
+      uint32_t g = (r < ne) ? __ldg(gslot + r) : SSB_INVALID_SLOT;
+      uint16_t o = 0xFFFF, rk = 0;
+      uint32_t sl = 0;
+      if (g != SSB_INVALID_SLOT) {
+        o = (uint16_t)(g / v.capacity);
+        sl = g - (uint32_t)o * v.capacity;
+        if ((int)o != self_shard) rk = (uint16_t)atomicAdd(&cnt[o], 1u);
+      }
+      row_owner[threadIdx.x] = o; row_rank[threadIdx.x] = rk; row_slot[threadIdx.x] = sl;
+    }
+    __syncthreads();
+    if (threadIdx.x < v.num_shards && cnt[threadIdx.x])
+      base[threadIdx.x] = atomicAdd(ib.count[threadIdx.x], cnt[threadIdx.x]);   // remote claim, once per (block, owner)
+    __syncthreads();
+    for (int k = warp; k < kSendRows; k += 8) {
+      const uint32_t r = r0 + k;
+      const int o = row_owner[k];
+      if (o == 0xFFFF) continue;
+      const float* gr = grads + (size_t)r * D;
+      if (o == self_shard) {
+        // local row: apply directly
+        float* row = v.rows[o] + (size_t)row_slot[k] * D;
+        float* st = kAdaGrad ? v.state[o] + (size_t)row_slot[k] * D : nullptr;
+        for (int j = lane * 4; j < D; j += 128) {
+          float4 gv = *reinterpret_cast<const float4*>(gr + j);
+          if (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
+          float4 d;
+          if (kAdaGrad) {
+            float4 g2 = make_float4(gv.x * gv.x, gv.y * gv.y, gv.z * gv.z, gv.w * gv.w);
+            float4 a = atom_add_f4_sys(st + j, g2);
+            d.x = -lr * gv.x * rsqrtf(a.x + g2.x + eps); d.y = -lr * gv.y * rsqrtf(a.y + g2.y + eps);
+            d.z = -lr * gv.z * rsqrtf(a.z + g2.z + eps); d.w = -lr * gv.w * rsqrtf(a.w + g2.w + eps);
+          } else {
+            d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
+          }
+          red_add_f4_sys(row + j, d);
+        }
+      } else {
+        const uint32_t idx = base[o] + row_rank[k];
+        if (idx >= ib.capacity) { if (lane == 0) atomicAdd(overflow, 1u); continue; }
+        if (lane == 0) ib.slots[o][idx] = row_slot[k];
+        float* dst = ib.rows[o] + (size_t)idx * D;
+        for (int j = lane * 4; j < D; j += 128) *reinterpret_cast<float4*>(dst + j) = *reinterpret_cast<const float4*>(gr + j);
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // ---- bulk load (checkpoint resume; new capability, the reference never reads a dump back) ----
 __global__ void __launch_bounds__(256)
 table_load_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ keys,
@@ -387,6 +462,21 @@ int ssb_push_adagrad(const SsbTableView* view, const uint32_t* gslot, float* gra
   if (n <= 0) return 0;
   ssb::push_kernel<true><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, grads, n, n_dev, lr,
                                                                         eps, zero_grads);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_push_send(const SsbTableView* view, const SsbInboxView* inbox, const uint32_t* gslot, const float* grads,
+                  int64_t n, const uint32_t* n_dev, int32_t self_shard, float lr, float eps, int32_t adagrad,
+                  uint32_t* overflow, void* stream) {
+  if (int e = check_view(view)) return e;
+  if (!inbox || inbox->capacity == 0 || (view->dim & 3) != 0) return (int)cudaErrorInvalidValue;
+  if (n <= 0) return 0;
+  int blocks = ssb::grid_for(n, ssb::kSendRows, ssb::kNumSMs * 8);
+  if (adagrad)
+    ssb::push_send_kernel<true><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, overflow);
+  else
+    ssb::push_send_kernel<false><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, overflow);
   SSB_LAUNCH_CHECK();
   return 0;
 }

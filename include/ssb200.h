@@ -97,6 +97,22 @@ int ssb_push_sgd(const SsbTableView *view, const uint32_t *gslot, float *grads, 
 int ssb_push_adagrad(const SsbTableView *view, const uint32_t *gslot, float *grads, int64_t n,
                      const uint32_t *n_dev, float lr, float eps, int zero_grads, void *stream);
 
+/* Inbox push (multi-GPU AdaGrad): ship (slot, grad row) once into the owner's inbox with peer
+ * stores; rows owned by `self_shard` are applied directly. After a cross-GPU barrier the owner
+ * applies its inbox with ssb_push_adagrad / ssb_push_sgd on a one-shard local view
+ * (gslot = inbox slots, grads = inbox rows, n_dev = inbox count) and clears the count.
+ * ref: global_push_access.h:123-149 + server/init.h:116-132 (send (key, grad)*, the owner applies). */
+typedef struct SsbInboxView {
+  float *rows[SSB_MAX_SHARDS];     /* [capacity][dim] per owner (peer-mapped)        */
+  uint32_t *slots[SSB_MAX_SHARDS]; /* [capacity] slot within the owner shard        */
+  uint32_t *count[SSB_MAX_SHARDS]; /* entries claimed so far                        */
+  uint32_t capacity;
+  uint32_t pad_;
+} SsbInboxView;
+int ssb_push_send(const SsbTableView *view, const SsbInboxView *inbox, const uint32_t *gslot,
+                  const float *grads, int64_t n, const uint32_t *n_dev, int32_t self_shard, float lr,
+                  float eps, int32_t adagrad, uint32_t *overflow, void *stream);
+
 /* ---- K9: negative sampling (alias method, Philox4x32-10 counter RNG) ---------------------- */
 int ssb_neg_sample(const float *prob, const uint32_t *alias, uint32_t vocab, uint64_t seed,
                    uint64_t offset, uint32_t key_offset, uint32_t *out, int64_t n, void *stream);

@@ -43,6 +43,16 @@ class SsbTableView(C.Structure):
     ]
 
 
+class SsbInboxView(C.Structure):
+    _fields_ = [
+        ("rows", C.c_void_p * MAX_SHARDS),
+        ("slots", C.c_void_p * MAX_SHARDS),
+        ("count", C.c_void_p * MAX_SHARDS),
+        ("capacity", C.c_uint32),
+        ("pad_", C.c_uint32),
+    ]
+
+
 _vp, _i64, _i32, _u32, _u64, _f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32, C.c_uint64, C.c_float
 
 # name -> (argtypes, kernel launches per call)
@@ -55,6 +65,7 @@ _KERNEL_SIGS = {
     "ssb_gather_slots": ([C.POINTER(SsbTableView), _vp, _i64, _vp, _vp, _vp], 1),
     "ssb_push_sgd": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _i32, _vp], 1),
     "ssb_push_adagrad": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _f32, _i32, _vp], 1),
+    "ssb_push_send": ([C.POINTER(SsbTableView), C.POINTER(SsbInboxView), _vp, _vp, _i64, _vp, _i32, _f32, _f32, _i32, _vp, _vp], 1),
     "ssb_neg_sample": ([_vp, _vp, _u32, _u64, _u64, _u32, _vp, _i64, _vp], 1),
     "ssb_sgns_make_pairs": ([_vp, _vp, _i64, _i32, _i32, _u64, _u64, _vp, _vp, _vp, _vp], 1),
     "ssb_sgns_tiles": ([_vp, _vp, _i32, _vp, _vp, _vp, _i64, _vp, _i32, _f32, _vp, _vp], 1),

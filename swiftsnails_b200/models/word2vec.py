@@ -93,6 +93,7 @@ class _StepBuffers:
         self.n_pairs = torch.zeros(1, **i32)
         self.dedup = Deduper(n_keys, device)
         self.pulled = torch.cuda.Event()
+        self.computed = torch.cuda.Event()
         self.freed = torch.cuda.Event()
         self.step_idx = 0
 
@@ -137,6 +138,7 @@ class Word2VecWorker:
             lo, hi = torch.cuda.Stream.priority_range()
             self.comm_stream = torch.cuda.Stream(device=device, priority=lo)
             self.comp_stream = torch.cuda.Stream(device=device, priority=hi)
+            self.push_stream = torch.cuda.Stream(device=device, priority=lo)
         # aliases for the non-pipelined path / introspection
         self.n_unique = self.sets[0].n_unique
         self.grads = self.sets[0].grads
@@ -169,8 +171,15 @@ class Word2VecWorker:
                                 cfg.seed, s.step_idx * B, s.pairs_in, s.pairs_out, s.n_pairs)
             sgns_ops.sgns_tiles(s.params, s.grads, s.pairs_in, s.pairs_out, s.n_pairs,
                                 self.max_pairs, s.inverse[2 * B:], cfg.neg_pool, self.neg_weight, self.loss)
+
+    def _push(self, s):
+        cfg = self.cfg
         # K7/K8: scatter-add fused with the server update
-        if cfg.optimizer == "adagrad":
+        inbox = getattr(self.table, "inbox", None)
+        if inbox is not None and cfg.optimizer == "adagrad":
+            # multi-GPU AdaGrad: ship gradients once, the owner applies (one NVLink crossing per row)
+            inbox.push(s.gslot, s.grads, cfg.lr, cfg.adagrad_eps, adagrad=True, n_dev=s.n_unique, n=self.n_keys)
+        elif cfg.optimizer == "adagrad":
             self.table.push_adagrad(s.gslot, s.grads, cfg.lr, cfg.adagrad_eps, n_dev=s.n_unique,
                                     zero_grads=False, n=self.n_keys)
         else:
@@ -185,6 +194,7 @@ class Word2VecWorker:
         if not self.pipeline:
             self._comm(s, tokens)
             self._compute(s)
+            self._push(s)
         else:
             # keep the host at most two steps ahead of the device: deeper queues on the two
             # streams measurably reduce their overlap (the e2e arm, which is throttled by its loss
@@ -199,7 +209,11 @@ class Word2VecWorker:
             with torch.cuda.stream(self.comp_stream):
                 self.comp_stream.wait_event(s.pulled)
                 self._compute(s)
-                s.freed.record(self.comp_stream)
+                s.computed.record(self.comp_stream)
+            with torch.cuda.stream(self.push_stream):       # push(i) overlaps the SGNS tiles of step i+1
+                self.push_stream.wait_event(s.computed)
+                self._push(s)
+                s.freed.record(self.push_stream)
             tokens.record_stream(self.comm_stream)
         self.step_idx += 1
         return self.loss
@@ -210,6 +224,7 @@ class Word2VecWorker:
             cur = torch.cuda.current_stream()
             cur.wait_stream(self.comm_stream)
             cur.wait_stream(self.comp_stream)
+            cur.wait_stream(self.push_stream)
 
     def reset_loss(self):
         if self.pipeline:

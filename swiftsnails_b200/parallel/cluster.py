@@ -72,3 +72,79 @@ def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, f
     table.peer_memory = pm
     table.layout = lay
     return table
+
+
+class Inbox:
+    """Owner-side gradient inboxes for the one-way multi-GPU push (csrc/kernels/table.cu,
+    push_send_kernel): every rank owns two inboxes (step parity) in peer-mapped memory; a push
+    ships (slot, grad row) to the owners, a tiny all-reduce is the barrier, then each owner applies
+    its inbox to its own shard at local-HBM speed and clears it.  This is the reference's
+    "send (key, grad)* to the server, the server applies" (global_push_access.h:123-149,
+    system/server/init.h:116-132) carried by NVLink stores instead of ZeroMQ frames."""
+
+    def __init__(self, table: ShardedTable, capacity: int, device):
+        import ctypes as C
+
+        import torch.distributed as dist
+
+        self.table, self.device, self.capacity = table, device, int(capacity)
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        D = table.dim
+        rows_b = self.capacity * D * 4
+        slots_off = rows_b
+        count_off = slots_off + self.capacity * 4
+        per = (count_off + 256 + 4095) // 4096 * 4096
+        self.pm = PeerMemory(2 * per, device)
+        seg = self.pm.local_tensor()
+        seg.zero_()
+        self.views, self.rows_l, self.slots_l, self.count_l = [], [], [], []
+        for par in range(2):
+            v = _lib.SsbInboxView()
+            for r in range(self.world):
+                b = self.pm.segment_ptr(r) + par * per
+                v.rows[r], v.slots[r], v.count[r] = b, b + slots_off, b + count_off
+            v.capacity = self.capacity
+            self.views.append(v)
+            base = par * per
+            self.rows_l.append(seg[base:base + rows_b].view(torch.float32).view(self.capacity, D))
+            self.slots_l.append(seg[base + slots_off:base + slots_off + self.capacity * 4].view(torch.int32))
+            self.count_l.append(seg[base + count_off:base + count_off + 4].view(torch.int32))
+        shard = table.owned[0]
+        self.local = ShardedTable(HashFrag(1, 1), table.capacity, D, [shard.ptrs()], device, seed=table.seed,
+                                  init_scale=table.init_scale, owned=[shard])
+        self.overflow = torch.zeros(1, dtype=torch.int32, device=device)
+        self.token = torch.zeros(1, dtype=torch.int32, device=device)
+        self.parity = 0
+        self._C = C
+        torch.cuda.synchronize(device)
+        dist.barrier()
+
+    def push(self, gslot, grads, lr, eps=1e-8, adagrad=True, n_dev=None, n=None):
+        import torch.distributed as dist
+
+        C = self._C
+        n = gslot.numel() if n is None else n
+        par = self.parity
+        self.parity ^= 1
+        _lib.call("ssb_push_send", self.table._view_ref(), C.byref(self.views[par]), gslot.data_ptr(), grads.data_ptr(), n,
+                  _lib.ptr(n_dev), self.rank, float(lr), float(eps), 1 if adagrad else 0, self.overflow.data_ptr(),
+                  _lib.stream_ptr())
+        dist.all_reduce(self.token)          # barrier: every rank's shipment has landed in my inbox
+        if adagrad:
+            self.local.push_adagrad(self.slots_l[par], self.rows_l[par], lr, eps, n_dev=self.count_l[par],
+                                    zero_grads=False, n=self.capacity)
+        else:
+            self.local.push_sgd(self.slots_l[par], self.rows_l[par], lr, n_dev=self.count_l[par], zero_grads=False,
+                                n=self.capacity)
+        self.count_l[par].zero_()
+
+
+def attach_inbox(table: ShardedTable, capacity: int):
+    """Give a peer-mapped table owner-side inboxes (no-op for a single process)."""
+    import torch.distributed as dist
+
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        table.inbox = None
+        return None
+    table.inbox = Inbox(table, capacity, table.device)
+    return table.inbox
