@@ -183,7 +183,7 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __maxnreg__(64)
 sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict__ grads,
                      const uint32_t* __restrict__ inv_in, const uint32_t* __restrict__ inv_out,
                      int n_tok, int sent_len, int window, uint64_t seed, uint64_t offset,
@@ -379,12 +379,17 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
         }
         const int s_lo = (gi / sent_len) * sent_len;
         const int tok_lo = max(s_lo, 0), tok_hi = min(s_lo + sent_len, n_tok);
-        // column c <-> token t0 - 8 + c ; centre i <-> column i + 8
+        // column c <-> token t0 - 8 + c ; centre i <-> column i + 8. Valid context columns of row i
+        // form one range [c_lo, c_hi] minus the centre itself (plus, rarely, INVALID rows inside it).
+        const int self_c = i + kHalo;
+        int c_lo = 1, c_hi = 0;
+        if (row_ok) {
+          c_lo = max(gi - eff, tok_lo) - (t0 - kHalo);
+          c_hi = min(gi + eff, tok_hi - 1) - (t0 - kHalo);
+        }
+        const bool chk_rows = misc->ctx_has_invalid[b] != 0;
         auto col_ok = [&](int c) -> bool {
-          const int rel = c - (i + kHalo);
-          const int tok = t0 - kHalo + c;
-          return row_ok && rel != 0 && rel >= -eff && rel <= eff && tok >= tok_lo && tok < tok_hi &&
-                 misc->on_row[b][c] != SSB_INVALID_SLOT;
+          return c >= c_lo && c <= c_hi && c != self_c && (!chk_rows || misc->on_row[b][c] != SSB_INVALID_SLOT);
         };
         // G[lead(i)][lead(c)] += g   (bf16x2 shared-memory reduction; G was zeroed by the previous tile)
         auto g_add = [&](int c, float g) {
@@ -416,29 +421,31 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
           }
         }
         {
-          // negatives: weight m_i * K / 16 each, m_i = number of valid contexts of centre i
+          // negatives: weight m_i * K / 16 each, m_i = number of valid contexts of centre i. The 16
+          // negatives are split 4/2/4/6 over the column parts to even out the band work (the
+          // middle band block holds most of a row's valid contexts, part 3 has no band block).
           float m_i = 0.f;
           if (row_ok) {
-            if (misc->ctx_has_invalid[b]) {
+            if (chk_rows) {
 #pragma unroll
               for (int c = 0; c <= 2 * kHalo; ++c) m_i += col_ok(i + c) ? 1.f : 0.f;
             } else {
-              const int lo = max(gi - eff, tok_lo), hi = min(gi + eff, tok_hi - 1);
-              m_i = (float)max(hi - lo, 0);
+              m_i = (float)max(c_hi - c_lo, 0);
             }
           }
-          float v4[4];
-          tmem_ld4(lane_base + kTmemS + kCtx + 4 * part, v4);
+          const int n_lo = (part == 0) ? 0 : (part == 1) ? 4 : (part == 2) ? 6 : 10;
+          const int n_hi = (part == 0) ? 4 : (part == 1) ? 6 : (part == 2) ? 10 : 16;
+          float v[16];
+          tmem_ld16(lane_base + kTmemS + kCtx, v);
           const float w = m_i * neg_k * (1.0f / kNeg);
           if (m_i > 0.f) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const int c = kCtx + 4 * part + j;
-              if (misc->on_row[b][c] != SSB_INVALID_SLOT) {
+            for (int j = 0; j < 16; ++j) {
+              if (j >= n_lo && j < n_hi && misc->on_row[b][kCtx + j] != SSB_INVALID_SLOT) {
                 float sg, lt;
-                sig_logt(v4[j], sg, lt);
-                g_add(c, w * sg);
-                loss_acc += w * (v4[j] + lt);
+                sig_logt(v[j], sg, lt);
+                g_add(kCtx + j, w * sg);
+                loss_acc += w * (v[j] + lt);
               }
             }
           }
