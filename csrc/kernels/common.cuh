@@ -161,9 +161,15 @@ struct Philox {
   }
 };
 
+// Optional cap on resident blocks per SM for the (grid-stride) table / dedup / sampling kernels.
+// In the pipelined worker these kernels run next to the persistent tensor-core kernel of the
+// previous step; a grid that fills every SM would make that kernel's CTAs wait for them to drain.
+extern int g_blocks_per_sm_cap;   // 0 = no cap (defined in route.cu)
+
 inline int grid_for(int64_t work_items, int per_block, int max_blocks = kNumSMs * 16) {
   int64_t b = (work_items + per_block - 1) / per_block;
   if (b < 1) b = 1;
+  if (g_blocks_per_sm_cap > 0 && max_blocks > kNumSMs * g_blocks_per_sm_cap) max_blocks = kNumSMs * g_blocks_per_sm_cap;
   if (b > max_blocks) b = max_blocks;
   return (int)b;
 }

@@ -7,6 +7,8 @@
 
 namespace ssb {
 
+int g_blocks_per_sm_cap = 0;
+
 __global__ void fmix64_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, int64_t n) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     out[i] = fmix64(in[i]);
@@ -95,6 +97,9 @@ int ssb_fill_u32(uint32_t* p, uint32_t v, int64_t n, void* stream) {
   SSB_LAUNCH_CHECK();
   return 0;
 }
+
+// 0 removes the cap. Host-side setting, applies to launches issued afterwards.
+void ssb_set_blocks_per_sm_cap(int blocks_per_sm) { ssb::g_blocks_per_sm_cap = blocks_per_sm < 0 ? 0 : blocks_per_sm; }
 
 const char* ssb_error_string(int err) { return cudaGetErrorString((cudaError_t)err); }
 int ssb_version(void) { return 100; }

@@ -153,6 +153,9 @@ int ssb_p2p_copy(const void *src, void *dst, int64_t n_bytes, int32_t blocks, vo
 
 /* ---- misc ---------------------------------------------------------------------------------- */
 int ssb_fill_u32(uint32_t *p, uint32_t v, int64_t n, void *stream);
+/* Cap the grid of the grid-stride kernels (pull, push, dedup, sampling, route) at this many blocks
+ * per SM so they can share the SMs with the persistent tensor-core kernel (0 = no cap). */
+void ssb_set_blocks_per_sm_cap(int blocks_per_sm);
 const char *ssb_error_string(int err);
 int ssb_version(void);
 

@@ -139,6 +139,11 @@ class Word2VecWorker:
             self.comm_stream = torch.cuda.Stream(device=device, priority=lo)
             self.comp_stream = torch.cuda.Stream(device=device, priority=hi)
             self.push_stream = torch.cuda.Stream(device=device, priority=lo)
+            # optional cap on the grid of the grid-stride comm kernels (blocks per SM). Measured: no
+            # cap is best (0.362 ms/step vs 0.366 at 5, 0.380 at 3, 0.388 at 2 on one B200)
+            import os
+
+            _lib.kernels().ssb_set_blocks_per_sm_cap(int(os.environ.get("SSB200_BLOCKS_PER_SM_CAP", "0")))
         # aliases for the non-pipelined path / introspection
         self.n_unique = self.sets[0].n_unique
         self.grads = self.sets[0].grads
