@@ -191,7 +191,7 @@ def run_ours(args):
                        "tokens_per_step_per_gpu": B, "seq_len": cfg.sent_len, "optimizer": cfg.optimizer,
                        "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if args.impl == "nccl" else "P2P"),
                        "table": "all 2*vocab rows created before timing" if args.prepopulate else "empty at start, rows created lazily inside the timed region",
-                       "pipeline": "2-stream, pull one step ahead (staleness <= 1 step)" if worker.pipeline else "off",
+                       "pipeline": "3 streams: dedup+pull of step i+1 | SGNS of step i | push of step i-1 (staleness <= 1 step)" if worker.pipeline else "off",
                        "tile_impl": tile_impl, "pairs_per_step_per_gpu": n_pairs / K, "unique_keys_last_step": n_unique_last,
                        "precision": "bf16 tensor-core operands (tcgen05), fp32 accumulate, fp32 master table / AdaGrad state / gradients",
                        "l2": "no flush: table (%.2f GiB/shard) and caches exceed the 126 MB L2"
