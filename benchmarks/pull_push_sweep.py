@@ -89,8 +89,7 @@ def main():
                 w.pull(keys)
                 w.push(n_eff)
             ms_pull = timed(lambda: w.pull(keys), a.iters)
-            ms_push = timed(lambda: (w.pull(keys), w.push(n_eff)), a.iters) - ms_pull if impl == "nccl" else \
-                timed(lambda: w.push(n_eff), a.iters)
+            ms_push = timed(lambda: w.push(n_eff), a.iters)   # NCCL: re-uses the exchange plan of the last pull
             row_b = a.dim * 4
             remote = (world - 1) / world
             # bytes that must move per key: pull = key-bucket probe (128 B) + row read + row write;
