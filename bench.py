@@ -44,6 +44,9 @@ def parse_args():
     ap.add_argument("--tile-impl", default="auto", choices=["auto", "cuda_core", "tcgen05"])
     ap.add_argument("--lr", type=float, default=0.05)
     ap.add_argument("--zipf-s", type=float, default=1.0)
+    ap.add_argument("--shadow", type=int, default=1, help="bf16 mirror of the table rows, read by the pull (half the row bytes)")
+    ap.add_argument("--inbox-bf16", type=int, default=1, help="ship inbox gradient rows as bf16")
+    ap.add_argument("--inbox-barrier", default="flags", choices=["flags", "nccl"])
     ap.add_argument("--inbox", type=int, default=1, help="multi-GPU AdaGrad push through owner inboxes (one-way) instead of remote atomics")
     ap.add_argument("--prepopulate", type=int, default=1, help="create all 2*vocab rows before timing (steady-state table)")
     ap.add_argument("--pipeline", type=int, default=1, help="overlap dedup+pull of step i+1 with SGNS+push of step i (2 streams)")
@@ -89,13 +92,17 @@ def run_ours(args):
                          optimizer=args.optimizer, seed=1 + rank, tile_impl=tile_impl, zipf_s=args.zipf_s)
     # 2*vocab keys (input + output vectors) spread over `world` shards at load factor 0.5
     rows_per_shard = (2 * cfg.vocab + world - 1) // world
+    use_inbox = args.impl == "ours" and args.inbox and world > 1 and cfg.optimizer == "adagrad"
+    # bf16 mirror of the rows for the (bf16-only) pull; kept in step by owner-side writers, so it is
+    # enabled when every push is applied by the owner (single GPU, or the inbox push)
+    with_shadow = bool(args.shadow) and args.impl == "ours" and tile_impl == "tcgen05" and (world == 1 or use_inbox)
     table = make_table(rows_per_shard, cfg.dim, dev, with_state=(cfg.optimizer == "adagrad"),
-                       init_scale=1.0 / cfg.dim, frag_num=max(1024, world))
-    if args.impl == "ours" and args.inbox and world > 1 and cfg.optimizer == "adagrad":
+                       init_scale=1.0 / cfg.dim, frag_num=max(1024, world), with_shadow=with_shadow)
+    if use_inbox:
         from swiftsnails_b200.parallel.cluster import attach_inbox
 
         n_keys_max = 2 * cfg.tokens_per_step + ((cfg.tokens_per_step + 127) // 128) * cfg.neg_pool
-        attach_inbox(table, 2 * n_keys_max)
+        attach_inbox(table, 2 * n_keys_max, bf16_rows=bool(args.inbox_bf16), barrier=args.inbox_barrier)
     if args.impl == "nccl":
         from swiftsnails_b200.parallel.nccl_baseline import NcclShardedTable
 
@@ -190,6 +197,7 @@ def run_ours(args):
                        "neg_pool_per_128_pair_tile": cfg.neg_pool, "global_batch": B * world,
                        "tokens_per_step_per_gpu": B, "seq_len": cfg.sent_len, "optimizer": cfg.optimizer,
                        "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if args.impl == "nccl" else "P2P"),
+                       "bf16_row_mirror": with_shadow, "inbox_push": bool(use_inbox), "inbox_rows_bf16": bool(use_inbox and args.inbox_bf16),
                        "table": "all 2*vocab rows created before timing" if args.prepopulate else "empty at start, rows created lazily inside the timed region",
                        "pipeline": "3 streams: dedup+pull of step i+1 | SGNS of step i | push of step i-1 (staleness <= 1 step)" if worker.pipeline else "off",
                        "tile_impl": tile_impl, "pairs_per_step_per_gpu": n_pairs / K, "unique_keys_last_step": n_unique_last,

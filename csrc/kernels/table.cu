@@ -65,6 +65,28 @@ __device__ __forceinline__ void publish(const SsbTableView& v, const Probe& p, u
   if (lane == 0) st_release_sys(v.keys[p.owner] + p.slot, key);
 }
 
+__device__ __forceinline__ uint2 pack_bf16x4(float4 v) {
+  __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+  uint2 pk;
+  pk.x = *reinterpret_cast<uint32_t*>(&lo);
+  pk.y = *reinterpret_cast<uint32_t*>(&hi);
+  return pk;
+}
+__device__ __forceinline__ uint2 ld_shadow_u2(const void* p) {
+  uint2 r;
+  asm volatile("ld.relaxed.sys.global.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p) : "memory");
+  return r;
+}
+// w += d on an owner-side row, keeping the bf16 mirror in step when there is one
+__device__ __forceinline__ void row_update_f4(float* row, __nv_bfloat16* shadow, float4 d) {
+  if (shadow) {
+    float4 o = atom_add_f4_sys(row, d);
+    *reinterpret_cast<uint2*>(shadow) = pack_bf16x4(make_float4(o.x + d.x, o.y + d.y, o.z + d.z, o.w + d.w));
+  } else {
+    red_add_f4_sys(row, d);
+  }
+}
+
 __device__ __forceinline__ uint32_t effective_n(int64_t n, const uint32_t* n_dev) {
   uint32_t ne = (uint32_t)n;
   if (n_dev) { uint32_t d = *n_dev; if (d < ne) ne = d; }
@@ -88,6 +110,19 @@ __device__ __forceinline__ void pull_emit(const SsbTableView& v, uint32_t key, b
   const int D = v.dim;
   const bool have = p.slot != SSB_INVALID_SLOT;
   float* row = have ? v.rows[p.owner] + (size_t)p.slot * D : nullptr;
+  __nv_bfloat16* shadow = (have && v.shadow[p.owner]) ? reinterpret_cast<__nv_bfloat16*>(v.shadow[p.owner]) + (size_t)p.slot * D : nullptr;
+  // bf16-only pull of an existing row: read the 2-byte mirror instead of the fp32 row
+  if (have && !p.is_new && shadow && !rows_out && rows_bf16 && (D & 3) == 0) {
+    __nv_bfloat16* oh = rows_bf16 + (size_t)w * D;
+    float* gz0 = grads_zero ? grads_zero + (size_t)w * D : nullptr;
+    for (int j = lane * 4; j < D; j += 128) {
+      uint2 pk = (have_pre && j < 128) ? make_uint2(__float_as_uint(preloaded.x), __float_as_uint(preloaded.y)) : ld_shadow_u2(shadow + j);
+      *reinterpret_cast<uint2*>(oh + j) = pk;
+      if (gz0) *reinterpret_cast<float4*>(gz0 + j) = make_float4(0, 0, 0, 0);
+    }
+    if (lane == 0) gslot_out[w] = (uint32_t)p.owner * v.capacity + p.slot;
+    return;
+  }
   float* out = rows_out ? rows_out + (size_t)w * D : nullptr;
   __nv_bfloat16* outh = rows_bf16 ? rows_bf16 + (size_t)w * D : nullptr;
   float* gz = grads_zero ? grads_zero + (size_t)w * D : nullptr;
@@ -102,18 +137,15 @@ __device__ __forceinline__ void pull_emit(const SsbTableView& v, uint32_t key, b
         val.y = init_value(key, j + 1, v.seed, v.init_scale);
         val.z = init_value(key, j + 2, v.seed, v.init_scale);
         val.w = init_value(key, j + 3, v.seed, v.init_scale);
-        if (p.is_new) *reinterpret_cast<float4*>(row + j) = val;
+        if (p.is_new) {
+          *reinterpret_cast<float4*>(row + j) = val;
+          if (shadow) *reinterpret_cast<uint2*>(shadow + j) = pack_bf16x4(val);
+        }
       } else {
         val = make_float4(0, 0, 0, 0);
       }
       if (out) *reinterpret_cast<float4*>(out + j) = val;
-      if (outh) {
-        __nv_bfloat162 lo = __floats2bfloat162_rn(val.x, val.y), hi = __floats2bfloat162_rn(val.z, val.w);
-        uint2 pk;
-        pk.x = *reinterpret_cast<uint32_t*>(&lo);
-        pk.y = *reinterpret_cast<uint32_t*>(&hi);
-        *reinterpret_cast<uint2*>(outh + j) = pk;
-      }
+      if (outh) *reinterpret_cast<uint2*>(outh + j) = pack_bf16x4(val);
       if (gz) *reinterpret_cast<float4*>(gz + j) = make_float4(0, 0, 0, 0);
     }
   } else {
@@ -153,6 +185,7 @@ pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
   const int D = v.dim;
   const bool want = rows_out || rows_bf16;
   const bool fast_rows = want && (D & 3) == 0;
+  const bool from_shadow = !rows_out && rows_bf16 && v.shadow[0] != nullptr && (D & 3) == 0;
   const uint32_t nb = v.capacity / SSB_BUCKET;
   for (uint32_t w0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * kPullK; w0 < ne; w0 += warps * kPullK) {
     uint32_t key[kPullK], kv[kPullK], bucket[kPullK];
@@ -182,7 +215,14 @@ pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
       fast[k] = m != 0;
       if (fast[k]) {
         p[k].slot = bucket[k] * SSB_BUCKET + (__ffs(m) - 1);
-        if (fast_rows && lane * 4 < D) pre[k] = ld_row_f4(v.rows[owner[k]] + (size_t)p[k].slot * D + lane * 4);
+        if (from_shadow) {
+          if (lane * 4 < D) {
+            uint2 pk = ld_shadow_u2(reinterpret_cast<const __nv_bfloat16*>(v.shadow[owner[k]]) + (size_t)p[k].slot * D + lane * 4);
+            pre[k].x = __uint_as_float(pk.x); pre[k].y = __uint_as_float(pk.y);
+          }
+        } else if (fast_rows && lane * 4 < D) {
+          pre[k] = ld_row_f4(v.rows[owner[k]] + (size_t)p[k].slot * D + lane * 4);
+        }
       }
     }
     // phase 3: slow path for the rest (miss in first bucket, locked slot, insert), then emit
@@ -236,6 +276,7 @@ push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
     uint32_t o = g / v.capacity, s = g - o * v.capacity;
     float* row = v.rows[o] + (size_t)s * D;
     float* st = kAdaGrad ? v.state[o] + (size_t)s * D : nullptr;
+    __nv_bfloat16* sh = v.shadow[o] ? reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)s * D : nullptr;
     float* gr = grads + (size_t)w * D;
     if ((D & 3) == 0) {
       for (int j = lane * 4; j < D; j += 128) {
@@ -252,7 +293,7 @@ push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
         } else {
           d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
         }
-        red_add_f4_sys(row + j, d);
+        row_update_f4(row + j, sh ? sh + j : nullptr, d);
         if (zero_grads) *reinterpret_cast<float4*>(gr + j) = make_float4(0, 0, 0, 0);
       }
     } else {
@@ -267,11 +308,70 @@ push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
         } else {
           d = -lr * gv;
         }
-        red_add_f1_sys(row + j, d);
+        if (sh) { float o1 = atom_add_f1_sys(row + j, d); sh[j] = __float2bfloat16_rn(o1 + d); }
+        else red_add_f1_sys(row + j, d);
         if (zero_grads) gr[j] = 0.f;
       }
     }
   }
+}
+
+// Owner-side apply of an inbox whose gradient rows travelled as bf16 (half the NVLink bytes); the
+// update itself is fp32 on fp32 rows / accumulators. D must be a multiple of 4.
+template <bool kAdaGrad>
+__global__ void __launch_bounds__(256)
+push_bf16_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot,
+                 const __nv_bfloat16* __restrict__ grads, int64_t n, const uint32_t* __restrict__ n_dev, float lr, float eps) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t ne = effective_n(n, n_dev);
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const int D = v.dim;
+  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
+    uint32_t g = __ldg(gslot + w);
+    if (g == SSB_INVALID_SLOT) continue;
+    uint32_t o = g / v.capacity, s = g - o * v.capacity;
+    float* row = v.rows[o] + (size_t)s * D;
+    float* st = kAdaGrad ? v.state[o] + (size_t)s * D : nullptr;
+    const __nv_bfloat16* gr = grads + (size_t)w * D;
+    __nv_bfloat16* sh = v.shadow[o] ? reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)s * D : nullptr;
+    for (int j = lane * 4; j < D; j += 128) {
+      const uint2 pk = *reinterpret_cast<const uint2*>(gr + j);
+      const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162*>(&pk.x), hi = *reinterpret_cast<const __nv_bfloat162*>(&pk.y);
+      const float2 a01 = __bfloat1622float2(lo), a23 = __bfloat1622float2(hi);
+      const float4 gv = make_float4(a01.x, a01.y, a23.x, a23.y);
+      if (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
+      float4 d;
+      if (kAdaGrad) {
+        float4 g2 = make_float4(gv.x * gv.x, gv.y * gv.y, gv.z * gv.z, gv.w * gv.w);
+        float4 a = atom_add_f4_sys(st + j, g2);
+        d.x = -lr * gv.x * rsqrtf(a.x + g2.x + eps); d.y = -lr * gv.y * rsqrtf(a.y + g2.y + eps);
+        d.z = -lr * gv.z * rsqrtf(a.z + g2.z + eps); d.w = -lr * gv.w * rsqrtf(a.w + g2.w + eps);
+      } else {
+        d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
+      }
+      row_update_f4(row + j, sh ? sh + j : nullptr, d);
+    }
+  }
+}
+
+// Cross-GPU hand-off flags for the inbox push (replaces a collective as the barrier): after its
+// shipment kernel a rank stores the step number into flags[owner][rank] on every owner; an owner
+// waits until all of its flags reached the step before applying its inbox. The waiter only spins
+// on ITS OWN memory, every rank runs on its own GPU, and the spin is bounded (trap, not hang).
+__global__ void flags_signal_kernel(const __grid_constant__ SsbInboxView ib, int num_shards, int self, uint32_t value) {
+  __threadfence_system();
+  if ((int)threadIdx.x < num_shards) st_release_sys(ib.flags[threadIdx.x] + self, value);
+}
+__global__ void flags_wait_kernel(const uint32_t* __restrict__ my_flags, int num_shards, uint32_t value) {
+  if ((int)threadIdx.x < num_shards) {
+    uint32_t it = 0;
+    while ((int32_t)(ld_acquire_sys(my_flags + threadIdx.x) - value) < 0) {
+      __nanosleep(200);
+      if (++it > (1u << 24)) __trap();
+    }
+  }
+  __syncthreads();
+  __threadfence_system();
 }
 
 // ---- inbox push: one-way gradient shipment, owner applies the update --------------------------------
@@ -284,7 +384,7 @@ push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
 // the owner applies" (global_push_access.h:123-149, server/init.h:116-132) — this is its NVLink form.
 constexpr int kSendRows = 64;   // rows per block
 
-template <bool kAdaGrad>
+template <bool kAdaGrad, bool kBf16>
 __global__ void __launch_bounds__(256)
 push_send_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__ SsbInboxView ib,
                  const uint32_t* __restrict__ gslot, const float* __restrict__ grads, int64_t n,
@@ -323,6 +423,7 @@ push_send_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__
         // local row: apply directly
         float* row = v.rows[o] + (size_t)row_slot[k] * D;
         float* st = kAdaGrad ? v.state[o] + (size_t)row_slot[k] * D : nullptr;
+        __nv_bfloat16* sh = v.shadow[o] ? reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)row_slot[k] * D : nullptr;
         for (int j = lane * 4; j < D; j += 128) {
           float4 gv = *reinterpret_cast<const float4*>(gr + j);
           if (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
@@ -335,14 +436,25 @@ push_send_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__
           } else {
             d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
           }
-          red_add_f4_sys(row + j, d);
+          row_update_f4(row + j, sh ? sh + j : nullptr, d);
         }
       } else {
         const uint32_t idx = base[o] + row_rank[k];
         if (idx >= ib.capacity) { if (lane == 0) atomicAdd(overflow, 1u); continue; }
         if (lane == 0) ib.slots[o][idx] = row_slot[k];
-        float* dst = ib.rows[o] + (size_t)idx * D;
-        for (int j = lane * 4; j < D; j += 128) *reinterpret_cast<float4*>(dst + j) = *reinterpret_cast<const float4*>(gr + j);
+        if (kBf16) {
+          __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(ib.rows[o]) + (size_t)idx * D;
+          for (int j = lane * 4; j < D; j += 128) {
+            const float4 gv = *reinterpret_cast<const float4*>(gr + j);
+            __nv_bfloat162 lo = __floats2bfloat162_rn(gv.x, gv.y), hi = __floats2bfloat162_rn(gv.z, gv.w);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t*>(&lo); pk.y = *reinterpret_cast<uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(dst + j) = pk;
+          }
+        } else {
+          float* dst = ib.rows[o] + (size_t)idx * D;
+          for (int j = lane * 4; j < D; j += 128) *reinterpret_cast<float4*>(dst + j) = *reinterpret_cast<const float4*>(gr + j);
+        }
       }
     }
     __syncthreads();
@@ -364,6 +476,10 @@ table_load_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __rest
     if (p.slot == SSB_INVALID_SLOT) { if (lane == 0 && stats) atomicAdd(stats + 1, 1u); continue; }
     float* row = v.rows[p.owner] + (size_t)p.slot * D;
     for (int j = lane; j < D; j += 32) row[j] = rows[(size_t)w * D + j];
+    if (v.shadow[p.owner]) {
+      __nv_bfloat16* sh = reinterpret_cast<__nv_bfloat16*>(v.shadow[p.owner]) + (size_t)p.slot * D;
+      for (int j = lane; j < D; j += 32) sh[j] = __float2bfloat16_rn(rows[(size_t)w * D + j]);
+    }
     if (state && v.state[p.owner]) {
       float* st = v.state[p.owner] + (size_t)p.slot * D;
       for (int j = lane; j < D; j += 32) st[j] = state[(size_t)w * D + j];
@@ -468,15 +584,42 @@ int ssb_push_adagrad(const SsbTableView* view, const uint32_t* gslot, float* gra
 
 int ssb_push_send(const SsbTableView* view, const SsbInboxView* inbox, const uint32_t* gslot, const float* grads,
                   int64_t n, const uint32_t* n_dev, int32_t self_shard, float lr, float eps, int32_t adagrad,
-                  uint32_t* overflow, void* stream) {
+                  int32_t bf16_rows, uint32_t* overflow, void* stream) {
   if (int e = check_view(view)) return e;
   if (!inbox || inbox->capacity == 0 || (view->dim & 3) != 0) return (int)cudaErrorInvalidValue;
   if (n <= 0) return 0;
   int blocks = ssb::grid_for(n, ssb::kSendRows, ssb::kNumSMs * 8);
+#define SSB_SEND(A, B) ssb::push_send_kernel<A, B><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, overflow)
+  if (adagrad) { if (bf16_rows) SSB_SEND(true, true); else SSB_SEND(true, false); }
+  else { if (bf16_rows) SSB_SEND(false, true); else SSB_SEND(false, false); }
+#undef SSB_SEND
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_push_bf16(const SsbTableView* view, const uint32_t* gslot, const void* grads_bf16, int64_t n, const uint32_t* n_dev,
+                  float lr, float eps, int32_t adagrad, void* stream) {
+  if (int e = check_view(view)) return e;
+  if ((view->dim & 3) != 0) return (int)cudaErrorInvalidValue;
+  if (n <= 0) return 0;
   if (adagrad)
-    ssb::push_send_kernel<true><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, overflow);
+    ssb::push_bf16_kernel<true><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, (const __nv_bfloat16*)grads_bf16, n, n_dev, lr, eps);
   else
-    ssb::push_send_kernel<false><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, overflow);
+    ssb::push_bf16_kernel<false><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, (const __nv_bfloat16*)grads_bf16, n, n_dev, lr, eps);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_flags_signal(const SsbInboxView* inbox, int32_t num_shards, int32_t self, uint32_t value, void* stream) {
+  if (!inbox || num_shards < 1 || num_shards > SSB_MAX_SHARDS) return (int)cudaErrorInvalidValue;
+  ssb::flags_signal_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*inbox, num_shards, self, value);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_flags_wait(const uint32_t* my_flags, int32_t num_shards, uint32_t value, void* stream) {
+  if (num_shards < 1 || num_shards > SSB_MAX_SHARDS) return (int)cudaErrorInvalidValue;
+  ssb::flags_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(my_flags, num_shards, value);
   SSB_LAUNCH_CHECK();
   return 0;
 }

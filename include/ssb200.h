@@ -27,6 +27,10 @@ typedef struct SsbTableView {
   uint32_t *keys[SSB_MAX_SHARDS];  /* [capacity] per shard, SSB_EMPTY_KEY when free          */
   float *rows[SSB_MAX_SHARDS];     /* [capacity][dim] parameter rows                          */
   float *state[SSB_MAX_SHARDS];    /* [capacity][dim] AdaGrad accumulators, or NULL           */
+  void *shadow[SSB_MAX_SHARDS];    /* [capacity][dim] bf16 mirror of rows, or NULL. Kept in step by
+                                      every owner-side writer (insert, load, local/inbox push); a
+                                      pull that only wants bf16 reads it: half the row bytes over
+                                      HBM / NVLink. Not maintained by REMOTE direct pushes.       */
   const uint32_t *frag_map;        /* [frag_num] fragment -> node id (1..num_shards), device  */
   uint32_t frag_num;
   uint32_t capacity;               /* slots per shard, multiple of SSB_BUCKET                 */
@@ -106,12 +110,20 @@ typedef struct SsbInboxView {
   float *rows[SSB_MAX_SHARDS];     /* [capacity][dim] per owner (peer-mapped)        */
   uint32_t *slots[SSB_MAX_SHARDS]; /* [capacity] slot within the owner shard        */
   uint32_t *count[SSB_MAX_SHARDS]; /* entries claimed so far                        */
+  uint32_t *flags[SSB_MAX_SHARDS]; /* [num_shards] per owner: last step each sender finished */
   uint32_t capacity;
   uint32_t pad_;
 } SsbInboxView;
 int ssb_push_send(const SsbTableView *view, const SsbInboxView *inbox, const uint32_t *gslot,
                   const float *grads, int64_t n, const uint32_t *n_dev, int32_t self_shard, float lr,
-                  float eps, int32_t adagrad, uint32_t *overflow, void *stream);
+                  float eps, int32_t adagrad, int32_t bf16_rows, uint32_t *overflow, void *stream);
+/* Owner-side apply when the inbox rows are bf16 (bf16_rows=1 above): fp32 update from bf16 gradients. */
+int ssb_push_bf16(const SsbTableView *view, const uint32_t *gslot, const void *grads_bf16, int64_t n,
+                  const uint32_t *n_dev, float lr, float eps, int32_t adagrad, void *stream);
+/* Hand-off flags instead of a collective: signal = store `value` into flags[owner][self] on every
+ * owner (after a system fence); wait = spin (bounded) until all of my flags reached `value`. */
+int ssb_flags_signal(const SsbInboxView *inbox, int32_t num_shards, int32_t self, uint32_t value, void *stream);
+int ssb_flags_wait(const uint32_t *my_flags, int32_t num_shards, uint32_t value, void *stream);
 
 /* ---- K9: negative sampling (alias method, Philox4x32-10 counter RNG) ---------------------- */
 int ssb_neg_sample(const float *prob, const uint32_t *alias, uint32_t vocab, uint64_t seed,

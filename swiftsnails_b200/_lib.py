@@ -32,6 +32,7 @@ class SsbTableView(C.Structure):
         ("keys", C.c_void_p * MAX_SHARDS),
         ("rows", C.c_void_p * MAX_SHARDS),
         ("state", C.c_void_p * MAX_SHARDS),
+        ("shadow", C.c_void_p * MAX_SHARDS),
         ("frag_map", C.c_void_p),
         ("frag_num", C.c_uint32),
         ("capacity", C.c_uint32),
@@ -48,6 +49,7 @@ class SsbInboxView(C.Structure):
         ("rows", C.c_void_p * MAX_SHARDS),
         ("slots", C.c_void_p * MAX_SHARDS),
         ("count", C.c_void_p * MAX_SHARDS),
+        ("flags", C.c_void_p * MAX_SHARDS),
         ("capacity", C.c_uint32),
         ("pad_", C.c_uint32),
     ]
@@ -65,7 +67,10 @@ _KERNEL_SIGS = {
     "ssb_gather_slots": ([C.POINTER(SsbTableView), _vp, _i64, _vp, _vp, _vp], 1),
     "ssb_push_sgd": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _i32, _vp], 1),
     "ssb_push_adagrad": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _f32, _i32, _vp], 1),
-    "ssb_push_send": ([C.POINTER(SsbTableView), C.POINTER(SsbInboxView), _vp, _vp, _i64, _vp, _i32, _f32, _f32, _i32, _vp, _vp], 1),
+    "ssb_push_send": ([C.POINTER(SsbTableView), C.POINTER(SsbInboxView), _vp, _vp, _i64, _vp, _i32, _f32, _f32, _i32, _i32, _vp, _vp], 1),
+    "ssb_push_bf16": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _f32, _i32, _vp], 1),
+    "ssb_flags_signal": ([C.POINTER(SsbInboxView), _i32, _i32, _u32, _vp], 1),
+    "ssb_flags_wait": ([_vp, _i32, _u32, _vp], 1),
     "ssb_neg_sample": ([_vp, _vp, _u32, _u64, _u64, _u32, _vp, _i64, _vp], 1),
     "ssb_sgns_make_pairs": ([_vp, _vp, _i64, _i32, _i32, _u64, _u64, _vp, _vp, _vp, _vp], 1),
     "ssb_sgns_tiles": ([_vp, _vp, _i32, _vp, _vp, _vp, _i64, _vp, _i32, _f32, _vp, _vp], 1),

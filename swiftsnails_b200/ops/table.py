@@ -30,7 +30,7 @@ def round_capacity(rows_expected: int, load_factor: float = 0.5) -> int:
 class DeviceShard:
     """Storage of one shard on one device."""
 
-    def __init__(self, capacity: int, dim: int, device, with_state: bool, alloc=None):
+    def __init__(self, capacity: int, dim: int, device, with_state: bool, alloc=None, with_shadow: bool = False):
         assert capacity % _lib.BUCKET == 0
         self.capacity, self.dim, self.device = int(capacity), int(dim), device
         if alloc is None:
@@ -43,12 +43,16 @@ class DeviceShard:
         if with_state:
             self.state = alloc((capacity, dim), torch.float32)
             self.state.zero_()
+        # optional bf16 mirror of the rows (read by bf16-only pulls: half the row bytes)
+        self.shadow = alloc((capacity, dim), torch.bfloat16) if with_shadow else None
 
     def ptrs(self):
-        return (self.keys.data_ptr(), self.rows.data_ptr(), 0 if self.state is None else self.state.data_ptr())
+        return (self.keys.data_ptr(), self.rows.data_ptr(), 0 if self.state is None else self.state.data_ptr(),
+                0 if self.shadow is None else self.shadow.data_ptr())
 
     def nbytes(self):
         n = self.keys.numel() * 4 + self.rows.numel() * 4
+        n += self.shadow.numel() * 2 if self.shadow is not None else 0
         return n + (self.state.numel() * 4 if self.state is not None else 0)
 
 
@@ -72,8 +76,10 @@ class ShardedTable:
         self.init_scale = float(init_scale if init_scale is not None else 1.0 / dim)
         self.seed = int(seed)
         v = _lib.SsbTableView()
-        for i, (k, r, s) in enumerate(shard_ptrs):
-            v.keys[i], v.rows[i], v.state[i] = k, r, (s or None)
+        for i, ptrs in enumerate(shard_ptrs):
+            k, r, s = ptrs[0], ptrs[1], ptrs[2]
+            sh = ptrs[3] if len(ptrs) > 3 else 0
+            v.keys[i], v.rows[i], v.state[i], v.shadow[i] = k, r, (s or None), (sh or None)
         v.frag_map = self.frag_map_dev.data_ptr()
         v.frag_num = hashfrag.frag_num
         v.capacity = self.capacity
@@ -82,14 +88,15 @@ class ShardedTable:
         v.seed = self.seed
         v.init_scale = self.init_scale
         self.view = v
-        self.has_state = all(s for (_, _, s) in shard_ptrs)
+        self.has_state = all(p[2] for p in shard_ptrs)
+        self.has_shadow = all(len(p) > 3 and p[3] for p in shard_ptrs)
         self.stats = torch.zeros(4, dtype=torch.int32, device=device)  # [inserts, misses/full, -, -]
 
     # -- construction --------------------------------------------------------------------------
     @classmethod
-    def local(cls, capacity, dim, device, num_shards=1, frag_num=None, with_state=False, **kw):
+    def local(cls, capacity, dim, device, num_shards=1, frag_num=None, with_state=False, with_shadow=False, **kw):
         hf = HashFrag(num_shards, frag_num or max(num_shards, 1024 if num_shards > 1 else 1))
-        shards = [DeviceShard(capacity, dim, device, with_state) for _ in range(num_shards)]
+        shards = [DeviceShard(capacity, dim, device, with_state, with_shadow=with_shadow) for _ in range(num_shards)]
         return cls(hf, capacity, dim, [s.ptrs() for s in shards], device, owned=shards, **kw)
 
     def _view_ref(self):

@@ -17,7 +17,7 @@ from .hashfrag import HashFrag
 from .peer import PeerMemory, tensor_from_ptr
 
 
-def shard_layout(capacity, dim, with_state):
+def shard_layout(capacity, dim, with_state, with_shadow=False):
     """Byte offsets of keys / rows / state inside a shard segment.  rows_off and the total are
     multiples of the row pitch so the mapped range is one 2-D [rows, dim] tensor for TMA."""
     pitch = dim * 4
@@ -26,13 +26,14 @@ def shard_layout(capacity, dim, with_state):
     rows_off = (keys_bytes + unit - 1) // unit * unit
     rows_bytes = capacity * pitch
     state_off = rows_off + rows_bytes
-    total = state_off + (rows_bytes if with_state else 0)
+    shadow_off = state_off + (rows_bytes if with_state else 0)
+    total = shadow_off + (rows_bytes // 2 if with_shadow else 0)
     return {"keys_off": 0, "rows_off": rows_off, "state_off": state_off if with_state else None,
-            "total": total, "pitch": pitch}
+            "shadow_off": shadow_off if with_shadow else None, "total": total, "pitch": pitch}
 
 
 def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, frag_num=1024, seed=0x5EED,
-               load_factor=0.5, force_peer=False):
+               load_factor=0.5, force_peer=False, with_shadow=False):
     import torch.distributed as dist
 
     world = dist.get_world_size() if dist.is_initialized() else 1
@@ -40,10 +41,10 @@ def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, f
     capacity = round_capacity(rows_per_shard, load_factor)
     hf = HashFrag(world, max(frag_num, world))
     if world == 1 and not force_peer:
-        shard = DeviceShard(capacity, dim, device, with_state)
+        shard = DeviceShard(capacity, dim, device, with_state, with_shadow=with_shadow)
         return ShardedTable(hf, capacity, dim, [shard.ptrs()], device, seed=seed, init_scale=init_scale,
                             owned=[shard], rank=0)
-    lay = shard_layout(capacity, dim, with_state)
+    lay = shard_layout(capacity, dim, with_state, with_shadow)
     pm = PeerMemory(lay["total"], device, align_to=lay["pitch"])
     seg = pm.local_tensor()
 
@@ -51,14 +52,15 @@ def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, f
         n = 1
         for s in shape:
             n *= s
-        return seg[off:off + n * 4].view(dtype).view(*shape)
+        esz = 2 if dtype == torch.bfloat16 else 4
+        return seg[off:off + n * esz].view(dtype).view(*shape)
 
     class _Shard(DeviceShard):
         pass
 
-    offs = {"keys": lay["keys_off"], "rows": lay["rows_off"], "state": lay["state_off"]}
-    order = iter(["keys", "rows", "state"])
-    shard = DeviceShard(capacity, dim, device, with_state,
+    offs = {"keys": lay["keys_off"], "rows": lay["rows_off"], "state": lay["state_off"], "shadow": lay["shadow_off"]}
+    order = iter(["keys", "rows"] + (["state"] if with_state else []) + (["shadow"] if with_shadow else []))
+    shard = DeviceShard(capacity, dim, device, with_state, with_shadow=with_shadow,
                         alloc=lambda shape, dtype: alloc_at(offs[next(order)], shape, dtype))
     torch.cuda.synchronize(device)
     if world > 1:
@@ -66,7 +68,8 @@ def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, f
     ptrs = []
     for r in range(world):
         b = pm.segment_ptr(r)
-        ptrs.append((b + lay["keys_off"], b + lay["rows_off"], (b + lay["state_off"]) if with_state else 0))
+        ptrs.append((b + lay["keys_off"], b + lay["rows_off"], (b + lay["state_off"]) if with_state else 0,
+                     (b + lay["shadow_off"]) if with_shadow else 0))
     table = ShardedTable(hf, capacity, dim, ptrs, device, seed=seed, init_scale=init_scale, owned=[shard],
                          rank=rank)
     table.peer_memory = pm
@@ -77,24 +80,30 @@ def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, f
 class Inbox:
     """Owner-side gradient inboxes for the one-way multi-GPU push (csrc/kernels/table.cu,
     push_send_kernel): every rank owns two inboxes (step parity) in peer-mapped memory; a push
-    ships (slot, grad row) to the owners, a tiny all-reduce is the barrier, then each owner applies
-    its inbox to its own shard at local-HBM speed and clears it.  This is the reference's
-    "send (key, grad)* to the server, the server applies" (global_push_access.h:123-149,
-    system/server/init.h:116-132) carried by NVLink stores instead of ZeroMQ frames."""
+    ships (slot, grad row) to the owners, hand-off flags in peer memory tell each owner when every
+    sender has finished (no collective on the hot path), then the owner applies its inbox to its
+    own shard at local-HBM speed and clears it.  This is the reference's "send (key, grad)* to the
+    server, the server applies" (global_push_access.h:123-149, system/server/init.h:116-132) carried
+    by NVLink stores instead of ZeroMQ frames.  ``bf16_rows`` ships the gradient rows as bf16 (half
+    the NVLink bytes; the update stays fp32 on fp32 rows and accumulators).  ``barrier`` selects the
+    hand-off: "flags" (default) or "nccl" (a 4-byte all-reduce)."""
 
-    def __init__(self, table: ShardedTable, capacity: int, device):
+    def __init__(self, table: ShardedTable, capacity: int, device, bf16_rows: bool = False, barrier: str = "flags"):
         import ctypes as C
 
         import torch.distributed as dist
 
         self.table, self.device, self.capacity = table, device, int(capacity)
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.bf16_rows, self.barrier = bool(bf16_rows), barrier
         D = table.dim
-        rows_b = self.capacity * D * 4
+        esz = 2 if self.bf16_rows else 4
+        rows_b = self.capacity * D * esz
         slots_off = rows_b
         count_off = slots_off + self.capacity * 4
         per = (count_off + 256 + 4095) // 4096 * 4096
-        self.pm = PeerMemory(2 * per, device)
+        flags_off = 2 * per
+        self.pm = PeerMemory(flags_off + 4096, device)
         seg = self.pm.local_tensor()
         seg.zero_()
         self.views, self.rows_l, self.slots_l, self.count_l = [], [], [], []
@@ -103,18 +112,22 @@ class Inbox:
             for r in range(self.world):
                 b = self.pm.segment_ptr(r) + par * per
                 v.rows[r], v.slots[r], v.count[r] = b, b + slots_off, b + count_off
+                v.flags[r] = self.pm.segment_ptr(r) + flags_off
             v.capacity = self.capacity
             self.views.append(v)
             base = par * per
-            self.rows_l.append(seg[base:base + rows_b].view(torch.float32).view(self.capacity, D))
+            rows = seg[base:base + rows_b]
+            self.rows_l.append(rows.view(torch.bfloat16 if self.bf16_rows else torch.float32).view(self.capacity, D))
             self.slots_l.append(seg[base + slots_off:base + slots_off + self.capacity * 4].view(torch.int32))
             self.count_l.append(seg[base + count_off:base + count_off + 4].view(torch.int32))
+        self.flags_l = seg[flags_off:flags_off + 4 * self.world].view(torch.int32)
         shard = table.owned[0]
         self.local = ShardedTable(HashFrag(1, 1), table.capacity, D, [shard.ptrs()], device, seed=table.seed,
                                   init_scale=table.init_scale, owned=[shard])
         self.overflow = torch.zeros(1, dtype=torch.int32, device=device)
         self.token = torch.zeros(1, dtype=torch.int32, device=device)
         self.parity = 0
+        self.step = 0
         self._C = C
         torch.cuda.synchronize(device)
         dist.barrier()
@@ -126,11 +139,20 @@ class Inbox:
         n = gslot.numel() if n is None else n
         par = self.parity
         self.parity ^= 1
+        self.step += 1
+        sp = _lib.stream_ptr()
         _lib.call("ssb_push_send", self.table._view_ref(), C.byref(self.views[par]), gslot.data_ptr(), grads.data_ptr(), n,
-                  _lib.ptr(n_dev), self.rank, float(lr), float(eps), 1 if adagrad else 0, self.overflow.data_ptr(),
-                  _lib.stream_ptr())
-        dist.all_reduce(self.token)          # barrier: every rank's shipment has landed in my inbox
-        if adagrad:
+                  _lib.ptr(n_dev), self.rank, float(lr), float(eps), 1 if adagrad else 0, 1 if self.bf16_rows else 0,
+                  self.overflow.data_ptr(), sp)
+        if self.barrier == "flags":
+            _lib.call("ssb_flags_signal", C.byref(self.views[par]), self.world, self.rank, self.step, sp)
+            _lib.call("ssb_flags_wait", self.flags_l.data_ptr(), self.world, self.step, sp)
+        else:
+            dist.all_reduce(self.token)      # every rank's shipment has landed in my inbox
+        if self.bf16_rows:
+            _lib.call("ssb_push_bf16", self.local._view_ref(), self.slots_l[par].data_ptr(), self.rows_l[par].data_ptr(),
+                      self.capacity, self.count_l[par].data_ptr(), float(lr), float(eps), 1 if adagrad else 0, sp)
+        elif adagrad:
             self.local.push_adagrad(self.slots_l[par], self.rows_l[par], lr, eps, n_dev=self.count_l[par],
                                     zero_grads=False, n=self.capacity)
         else:
@@ -139,12 +161,12 @@ class Inbox:
         self.count_l[par].zero_()
 
 
-def attach_inbox(table: ShardedTable, capacity: int):
+def attach_inbox(table: ShardedTable, capacity: int, bf16_rows: bool = False, barrier: str = "flags"):
     """Give a peer-mapped table owner-side inboxes (no-op for a single process)."""
     import torch.distributed as dist
 
     if not dist.is_initialized() or dist.get_world_size() == 1:
         table.inbox = None
         return None
-    table.inbox = Inbox(table, capacity, table.device)
+    table.inbox = Inbox(table, capacity, table.device, bf16_rows=bf16_rows, barrier=barrier)
     return table.inbox

@@ -102,6 +102,19 @@ def main():
     assert torch.allclose(w1, wo, rtol=1e-4, atol=1e-5), "inbox AdaGrad differs from the oracle"
     assert int(ib.overflow.item()) == 0
     out["inbox_ok"] = True
+    # variants: collective as the hand-off, and bf16 gradient rows on the wire (0.5 is exact in bf16)
+    for kw in (dict(barrier="nccl"), dict(bf16_rows=True)):
+        dist.barrier()
+        ib2 = attach_inbox(table, 2 * len(common), **kw)
+        for it in range(2):
+            ib2.push(cslot, gr, lr=0.1, eps=1e-8, adagrad=True)
+        torch.cuda.synchronize(); dist.barrier()
+        for _ in range(2 * world):
+            ao = ao + gr * gr
+            wo = wo - 0.1 * gr / torch.sqrt(ao + 1e-8)
+        w2, _ = table.pull(u32_tensor(common, dev))
+        assert torch.allclose(w2, wo, rtol=1e-4, atol=1e-5), ("inbox variant differs", kw)
+        assert int(ib2.overflow.item()) == 0
 
     # ---- 3. NVLink copy probe (kernel ld/st on a peer mapping), timed on the device
     pm = table.peer_memory

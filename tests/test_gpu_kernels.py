@@ -360,3 +360,37 @@ def test_word2vec_pipelined_two_streams(device):
     assert all(np.isfinite(losses))
     assert losses[-1] < 0.9 * losses[0], losses
     assert float(w.loss[1]) > 0
+
+
+def test_bf16_row_mirror_stays_in_step(device):
+    """With a bf16 mirror in the shard, a bf16-only pull reads the mirror; every owner-side writer
+    (lazy insert, SGD / AdaGrad push, bulk load) must keep it equal to bf16(row)."""
+    from swiftsnails_b200.ops._util import u32_tensor
+    from swiftsnails_b200.ops.table import ShardedTable
+
+    t = ShardedTable.local(8192, 128, device, num_shards=2, frag_num=16, with_state=True, with_shadow=True)
+    assert t.has_shadow
+    keys = np.unique(_keys(4000, seed=31))
+    kd = u32_tensor(keys, device)
+    n = len(keys)
+
+    def check():
+        fp32, gslot = t.pull(kd)                                  # reads the fp32 rows
+        bf = torch.empty(n, 128, dtype=torch.bfloat16, device=device)
+        t.pull(kd, rows_bf16=bf, want_fp32=False)                 # reads the mirror
+        assert torch.equal(bf, fp32.to(torch.bfloat16))
+        return gslot
+
+    bf0 = torch.empty(n, 128, dtype=torch.bfloat16, device=device)
+    _, gslot = t.pull(kd, rows_bf16=bf0, want_fp32=False)         # insert path writes row + mirror
+    check()
+    t.push_sgd(gslot, torch.randn(n, 128, device=device), lr=0.1)
+    check()
+    t.push_adagrad(gslot, torch.randn(n, 128, device=device), lr=0.1)
+    check()
+    more = np.setdiff1d(_keys(500, seed=32), keys)
+    t.load(u32_tensor(more, device), torch.randn(len(more), 128, device=device))
+    fp32, _ = t.pull(u32_tensor(more, device), insert=False)
+    bf = torch.empty(len(more), 128, dtype=torch.bfloat16, device=device)
+    t.pull(u32_tensor(more, device), rows_bf16=bf, want_fp32=False, insert=False)
+    assert torch.equal(bf, fp32.to(torch.bfloat16))
