@@ -44,7 +44,7 @@ def parse_args():
     ap.add_argument("--tile-impl", default="auto", choices=["auto", "cuda_core", "tcgen05"])
     ap.add_argument("--lr", type=float, default=0.05)
     ap.add_argument("--zipf-s", type=float, default=1.0)
-    ap.add_argument("--shadow", type=int, default=1, help="bf16 mirror of the table rows, read by the pull (half the row bytes)")
+    ap.add_argument("--shadow", type=int, default=-1, help="bf16 mirror of the table rows, read by the pull (half the row bytes over NVLink); -1 = auto: on from 4 GPUs (measured: 0.563 -> 0.532 ms/step at 8 GPUs, neutral at 2, -3%% at 1)")
     ap.add_argument("--inbox-bf16", type=int, default=1, help="ship inbox gradient rows as bf16")
     ap.add_argument("--inbox-barrier", default="flags", choices=["flags", "nccl"])
     ap.add_argument("--inbox", type=int, default=1, help="multi-GPU AdaGrad push through owner inboxes (one-way) instead of remote atomics")
@@ -95,7 +95,8 @@ def run_ours(args):
     use_inbox = args.impl == "ours" and args.inbox and world > 1 and cfg.optimizer == "adagrad"
     # bf16 mirror of the rows for the (bf16-only) pull; kept in step by owner-side writers, so it is
     # enabled when every push is applied by the owner (single GPU, or the inbox push)
-    with_shadow = bool(args.shadow) and args.impl == "ours" and tile_impl == "tcgen05" and (world == 1 or use_inbox)
+    shadow_on = (world >= 4) if args.shadow < 0 else bool(args.shadow)
+    with_shadow = shadow_on and args.impl == "ours" and tile_impl == "tcgen05" and (world == 1 or use_inbox)
     table = make_table(rows_per_shard, cfg.dim, dev, with_state=(cfg.optimizer == "adagrad"),
                        init_scale=1.0 / cfg.dim, frag_num=max(1024, world), with_shadow=with_shadow)
     if use_inbox:
