@@ -2,6 +2,7 @@
 #include <fstream>
 #include "../../include/ssb200_core.h"
 #include "../apps/algorithms.h"
+#include "corpus_loader.h"
 
 using namespace ssb;
 
@@ -157,6 +158,16 @@ int ssb_cpu_table_dump(void* tp, const char* path) {
   static_cast<CpuTable*>(tp)->table.output(out);
   return 0;
 }
+
+// ---- corpus loader (host-side data pipeline of the GPU workers) ----------------------------------
+void* ssb_corpus_open(const char* path, int batch_tokens, int sent_len, uint32_t pad_id, int epochs) {
+  FILE* f = std::fopen(path, "r");
+  if (!f) return nullptr;
+  std::fclose(f);
+  return new CorpusLoader(path, batch_tokens, sent_len, pad_id, epochs);
+}
+long ssb_corpus_next(void* h, uint32_t* out) { return static_cast<CorpusLoader*>(h)->next(out); }
+void ssb_corpus_close(void* h) { delete static_cast<CorpusLoader*>(h); }
 
 // ---- roles (one role per process; they use the process-wide transfer) ----------------------------
 int ssb_run_master(const char* config_path) {

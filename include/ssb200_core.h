@@ -43,6 +43,13 @@ int64_t ssb_cpu_table_push(void *t, const uint32_t *keys, const float *grads, in
 int64_t ssb_cpu_table_size(void *t);
 int ssb_cpu_table_dump(void *t, const char *path);
 
+/* corpus loader: background parser of `one sentence of integer word ids per line` files into
+ * fixed-size token batches (sentences padded to sent_len with pad_id). next() returns the number
+ * of real tokens in the batch or -1 at the end. ref: utils/file.h:14-33 (scan_file_by_line). */
+void *ssb_corpus_open(const char *path, int batch_tokens, int sent_len, uint32_t pad_id, int epochs);
+long ssb_corpus_next(void *h, uint32_t *out);
+void ssb_corpus_close(void *h);
+
 /* roles — ref: core/framework/SwiftMaster.h, SwiftServer.h, SwiftWorker.h. One role per process. */
 int ssb_run_master(const char *config_path);
 int ssb_run_server(const char *config_path);

@@ -128,6 +128,7 @@ class Word2VecWorker:
             sampler = AliasSampler(unigram_weights_from_zipf(cfg.vocab, cfg.zipf_s), device, seed=cfg.seed + 77)
         self.sampler = sampler
         self.pipeline = bool(pipeline)
+        self.has_padding = False       # set when batches may contain padding tokens (ragged sentences)
         self.sets = [_StepBuffers(self.n_keys, cfg.dim, self.max_pairs, device, self.tc)
                      for _ in range(2 if self.pipeline else 1)]
         self.loss = torch.zeros(2, dtype=torch.float32, device=device)
@@ -156,6 +157,8 @@ class Word2VecWorker:
         ka = s.keys_all
         ka[:B].copy_(tokens)                               # input keys  = w
         torch.add(tokens, cfg.vocab, out=ka[B:2 * B])      # output keys = w + vocab
+        if self.has_padding:                               # padding tokens (0xFFFFFFFF) stay padding
+            ka[B:2 * B].masked_fill_(tokens == -1, -1)
         self.sampler.sample(self.n_negs, out=ka[2 * B:], key_offset=cfg.vocab)
         # K2: unique keys + inverse index (the cache has one entry per key)
         s.dedup(ka, unique=s.unique, inverse=s.inverse, n_unique=s.n_unique)
@@ -287,6 +290,25 @@ class Word2VecTrainer:
             prev = s / max(n, 1.0)
         self._i += 1
         return prev
+
+    def train_file(self, path, epochs=1, log_every=0):
+        """Train from a text corpus (one sentence of integer word ids per line — the reference's data
+        format, tools/gen_word2vec_data.py). Sentences are cut / padded to ``cfg.sent_len``; a native
+        background reader (utils/corpus.py) fills pinned batches while the GPU works.
+        Returns (tokens_trained, last_mean_loss)."""
+        from ..utils.corpus import CorpusLoader
+
+        self.worker.has_padding = True
+        loader = CorpusLoader(path, self.cfg.tokens_per_step, self.cfg.sent_len, epochs=epochs)
+        total, step = 0, 0
+        for buf, n_real in loader:
+            loss = self.train_step(buf)
+            total += n_real
+            step += 1
+            if log_every and step % log_every == 0 and loss is not None:
+                print("step %d  tokens %d  loss/pair %.4f" % (step, total, loss))
+        loader.close()
+        return total, self.finish()
 
     def finish(self):
         if self._i == 0:

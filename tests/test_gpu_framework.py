@@ -67,3 +67,28 @@ def test_user_algorithm_roundtrip(device, tmp_path):
     assert dump.save_table_binary(table, binp) > 0
     t3 = ShardedTable.local(4096, 8, device)
     assert dump.load_table_binary(t3, binp) == len(uniq)
+
+
+def test_train_from_text_corpus_with_ragged_sentences(device, tmp_path):
+    """Native corpus loader -> pinned batches -> tcgen05 step; padding tokens must be ignored."""
+    import subprocess
+    import sys
+
+    from swiftsnails_b200.models.word2vec import Word2VecConfig, Word2VecTrainer
+    from swiftsnails_b200.ops.table import ShardedTable, round_capacity
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    data = str(tmp_path / "corpus.txt")
+    subprocess.run([sys.executable, os.path.join(root, "tools", "gen_word2vec_data.py"), "--lines", "6000", "--vocab", "301",
+                    "--zipf", "1.0", "--out", data], check=True)                      # 6-15 ids per line, like the reference's generator
+    cfg = Word2VecConfig(vocab=301, dim=128, window=5, negatives=5, neg_pool=16, sent_len=16, tokens_per_step=4096,
+                         lr=0.05, optimizer="adagrad", tile_impl="tcgen05")
+    table = ShardedTable.local(round_capacity(2 * cfg.vocab), cfg.dim, device, with_state=True, init_scale=1.0 / cfg.dim)
+    tr = Word2VecTrainer(cfg, table, device)
+    n_lines = sum(1 for _ in open(data))
+    n_tokens = sum(len(l.split()) for l in open(data))
+    first = None
+    total, last = tr.train_file(data, epochs=3)
+    assert total == 3 * n_tokens                                                     # every real token, no padding counted
+    assert table.size() <= 2 * cfg.vocab                                             # no row was created for the padding key
+    assert np.isfinite(last) and last < 4.0, last                                    # 6*ln2 = 4.16 at init

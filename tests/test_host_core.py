@@ -176,3 +176,23 @@ def test_lr_app_local(native_built, tmp_path):
                        capture_output=True, text=True, timeout=120)
     assert p.returncode == 0, p.stderr
     assert parse_result_line(p.stdout)["mean_loss"] < 0.55   # below log(2): it learned
+
+
+def test_corpus_loader(native_built, tmp_path):
+    from swiftsnails_b200.utils.corpus import PAD, CorpusLoader
+
+    lines = [" ".join(str(10 * i + j) for j in range(3 + i % 4)) for i in range(10)]
+    p = tmp_path / "c.txt"
+    p.write_text("\n".join(lines) + "\n")
+    ld = CorpusLoader(str(p), batch_tokens=20, sent_len=5, epochs=2, pin=False)
+    toks, real = [], 0
+    for buf, n in ld:
+        toks.append(buf.numpy().view(np.uint32).copy())
+        real += n
+    ld.close()
+    allt = np.concatenate(toks)
+    assert len(allt) == 20 * 5 and real == 2 * sum(min(len(l.split()), 5) for l in lines)
+    sent0 = allt[:5]
+    assert list(sent0[:3]) == [0, 1, 2] and all(sent0[3:] == PAD)          # padded to sent_len
+    assert list(allt[5:10]) == [10, 11, 12, 13, PAD]
+    assert list(allt[50:53]) == [0, 1, 2]                                   # second epoch starts over
