@@ -41,7 +41,7 @@ def parse_args():
     ap.add_argument("--neg-pool", type=int, default=16)
     ap.add_argument("--tokens-per-step", type=int, default=262144)
     ap.add_argument("--optimizer", default="adagrad", choices=["sgd", "adagrad"])
-    ap.add_argument("--tile-impl", default="auto", choices=["auto", "cuda_core", "tcgen05"])
+    ap.add_argument("--tile-impl", default="auto", choices=["auto", "cuda_core", "tcgen05", "tcgen05_direct"])
     ap.add_argument("--lr", type=float, default=0.05)
     ap.add_argument("--zipf-s", type=float, default=1.0)
     ap.add_argument("--shadow", type=int, default=-1, help="bf16 mirror of the table rows, read by the pull (half the row bytes over NVLink); -1 = auto: on from 4 GPUs (measured: 0.563 -> 0.532 ms/step at 8 GPUs, neutral at 2, -3%% at 1)")
@@ -96,7 +96,7 @@ def run_ours(args):
     # bf16 mirror of the rows for the (bf16-only) pull; kept in step by owner-side writers, so it is
     # enabled when every push is applied by the owner (single GPU, or the inbox push)
     shadow_on = (world >= 4) if args.shadow < 0 else bool(args.shadow)
-    with_shadow = shadow_on and args.impl == "ours" and tile_impl == "tcgen05" and (world == 1 or use_inbox)
+    with_shadow = (shadow_on or tile_impl == "tcgen05_direct") and args.impl == "ours" and tile_impl.startswith("tcgen05") and (world == 1 or use_inbox)
     table = make_table(rows_per_shard, cfg.dim, dev, with_state=(cfg.optimizer == "adagrad"),
                        init_scale=1.0 / cfg.dim, frag_num=max(1024, world), with_shadow=with_shadow)
     if use_inbox:
@@ -191,7 +191,7 @@ def run_ours(args):
         out = {
             "metric": METRIC, "value": value, "unit": "words/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16" if tile_impl == "tcgen05" else "fp32",
+            "dtype": "bf16" if tile_impl.startswith("tcgen05") else "fp32",
             "data": "synthetic Zipf(s=1) corpus, random-init table", "impl": args.impl,
             "config": {"model": "word2vec skip-gram negative sampling", "vocab": cfg.vocab, "dim": cfg.dim,
                        "window": cfg.window, "negatives": cfg.negatives,

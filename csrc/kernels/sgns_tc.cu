@@ -51,7 +51,7 @@ constexpr uint32_t kOffIn = 0;                               // 2 stages
 constexpr uint32_t kOffOn = kOffIn + 2 * kInBytes;           // 65536, 2 stages
 constexpr uint32_t kOffG = kOffOn + 2 * kOnBytes;            // 147456
 constexpr uint32_t kOffMisc = kOffG + kGBlks * kInBlk;       // 212992
-constexpr uint32_t kSmemBytes = kOffMisc + 6144;
+constexpr uint32_t kSmemBytes = kOffMisc + 8192;
 
 // TMEM columns: S (160) | dIn (128) | dON rows 0..127 (128); dON rows 128..255 aliases S.
 constexpr uint32_t kTmemS = 0, kTmemDIn = 160, kTmemDOnA = 288, kTmemDOnB = 0, kTmemCols = 512;
@@ -59,6 +59,8 @@ constexpr uint32_t kTmemS = 0, kTmemDIn = 160, kTmemDOnA = 288, kTmemDOnB = 0, k
 struct Misc {
   uint32_t in_row[2][kM];
   uint32_t on_row[2][kN];
+  uint32_t in_tab[2][kM];       // direct mode: row of the (peer-mapped) bf16 table mirror to gather from
+  uint32_t on_tab[2][kN];
   uint32_t out_rows[kM + kN];   // gradient destination rows of the current tile (INVALID = skip)
   uint8_t lead_in[2][kM];       // first position in the tile holding the same row (tile-local dedup)
   uint8_t lead_on[2][kN];
@@ -71,7 +73,7 @@ struct Misc {
   float loss[kConsumerWarps];
   float pairs[kConsumerWarps];
 };
-static_assert(sizeof(Misc) <= 6144, "misc region too large");
+static_assert(sizeof(Misc) <= 8192, "misc region too large");
 
 // ---- PTX wrappers -----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -173,6 +175,17 @@ __device__ __forceinline__ uint32_t swz_off(uint32_t r, uint32_t c, uint32_t blk
   return cb * blk_bytes + r * 128 + ((ch ^ (r & 7)) << 4) + (e << 1);
 }
 
+// Direct ("fused pull") mode: the TMA gathers operand rows straight from the peer-mapped bf16 mirror of
+// the sharded table — local HBM or a peer's over NVLink — instead of from the worker's cache. All
+// shards sit side by side in one virtual range (parallel/peer.py), so ONE tensor map with a 256-byte
+// row pitch describes the whole distributed table: row = shard * shard_rows + mirror_row_off + slot.
+struct DirectMap {
+  const uint32_t* gslot;      // cache row -> global slot (shard * capacity + slot); nullptr = cache mode
+  uint32_t capacity;          // slots per shard
+  uint32_t shard_rows;        // 256-byte rows per shard segment
+  uint32_t mirror_row_off;    // first mirror row inside a segment
+};
+
 // ---- the kernel -------------------------------------------------------------------------------
 // Warp roles: warps 0..15 = consumers (thread 0 issues the MMAs, all 512 threads run the TMEM
 // epilogues: warp w owns TMEM lanes 32*(w%4).. and column part w/4), warp 16 = producer
@@ -188,7 +201,7 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
                      const uint32_t* __restrict__ inv_in, const uint32_t* __restrict__ inv_out,
                      int n_tok, int sent_len, int window, uint64_t seed, uint64_t offset,
                      const uint32_t* __restrict__ neg_idx, float neg_k, float* __restrict__ loss_out,
-                     const __grid_constant__ CUtensorMap tmap, int mode, float* __restrict__ debug) {
+                     const __grid_constant__ CUtensorMap tmap, int mode, float* __restrict__ debug, const DirectMap dm) {
   extern __shared__ __align__(1024) uint8_t smem[];
   Misc* misc = reinterpret_cast<Misc*>(smem + kOffMisc);
   const uint32_t sbase = smem_u32(smem);
@@ -220,7 +233,14 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
     // Per tile: (wait for the stage) -> publish the row indices -> start the gather (TMA) ->
     // prefetch the NEXT tile's indices into registers -> tile-local dedup -> signal lead_bar.
     // The dedup and the index prefetch run while the TMA engine fills the stage.
-    uint32_t ri[4], ro[5];
+    uint32_t ri[4], ro[5], ti[4], to[5];
+    auto tab_row = [&](uint32_t cache_row) -> uint32_t {
+      if (dm.gslot == nullptr || cache_row == SSB_INVALID_SLOT) return cache_row;
+      const uint32_t g = __ldg(dm.gslot + cache_row);
+      if (g == SSB_INVALID_SLOT) return SSB_INVALID_SLOT;
+      const uint32_t sh = g / dm.capacity;
+      return sh * dm.shard_rows + dm.mirror_row_off + (g - sh * dm.capacity);
+    };
     auto load_idx = [&](int tile) {
       const int t0 = tile * kM;
 #pragma unroll
@@ -242,6 +262,10 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
         }
         ro[k] = v;
       }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) ti[k] = tab_row(ri[k]);
+#pragma unroll
+      for (int k = 0; k < 5; ++k) to[k] = tab_row(ro[k]);
     };
     load_idx(blockIdx.x);
     uint32_t it = 0;
@@ -250,12 +274,30 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
       const int t0 = tile * kM;
       if (it >= 2) mbar_wait(&misc->empty_bar[b], ((it >> 1) - 1) & 1);   // stage freed by the MMAs of tile it-2
       bool bad = false;
+      if (dm.gslot != nullptr) {
+        // Masked-out positions still feed the MMAs (weight 0 in G), so they must gather FINITE data:
+        // 0 * NaN = NaN. In the cache, row 0 is always a real row; in the peer-mapped range row 0 is
+        // the key array of shard 0 (0xFFFFFFFF = bf16 NaN). Substitute a valid row of this tile.
+        uint32_t fb = SSB_INVALID_SLOT;
 #pragma unroll
-      for (int k = 0; k < 4; ++k) misc->in_row[b][lane + 32 * k] = ri[k];
+        for (int k = 0; k < 4; ++k) if (ti[k] != SSB_INVALID_SLOT) fb = ti[k];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) if (to[k] != SSB_INVALID_SLOT) fb = to[k];
+        const unsigned m = __ballot_sync(0xffffffffu, fb != SSB_INVALID_SLOT);
+        fb = __shfl_sync(0xffffffffu, fb, m ? __ffs(m) - 1 : 0);
+        if (m == 0) fb = dm.mirror_row_off;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (ti[k] == SSB_INVALID_SLOT) ti[k] = fb;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) if (to[k] == SSB_INVALID_SLOT) to[k] = fb;
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { misc->in_row[b][lane + 32 * k] = ri[k]; misc->in_tab[b][lane + 32 * k] = ti[k]; }
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
         const int r = lane + 32 * k;
         misc->on_row[b][r] = ro[k];
+        misc->on_tab[b][r] = to[k];
         const int g = t0 - kHalo + r;
         bad = bad || (r < kCtx && g >= 0 && g < n_tok && ro[k] == SSB_INVALID_SLOT);
       }
@@ -270,7 +312,7 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
         for (int g = lane; g < (kM + kN) / 4; g += 32) {
           const bool is_in = g < kM / 4;
           const int r = is_in ? g * 4 : (g - kM / 4) * 4;
-          const uint32_t* rows = is_in ? &misc->in_row[b][r] : &misc->on_row[b][r];
+          const uint32_t* rows = is_in ? &misc->in_tab[b][r] : &misc->on_tab[b][r];   // == cache rows unless direct
           uint32_t i0 = rows[0], i1 = rows[1], i2 = rows[2], i3 = rows[3];
           i0 = i0 == SSB_INVALID_SLOT ? 0 : i0; i1 = i1 == SSB_INVALID_SLOT ? 0 : i1;
           i2 = i2 == SSB_INVALID_SLOT ? 0 : i2; i3 = i3 == SSB_INVALID_SLOT ? 0 : i3;
@@ -285,7 +327,7 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
           const bool is_in = r < kM;
           const uint32_t rr = is_in ? r : r - kM;
           const int l16 = lane & 15;
-          uint32_t row = is_in ? misc->in_row[b][rr] : misc->on_row[b][rr];
+          uint32_t row = is_in ? misc->in_tab[b][rr] : misc->on_tab[b][rr];
           uint4 v = make_uint4(0u, 0u, 0u, 0u);
           if (row != SSB_INVALID_SLOT) v = *reinterpret_cast<const uint4*>(params + (size_t)row * kD + l16 * 8);
           uint32_t off = (is_in ? in_base : on_base) + swz_off(rr, l16 * 8, is_in ? kInBlk : kOnBlk);
@@ -593,10 +635,10 @@ extern "C" {
 // inv_in/inv_out [n_tok]: cache row of each token's input / output vector; neg_idx
 // [ceil(n_tok/128) * 16]: cache rows of each tile's negatives. window <= 8.
 // mode: 0 = vector-load gather, 1 = TMA tile::gather4.
-int ssb_sgns_block_tc(const void* params, float* grads, int64_t n_rows, int32_t dim, const uint32_t* inv_in,
-                      const uint32_t* inv_out, int64_t n_tok, int32_t sent_len, int32_t window, uint64_t seed,
-                      uint64_t offset, const uint32_t* neg_idx, float neg_k, float* loss_out, int32_t mode,
-                      int32_t box_rows, float* debug, void* stream) {
+static int launch_block_tc(const void* params, float* grads, int64_t n_rows, int32_t dim, const uint32_t* inv_in,
+                           const uint32_t* inv_out, int64_t n_tok, int32_t sent_len, int32_t window, uint64_t seed,
+                           uint64_t offset, const uint32_t* neg_idx, float neg_k, float* loss_out, int32_t mode,
+                           int32_t box_rows, float* debug, const ssb::tc::DirectMap& dm, void* stream) {
   using namespace ssb::tc;
   if (n_tok <= 0) return 0;
   if (n_tok >= (1ll << 31) - 4096) return (int)cudaErrorInvalidValue;
@@ -617,9 +659,34 @@ int ssb_sgns_block_tc(const void* params, float* grads, int64_t n_rows, int32_t 
   int blocks = (int)(tiles < ssb::kNumSMs ? tiles : ssb::kNumSMs);
   sgns_block_tc_kernel<<<blocks, kThreads, kSmemBytes, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)params, grads, inv_in, inv_out, (int)n_tok, sent_len, window, seed, offset, neg_idx, neg_k,
-      loss_out, tmap, mode, debug);
+      loss_out, tmap, mode, debug, dm);
   SSB_LAUNCH_CHECK();
   return 0;
+}
+
+int ssb_sgns_block_tc(const void* params, float* grads, int64_t n_rows, int32_t dim, const uint32_t* inv_in,
+                      const uint32_t* inv_out, int64_t n_tok, int32_t sent_len, int32_t window, uint64_t seed,
+                      uint64_t offset, const uint32_t* neg_idx, float neg_k, float* loss_out, int32_t mode,
+                      int32_t box_rows, float* debug, void* stream) {
+  ssb::tc::DirectMap dm{nullptr, 1, 0, 0};
+  return launch_block_tc(params, grads, n_rows, dim, inv_in, inv_out, n_tok, sent_len, window, seed, offset, neg_idx, neg_k,
+                         loss_out, mode, box_rows, debug, dm, stream);
+}
+
+// Fused-pull variant: operand rows are gathered by TMA straight from the bf16 mirror of the sharded
+// table (`mirror_base` = start of the virtual range that holds every shard segment, `shard_rows` /
+// `mirror_row_off` in 256-byte rows, `total_rows` = rows spanned by the tensor map), which may live
+// on peers over NVLink. inv_* / neg_idx still index the worker cache: that is where gradients go and
+// what `gslot[cache_row]` translates into table rows.
+int ssb_sgns_block_tc_direct(const void* mirror_base, uint64_t total_rows, uint32_t capacity, uint32_t shard_rows,
+                             uint32_t mirror_row_off, const uint32_t* gslot, float* grads, int32_t dim,
+                             const uint32_t* inv_in, const uint32_t* inv_out, int64_t n_tok, int32_t sent_len,
+                             int32_t window, uint64_t seed, uint64_t offset, const uint32_t* neg_idx, float neg_k,
+                             float* loss_out, int32_t mode, void* stream) {
+  if (!gslot || capacity == 0) return (int)cudaErrorInvalidValue;
+  ssb::tc::DirectMap dm{gslot, capacity, shard_rows, mirror_row_off};
+  return launch_block_tc(mirror_base, grads, (int64_t)total_rows, dim, inv_in, inv_out, n_tok, sent_len, window, seed, offset,
+                         neg_idx, neg_k, loss_out, mode, 1, nullptr, dm, stream);
 }
 
 }  // extern "C"

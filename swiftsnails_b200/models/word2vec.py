@@ -43,7 +43,7 @@ class Word2VecConfig:
     adagrad_eps: float = 1e-8
     zipf_s: float = 1.0
     seed: int = 1
-    tile_impl: str = "cuda_core"  # "cuda_core" | "tcgen05"
+    tile_impl: str = "cuda_core"  # "cuda_core" | "tcgen05" | "tcgen05_direct" (fused pull: TMA gathers from the table's bf16 mirror)
 
 
 def zipf_weights(vocab: int, s: float = 1.0):
@@ -112,7 +112,10 @@ class Word2VecWorker:
         assert table.dim == cfg.dim
         self.cfg, self.table, self.device = cfg, table, device
         B, w = cfg.tokens_per_step, cfg.window
-        self.tc = cfg.tile_impl == "tcgen05"
+        self.tc = cfg.tile_impl in ("tcgen05", "tcgen05_direct")
+        self.direct = cfg.tile_impl == "tcgen05_direct"
+        if self.direct and getattr(table, "mirror_map", None) is None:
+            raise ValueError("tcgen05_direct needs a table with a single-range bf16 row mirror (with_shadow=True)")
         if self.tc:
             # block formulation (csrc/kernels/sgns_tc.cu): a tile = 128 consecutive centre tokens
             # sharing 16 negatives; no pair list is materialised
@@ -163,12 +166,18 @@ class Word2VecWorker:
         # K2: unique keys + inverse index (the cache has one entry per key)
         s.dedup(ka, unique=s.unique, inverse=s.inverse, n_unique=s.n_unique)
         # K1+K3+K4: route, probe/insert, gather into the cache; grads zeroed in the same pass
-        self.table.pull(s.unique, n_dev=s.n_unique, rows_out=s.params, rows_bf16=s.params_bf16,
+        self.table.pull(s.unique, n_dev=s.n_unique, rows_out=s.params, rows_bf16=None if self.direct else s.params_bf16,
                         want_fp32=not self.tc, gslot_out=s.gslot, grads_zero=s.grads, n=self.n_keys)
 
     def _compute(self, s):
         cfg, B = self.cfg, self.cfg.tokens_per_step
-        if self.tc:
+        if self.direct:
+            # fused pull: the pull above only resolved slots and reset the gradients; the operand rows
+            # are gathered by TMA straight from the owners' bf16 row mirrors (own HBM or NVLink peers)
+            sgns_ops.sgns_block_tc_direct(self.table, s.gslot, s.grads, s.inverse[:B], s.inverse[B:2 * B],
+                                          cfg.sent_len, cfg.window, cfg.seed, s.step_idx * B, s.inverse[2 * B:],
+                                          float(cfg.negatives), self.loss, mode=self.tma_mode)
+        elif self.tc:
             # K5 on tensor cores: TMA gather4 -> tcgen05.mma (bf16) -> TMEM epilogue -> red
             sgns_ops.sgns_block_tc(s.params_bf16, s.grads, s.inverse[:B], s.inverse[B:2 * B],
                                    cfg.sent_len, cfg.window, cfg.seed, s.step_idx * B, s.inverse[2 * B:],

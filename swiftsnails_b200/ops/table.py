@@ -91,6 +91,11 @@ class ShardedTable:
         self.has_state = all(p[2] for p in shard_ptrs)
         self.has_shadow = all(len(p) > 3 and p[3] for p in shard_ptrs)
         self.stats = torch.zeros(4, dtype=torch.int32, device=device)  # [inserts, misses/full, -, -]
+        # (base ptr, total 256-byte rows, rows per shard segment, first mirror row in a segment) when the
+        # bf16 mirrors of all shards lie in ONE virtual range (used by the fused-pull tensor-core kernel)
+        self.mirror_map = None
+        if self.has_shadow and self.num_shards == 1 and self.dim == 128:
+            self.mirror_map = (shard_ptrs[0][3], self.capacity, 0, 0)
 
     # -- construction --------------------------------------------------------------------------
     @classmethod

@@ -74,6 +74,8 @@ def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, f
                          rank=rank)
     table.peer_memory = pm
     table.layout = lay
+    if with_shadow and dim == 128 and pm.stride % 256 == 0 and lay["shadow_off"] % 256 == 0:
+        table.mirror_map = (pm.base, world * pm.stride // 256, pm.stride // 256, lay["shadow_off"] // 256)
     return table
 
 

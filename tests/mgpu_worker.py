@@ -150,6 +150,39 @@ def main():
         losses.append(wk.mean_loss())
     assert all(np.isfinite(losses)) and np.mean(losses[-5:]) < 0.9 * np.mean(losses[:3]), losses
     out["w2v_loss_first_last"] = [losses[0], losses[-1]]
+    # ---- 5. fused pull: TMA gather straight from the peer-mapped bf16 row mirrors vs the cache path
+    from swiftsnails_b200.ops import sgns as sgns_ops
+    from swiftsnails_b200.ops.dedup import Deduper
+
+    dist.barrier()
+    t3 = make_table(4000, 128, dev, with_state=True, init_scale=0.5, frag_num=64, with_shadow=True)
+    rng3 = np.random.default_rng(7 + rank)
+    n_tok, V3 = 2048, 900
+    tokens = rng3.integers(0, V3, n_tok).astype(np.uint32)
+    negs = rng3.integers(0, V3, (n_tok // 128) * 16).astype(np.uint32) + V3
+    k3 = u32_tensor(np.concatenate([tokens, tokens + V3, negs]), dev)
+    uq, inv3, nu3 = Deduper(k3.numel(), dev)(k3)
+    n3 = k3.numel()
+    cache3 = torch.zeros(n3, 128, dtype=torch.bfloat16, device=dev)
+    gs3 = torch.empty(n3, dtype=torch.int32, device=dev)
+    t3.pull(uq, n_dev=nu3, rows_bf16=cache3, want_fp32=False, gslot_out=gs3, n=n3)
+    torch.cuda.synchronize(); dist.barrier()
+    ga, gb = torch.zeros(n3, 128, device=dev), torch.zeros(n3, 128, device=dev)
+    la, lb = torch.zeros(2, device=dev), torch.zeros(2, device=dev)
+    a3 = (inv3[:n_tok], inv3[n_tok:2 * n_tok], 100, 5, 9, 0, inv3[2 * n_tok:], 5.0)
+    sgns_ops.sgns_block_tc(cache3, ga, *a3, la, mode=1)
+    sgns_ops.sgns_block_tc_direct(t3, gs3, gb, *a3, lb, mode=1)
+    torch.cuda.synchronize()
+    nun = int(nu3.item())
+    owner = (to_u32_numpy(gs3)[:nun] // t3.capacity)
+    err_rows = (ga[:nun] - gb[:nun]).abs().amax(1).cpu().numpy()
+    scale = float(ga.abs().max())
+    info = {"loss_cache": float(la[0]), "loss_direct": float(lb[0]), "scale": scale,
+            "max_err_local_rows": float(err_rows[owner == rank].max()), "max_err_remote_rows": float(err_rows[owner != rank].max()),
+            "n_local": int((owner == rank).sum()), "n_remote": int((owner != rank).sum())}
+    print("RANK %d FUSED_PULL %s" % (rank, json.dumps(info)), flush=True)
+    assert np.isfinite(info["loss_direct"]) and err_rows.max() < 1e-2 * scale, info
+    out["fused_pull_ok"] = True
     torch.cuda.synchronize()
     dist.barrier()
     if rank == 0:
