@@ -150,6 +150,42 @@ int ssb_lr_fwd_bwd(const float *params, float *grads, const uint32_t *inv, const
                    const float *labels, int64_t n_ex, int32_t n_feat, float *loss_out,
                    void *stream);
 
+/* ---- K5 on tensor cores (tcgen05 / TMEM / TMA gather4), dim == 128 only ---------------------
+ * One tile = 128 consecutive centre tokens against their 144 context rows + 16 shared negatives.
+ * params: bf16 worker cache [n_rows][128]; grads: fp32 [n_rows][128] (accumulated with vector REDs).
+ * inv_in / inv_out [n_tok]: cache row of each token's input / output vector; neg_idx
+ * [ceil(n_tok/128)*16]: cache rows of each tile's negatives; window <= 8.
+ * mode: 0 = vector-load gather, 1 = TMA tile::gather4. box_rows must be 1; debug may be NULL. */
+int ssb_sgns_block_tc(const void *params, float *grads, int64_t n_rows, int32_t dim,
+                      const uint32_t *inv_in, const uint32_t *inv_out, int64_t n_tok,
+                      int32_t sent_len, int32_t window, uint64_t seed, uint64_t offset,
+                      const uint32_t *neg_idx, float neg_k, float *loss_out, int32_t mode,
+                      int32_t box_rows, float *debug, void *stream);
+/* Fused-pull variant: operand rows are gathered by TMA straight from the bf16 mirror of the
+ * sharded table (local or peer HBM); gslot[] maps a cache row to its global table slot.
+ * mirror_base = start of the virtual range holding every shard segment; shard_rows and
+ * mirror_row_off are in 256-byte rows; total_rows = rows spanned by the tensor map. */
+int ssb_sgns_block_tc_direct(const void *mirror_base, uint64_t total_rows, uint32_t capacity,
+                             uint32_t shard_rows, uint32_t mirror_row_off, const uint32_t *gslot,
+                             float *grads, int32_t dim, const uint32_t *inv_in,
+                             const uint32_t *inv_out, int64_t n_tok, int32_t sent_len,
+                             int32_t window, uint64_t seed, uint64_t offset,
+                             const uint32_t *neg_idx, float neg_k, float *loss_out, int32_t mode,
+                             void *stream);
+
+/* ---- peer memory (CUDA VMM; these DO allocate / map device memory) --------------------------
+ * One physical segment per GPU, exported as a POSIX fd, imported by the peers and mapped side by
+ * side in one reserved virtual range, so shard s lives at base + s * stride on every rank.    */
+int ssb_vmm_granularity(int device, uint64_t *out);
+int ssb_vmm_create(int device, uint64_t bytes, uint64_t *handle, int *fd);
+int ssb_vmm_import(int fd, uint64_t *handle);
+int ssb_vmm_reserve(uint64_t bytes, uint64_t align, uint64_t *va);
+int ssb_vmm_map(uint64_t va, uint64_t bytes, uint64_t handle, int device);
+int ssb_vmm_unmap(uint64_t va, uint64_t bytes);
+int ssb_vmm_release(uint64_t handle);
+int ssb_vmm_free_va(uint64_t va, uint64_t bytes);
+int ssb_memset_async(void *p, int value, uint64_t bytes, void *stream);
+
 /* ---- K11: parameter dump -----------------------------------------------------------------
  * Compacts the live slots of one shard: out_keys[*n_live], out_rows[*n_live][dim].        */
 int ssb_dump_compact(const uint32_t *keys, const float *rows, uint32_t capacity, int32_t dim,

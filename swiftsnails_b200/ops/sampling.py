@@ -31,19 +31,9 @@ def build_alias(weights):
     return prob.astype(np.float32), alias
 
 
-def build_alias_fast(weights):
-    """Vectorised alias construction for large vocabularies (1M+): sort-based pairing.
-    Falls back to the exact Vose loop for small tables."""
-    w = np.asarray(weights, dtype=np.float64)
-    if w.size <= 200_000:
-        return build_alias(w)
-    # Vose with numpy stacks is O(V) python-loop; for large V use the loop in chunks via lists
-    return build_alias(w)
-
-
 class AliasSampler:
     def __init__(self, weights, device, seed=1234):
-        prob, alias = build_alias_fast(weights)
+        prob, alias = build_alias(weights)
         self.vocab = int(prob.size)
         self.prob = torch.from_numpy(prob).to(device)
         self.alias = torch.from_numpy(alias.view(np.int32)).to(device)

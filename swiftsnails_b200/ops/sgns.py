@@ -30,12 +30,6 @@ def sgns_block_tc(params, grads, inv_in, inv_out, sent_len, window, seed, offset
     import torch
 
     assert params.dtype == torch.bfloat16 and grads.dtype == torch.float32
-    import ctypes as C
-
-    if "ssb_sgns_block_tc" not in _lib._KERNEL_SIGS:
-        vp, i64, i32, u64, f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint64, C.c_float
-        _lib.register_sig("ssb_sgns_block_tc", [vp, vp, i64, i32, vp, vp, i64, i32, i32, u64, u64, vp, f32, vp,
-                                                 i32, i32, vp, vp])
     n_rows, dim = params.shape
     n_tok = inv_in.numel()
     _lib.call("ssb_sgns_block_tc", params.data_ptr(), grads.data_ptr(), n_rows, dim, inv_in.data_ptr(),
@@ -49,15 +43,9 @@ def sgns_block_tc_direct(table, gslot, grads, inv_in, inv_out, sent_len, window,
     """Fused-pull variant: the TMA gathers operand rows straight from the table's bf16 row mirror
     (own HBM or peers over NVLink) instead of from a pulled cache.  ``table`` must have a mirror laid
     out in one virtual range (``make_table(..., with_shadow=True)`` or a single local shard)."""
-    import ctypes as C
-
     mm = getattr(table, "mirror_map", None)
     if mm is None:
         raise ValueError("table has no single-range bf16 row mirror (create it with with_shadow=True)")
-    if "ssb_sgns_block_tc_direct" not in _lib._KERNEL_SIGS:
-        vp, i64, i32, u32, u64, f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32, C.c_uint64, C.c_float
-        _lib.register_sig("ssb_sgns_block_tc_direct", [vp, u64, u32, u32, u32, vp, vp, i32, vp, vp, i64, i32, i32, u64, u64,
-                                                        vp, f32, vp, i32, vp])
     base, total_rows, shard_rows, mirror_row_off = mm
     _lib.call("ssb_sgns_block_tc_direct", base, total_rows, table.capacity, shard_rows, mirror_row_off, gslot.data_ptr(),
               grads.data_ptr(), table.dim, inv_in.data_ptr(), inv_out.data_ptr(), inv_in.numel(), sent_len, window, seed,

@@ -14,7 +14,7 @@ import torch
 from .. import _lib
 from ..ops.table import DeviceShard, ShardedTable, round_capacity
 from .hashfrag import HashFrag
-from .peer import PeerMemory, tensor_from_ptr
+from .peer import PeerMemory
 
 
 def shard_layout(capacity, dim, with_state, with_shadow=False):
