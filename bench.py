@@ -39,7 +39,8 @@ def parse_args():
     ap.add_argument("--window", type=int, default=5)
     ap.add_argument("--negatives", type=int, default=5)
     ap.add_argument("--neg-pool", type=int, default=16)
-    ap.add_argument("--tokens-per-step", type=int, default=262144)
+    ap.add_argument("--tokens-per-step", type=int, default=524288,
+                    help="minibatch per GPU; 524288 converges per token like 65536..262144 (benchmarks/batch_size_convergence.py)")
     ap.add_argument("--optimizer", default="adagrad", choices=["sgd", "adagrad"])
     ap.add_argument("--tile-impl", default="auto", choices=["auto", "cuda_core", "tcgen05", "tcgen05_direct"])
     ap.add_argument("--lr", type=float, default=0.05)
