@@ -274,6 +274,13 @@ class Word2VecTrainer:
         self.h2d_bytes = cfg.tokens_per_step * 4
         self.d2h_bytes = 2 * 4
         self._i = 0
+        from ..utils.metrics import registry
+
+        reg = registry()
+        self._m_tokens = reg.counter("ssb_w2v_tokens_total", "tokens fed to Word2VecTrainer.train_step")
+        self._m_steps = reg.counter("ssb_w2v_steps_total", "minibatches trained")
+        self._m_rate = reg.meter("ssb_w2v_words_per_second", "tokens per second over the last 5 s")
+        self._m_loss = reg.gauge("ssb_w2v_loss_per_pair", "mean SGNS loss of the latest completed step")
 
     def train_step(self, tokens_host: torch.Tensor):
         i = self._i & 1
@@ -297,7 +304,11 @@ class Word2VecTrainer:
             self.events[j].synchronize()
             s, n = self.loss_host[j].tolist()
             prev = s / max(n, 1.0)
+            self._m_loss.set(prev)
         self._i += 1
+        self._m_tokens.inc(self.cfg.tokens_per_step)
+        self._m_steps.inc()
+        self._m_rate.mark(self.cfg.tokens_per_step)
         return prev
 
     def train_file(self, path, epochs=1, log_every=0):
