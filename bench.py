@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--prepopulate", type=int, default=1, help="create all 2*vocab rows before timing (steady-state table)")
     ap.add_argument("--pipeline", type=int, default=1, help="overlap dedup+pull of step i+1 with SGNS+push of step i (2 streams)")
     ap.add_argument("--tc-mode", type=int, default=1, help="tcgen05 kernel mode bits (1 = TMA gather4; 2 = perf experiment: skip gradient reds)")
+    ap.add_argument("--slot-cache", type=int, default=1, help="worker-side key->slot cache (starts empty after the table is populated; fills from the warm-up steps on)")
     ap.add_argument("--ref-tokens", type=int, default=60_000, help="tokens per worker for the reference arm")
     return ap.parse_args()
 
@@ -90,7 +91,8 @@ def run_ours(args):
                                   and os.environ.get("SSB200_NO_TC") != "1") else "cuda_core"
     cfg = Word2VecConfig(vocab=args.vocab, dim=args.dim, window=args.window, negatives=args.negatives,
                          neg_pool=args.neg_pool, tokens_per_step=args.tokens_per_step, lr=args.lr,
-                         optimizer=args.optimizer, seed=1 + rank, tile_impl=tile_impl, zipf_s=args.zipf_s)
+                         optimizer=args.optimizer, seed=1 + rank, tile_impl=tile_impl, zipf_s=args.zipf_s,
+                         slot_cache=bool(args.slot_cache) and args.impl == "ours")
     # 2*vocab keys (input + output vectors) spread over `world` shards at load factor 0.5
     rows_per_shard = (2 * cfg.vocab + world - 1) // world
     use_inbox = args.impl == "ours" and args.inbox and world > 1 and cfg.optimizer == "adagrad"
@@ -199,7 +201,7 @@ def run_ours(args):
                        "neg_pool_per_128_pair_tile": cfg.neg_pool, "global_batch": B * world,
                        "tokens_per_step_per_gpu": B, "seq_len": cfg.sent_len, "optimizer": cfg.optimizer,
                        "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if args.impl == "nccl" else "P2P"),
-                       "bf16_row_mirror": with_shadow, "inbox_push": bool(use_inbox), "inbox_rows_bf16": bool(use_inbox and args.inbox_bf16),
+                       "bf16_row_mirror": with_shadow, "worker_slot_cache": bool(cfg.slot_cache), "inbox_push": bool(use_inbox), "inbox_rows_bf16": bool(use_inbox and args.inbox_bf16),
                        "table": "all 2*vocab rows created before timing" if args.prepopulate else "empty at start, rows created lazily inside the timed region",
                        "pipeline": "3 streams: dedup+pull of step i+1 | SGNS of step i | push of step i-1 (staleness <= 1 step)" if worker.pipeline else "off",
                        "tile_impl": tile_impl, "pairs_per_step_per_gpu": n_pairs / K, "unique_keys_last_step": n_unique_last,

@@ -15,9 +15,14 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     opt = sys.argv[1] if len(sys.argv) > 1 else "adagrad"
-    cfg = Word2VecConfig(tile_impl="tcgen05", optimizer=opt, lr=0.05, tokens_per_step=262144, seed=1 + rank)
+    tps = int(sys.argv[2]) if len(sys.argv) > 2 else 524288
+    cfg = Word2VecConfig(tile_impl="tcgen05", optimizer=opt, lr=0.05, tokens_per_step=tps, seed=1 + rank)
+    # same table options as bench.py: bf16 row mirror from 4 GPUs, inbox push (bf16 rows, flag hand-off) from 2
     table = make_table((2 * cfg.vocab + world - 1) // world, cfg.dim, dev, with_state=(opt == "adagrad"), init_scale=1.0 / cfg.dim,
-                       frag_num=max(1024, world))
+                       frag_num=max(1024, world), with_shadow=(world >= 4))
+    if world > 1 and opt == "adagrad":
+        from swiftsnails_b200.parallel.cluster import attach_inbox
+        attach_inbox(table, 2 * (2 * tps + ((tps + 127) // 128) * cfg.neg_pool), bf16_rows=True, barrier="flags")
     allk = torch.arange(rank, 2 * cfg.vocab, world, dtype=torch.int32, device=dev)
     for c in range(0, allk.numel(), 1 << 20):
         table.resolve(allk[c:c + (1 << 20)])
@@ -48,8 +53,7 @@ def main():
                                             gslot_out=s0.gslot, grads_zero=s0.grads, n=w.n_keys)),
               phase("s", lambda: sgns_ops.sgns_block_tc(s0.params_bf16, s0.grads, s0.inverse[:B], s0.inverse[B:2 * B], cfg.sent_len,
                                                          cfg.window, cfg.seed, s * B, s0.inverse[2 * B:], 5.0, w.loss, mode=1)),
-              phase("u", lambda: (table.push_adagrad(s0.gslot, s0.grads, cfg.lr, 1e-8, n_dev=s0.n_unique, zero_grads=False, n=w.n_keys)
-                                  if opt == "adagrad" else table.push_sgd(s0.gslot, s0.grads, cfg.lr, n_dev=s0.n_unique, zero_grads=False, n=w.n_keys)))]
+              phase("u", lambda: w._push(s0))]
         if world > 1: dist.barrier()
         if s >= 2:
             for n, v in zip(names, ts):

@@ -1,6 +1,8 @@
 // route.h — BaseRoute: the process's zmq context plus id -> address / PUSH socket / mutex maps.
 // ref: /root/reference/src/core/transfer/Route.h:20-112.
 #pragma once
+#include <chrono>
+#include <thread>
 #include "../message.h"
 namespace ssb {
 
@@ -46,19 +48,34 @@ class BaseRoute : public VirtualObject {
     send_mutexes_.erase(id);
   }
   bool has_node(int id) { rwlock_read_guard g(lock_); return addrs_.count(id) > 0; }
+  // The master hands the route table to the nodes one after another, so a worker that already has
+  // it can reach a server whose copy is still in flight; the server then has to answer a node it
+  // does not know yet. Lookups therefore wait (bounded) for a missing id instead of aborting.
+  bool wait_for_node(int id, int timeout_ms) {
+    const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(timeout_ms);
+    while (!has_node(id)) {
+      if (std::chrono::steady_clock::now() >= deadline) return false;
+      std::this_thread::sleep_for(std::chrono::milliseconds(1));
+    }
+    return true;
+  }
+  void set_unknown_node_wait_ms(int ms) { unknown_node_wait_ms_ = ms; }
   void* sender(int id) {
+    if (!has_node(id)) wait_for_node(id, unknown_node_wait_ms_);
     rwlock_read_guard g(lock_);
     auto it = senders_.find(id);
     CHECK(it != senders_.end()) << "no route to node " << id;
     return it->second;
   }
   std::mutex& send_mutex(int id) {
+    if (!has_node(id)) wait_for_node(id, unknown_node_wait_ms_);
     rwlock_read_guard g(lock_);
     auto it = send_mutexes_.find(id);
     CHECK(it != send_mutexes_.end()) << "no route to node " << id;
     return *it->second;
   }
   std::string address(int id) {
+    if (!has_node(id)) wait_for_node(id, unknown_node_wait_ms_);
     rwlock_read_guard g(lock_);
     auto it = addrs_.find(id);
     CHECK(it != addrs_.end()) << "no route to node " << id;
@@ -70,6 +87,7 @@ class BaseRoute : public VirtualObject {
 
  protected:
   void* zmq_ctx_ = nullptr;
+  int unknown_node_wait_ms_ = 30000;
   RWLock lock_;
   std::map<int, std::string> addrs_;
   std::map<int, void*> senders_;

@@ -103,6 +103,12 @@ __device__ __forceinline__ uint32_t effective_n(int64_t n, const uint32_t* n_dev
 // bucket, LOCKED slot, insert — takes the acquire-based probe_insert() slow path.
 constexpr int kPullK = 4;
 
+// Direct-mapped worker-side slot cache: 2^bits entries of (key << 32 | global slot); empty = all ones
+// (0xFFFFFFFF is not a legal key). Fibonacci hashing spreads dense word ids without collisions.
+__device__ __forceinline__ uint32_t slot_cache_index(uint32_t key, int bits) {
+  return (key * 0x9E3779B1u) >> (32 - bits);
+}
+
 __device__ __forceinline__ void pull_emit(const SsbTableView& v, uint32_t key, bool valid, const Probe& p, uint32_t w,
                                           int lane, float* __restrict__ rows_out, __nv_bfloat16* __restrict__ rows_bf16,
                                           float* __restrict__ grads_zero, uint32_t* __restrict__ gslot_out,
@@ -178,7 +184,7 @@ __global__ void __launch_bounds__(256)
 pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ keys, int64_t n,
             const uint32_t* __restrict__ n_dev, uint32_t* __restrict__ gslot_out,
             float* __restrict__ rows_out, __nv_bfloat16* __restrict__ rows_bf16, float* __restrict__ grads_zero,
-            int insert, uint32_t* __restrict__ stats) {
+            int insert, uint32_t* __restrict__ stats, unsigned long long* __restrict__ slot_cache, int cache_bits) {
   const int lane = threadIdx.x & 31;
   const uint32_t ne = effective_n(n, n_dev);
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
@@ -188,15 +194,47 @@ pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
   const bool from_shadow = !rows_out && rows_bf16 && v.shadow[0] != nullptr && (D & 3) == 0;
   const uint32_t nb = v.capacity / SSB_BUCKET;
   for (uint32_t w0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * kPullK; w0 < ne; w0 += warps * kPullK) {
-    uint32_t key[kPullK], kv[kPullK], bucket[kPullK];
+    uint32_t key[kPullK], kv[kPullK], bucket[kPullK], cslot[kPullK];
     int owner[kPullK];
     bool valid[kPullK];
-    // phase 1: kPullK independent first-bucket probes
+    // phase 0: the worker's own key -> (shard, slot) cache (local memory). A hit replaces the probe of
+    // the owner's key bucket — a dependent round trip over NVLink when the owner is a peer — by one
+    // 8-byte local load. Slots never move and are cached only once published, so an entry stays true.
 #pragma unroll
     for (int k = 0; k < kPullK; ++k) {
       const uint32_t w = w0 + k;
       key[k] = (w < ne) ? __ldg(keys + w) : SSB_EMPTY_KEY;
       valid[k] = key[k] < SSB_LOCKED_KEY;
+      cslot[k] = SSB_INVALID_SLOT;
+    }
+    if (slot_cache) {
+      // lane 0 reads, the warp shares: every lane must act on the same snapshot of an entry that
+      // another warp (a different key with the same index) may overwrite at any time
+      uint32_t ck[kPullK], cs[kPullK];
+#pragma unroll
+      for (int k = 0; k < kPullK; ++k) {
+        unsigned long long ce = ~0ull;
+        if (lane == 0 && valid[k]) ce = *((const volatile unsigned long long*)(slot_cache + slot_cache_index(key[k], cache_bits)));
+        ck[k] = (uint32_t)(ce >> 32);
+        cs[k] = (uint32_t)ce;
+      }
+      const uint32_t total_slots = v.capacity * (uint32_t)v.num_shards;
+#pragma unroll
+      for (int k = 0; k < kPullK; ++k) {
+        ck[k] = __shfl_sync(0xffffffffu, ck[k], 0);
+        cs[k] = __shfl_sync(0xffffffffu, cs[k], 0);
+        if (valid[k] && ck[k] == key[k] && cs[k] < total_slots) cslot[k] = cs[k];
+      }
+    }
+    // phase 1: independent first-bucket probes for the keys the cache did not resolve
+#pragma unroll
+    for (int k = 0; k < kPullK; ++k) {
+      if (cslot[k] != SSB_INVALID_SLOT) {
+        owner[k] = (int)(cslot[k] / v.capacity);
+        bucket[k] = 0;
+        kv[k] = SSB_EMPTY_KEY;
+        continue;
+      }
       owner[k] = valid[k] ? owner_of(key[k], v.frag_map, v.frag_num) : 0;
       if (owner[k] < 0 || owner[k] >= v.num_shards) { owner[k] = 0; valid[k] = valid[k] && false; }
       bucket[k] = reduce_range(slot_hash(key[k]), nb);
@@ -211,10 +249,11 @@ pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
 #pragma unroll
     for (int k = 0; k < kPullK; ++k) {
       p[k].owner = owner[k]; p[k].slot = SSB_INVALID_SLOT; p[k].is_new = false;
+      const bool cached = cslot[k] != SSB_INVALID_SLOT;     // warp-uniform
       unsigned m = __ballot_sync(0xffffffffu, valid[k] && kv[k] == key[k]);
-      fast[k] = m != 0;
+      fast[k] = cached || m != 0;
       if (fast[k]) {
-        p[k].slot = bucket[k] * SSB_BUCKET + (__ffs(m) - 1);
+        p[k].slot = cached ? cslot[k] - (uint32_t)owner[k] * v.capacity : bucket[k] * SSB_BUCKET + (__ffs(m) - 1);
         if (from_shadow) {
           if (lane * 4 < D) {
             uint2 pk = ld_shadow_u2(reinterpret_cast<const __nv_bfloat16*>(v.shadow[owner[k]]) + (size_t)p[k].slot * D + lane * 4);
@@ -233,6 +272,10 @@ pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
       if (!fast[k] && valid[k]) p[k] = probe_insert(v, key[k], insert != 0, lane);
       pull_emit(v, key[k], valid[k], p[k], w, lane, rows_out, rows_bf16, grads_zero, gslot_out, stats,
                 fast[k] && fast_rows, pre[k]);
+      // remember the slot (after pull_emit: a row this warp created has been published by now)
+      if (slot_cache && lane == 0 && valid[k] && cslot[k] == SSB_INVALID_SLOT && p[k].slot != SSB_INVALID_SLOT)
+        slot_cache[slot_cache_index(key[k], cache_bits)] =
+            ((unsigned long long)key[k] << 32) | ((uint32_t)p[k].owner * v.capacity + p[k].slot);
     }
   }
 }
@@ -540,15 +583,23 @@ static int check_view(const SsbTableView* v) {
   return 0;
 }
 
+int ssb_pull_cached(const SsbTableView* view, const uint32_t* keys, int64_t n, const uint32_t* n_dev,
+                    uint32_t* gslot, float* rows_out, void* rows_bf16, float* grads_zero, int insert,
+                    uint32_t* stats, uint64_t* slot_cache, int32_t cache_bits, void* stream) {
+  if (int e = check_view(view)) return e;
+  if (slot_cache && (cache_bits < 4 || cache_bits > 31)) return (int)cudaErrorInvalidValue;
+  if (n <= 0) return 0;
+  ssb::pull_kernel<<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, keys, n, n_dev, gslot, rows_out,
+                                                                  (__nv_bfloat16*)rows_bf16, grads_zero, insert, stats,
+                                                                  (unsigned long long*)slot_cache, cache_bits);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
 int ssb_pull(const SsbTableView* view, const uint32_t* keys, int64_t n, const uint32_t* n_dev,
              uint32_t* gslot, float* rows_out, void* rows_bf16, float* grads_zero, int insert,
              uint32_t* stats, void* stream) {
-  if (int e = check_view(view)) return e;
-  if (n <= 0) return 0;
-  ssb::pull_kernel<<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, keys, n, n_dev, gslot, rows_out,
-                                                                  (__nv_bfloat16*)rows_bf16, grads_zero, insert, stats);
-  SSB_LAUNCH_CHECK();
-  return 0;
+  return ssb_pull_cached(view, keys, n, n_dev, gslot, rows_out, rows_bf16, grads_zero, insert, stats, nullptr, 0, stream);
 }
 
 int ssb_gather_slots(const SsbTableView* view, const uint32_t* gslot, int64_t n, const uint32_t* n_dev,

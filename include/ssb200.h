@@ -87,6 +87,14 @@ int ssb_dedup_static(const uint32_t *keys, int64_t n, uint32_t *unique, uint32_t
 int ssb_pull(const SsbTableView *view, const uint32_t *keys, int64_t n, const uint32_t *n_dev,
              uint32_t *gslot, float *rows_out, void *rows_bf16, float *grads_zero, int insert,
              uint32_t *stats, void *stream);
+/* Same, with a worker-side slot cache: slot_cache[2^cache_bits] 64-bit entries in the caller's own
+ * device memory, initialised to all ones (0xFF bytes) and owned by ONE table instance. A key found in
+ * the cache skips the probe of the owner's key bucket (one NVLink round trip less per remote key);
+ * keys resolved the slow way are remembered. Legal because slots never move and never die. */
+int ssb_pull_cached(const SsbTableView *view, const uint32_t *keys, int64_t n, const uint32_t *n_dev,
+                    uint32_t *gslot, float *rows_out, void *rows_bf16, float *grads_zero,
+                    int insert, uint32_t *stats, uint64_t *slot_cache, int32_t cache_bits,
+                    void *stream);
 /* Gather by already-resolved global slots (worker-side slot cache hit path). */
 int ssb_gather_slots(const SsbTableView *view, const uint32_t *gslot, int64_t n,
                      const uint32_t *n_dev, float *rows_out, void *stream);

@@ -64,6 +64,7 @@ _KERNEL_SIGS = {
     "ssb_bucket_scatter": ([_vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp], 1),
     "ssb_dedup": ([_vp, _i64, _vp, _vp, _u32, _u32, _vp, _vp, _vp, _i32, _vp], 2),
     "ssb_pull": ([C.POINTER(SsbTableView), _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp], 1),
+    "ssb_pull_cached": ([C.POINTER(SsbTableView), _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _vp], 1),
     "ssb_gather_slots": ([C.POINTER(SsbTableView), _vp, _i64, _vp, _vp, _vp], 1),
     "ssb_push_sgd": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _i32, _vp], 1),
     "ssb_push_adagrad": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _f32, _i32, _vp], 1),

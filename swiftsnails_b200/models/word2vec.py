@@ -44,6 +44,7 @@ class Word2VecConfig:
     zipf_s: float = 1.0
     seed: int = 1
     tile_impl: str = "cuda_core"  # "cuda_core" | "tcgen05" | "tcgen05_direct" (fused pull: TMA gathers from the table's bf16 mirror)
+    slot_cache: bool = True     # worker-side key -> slot cache: repeat pulls skip the owner's key-bucket probe
 
 
 def zipf_weights(vocab: int, s: float = 1.0):
@@ -130,6 +131,8 @@ class Word2VecWorker:
         if sampler is None:
             sampler = AliasSampler(unigram_weights_from_zipf(cfg.vocab, cfg.zipf_s), device, seed=cfg.seed + 77)
         self.sampler = sampler
+        if cfg.slot_cache and getattr(table, "slot_cache", 0) is None:
+            table.enable_slot_cache(2 * cfg.vocab)     # input + output vectors
         self.pipeline = bool(pipeline)
         self.has_padding = False       # set when batches may contain padding tokens (ragged sentences)
         self.sets = [_StepBuffers(self.n_keys, cfg.dim, self.max_pairs, device, self.tc)

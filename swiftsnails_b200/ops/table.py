@@ -94,6 +94,8 @@ class ShardedTable:
         # (base ptr, total 256-byte rows, rows per shard segment, first mirror row in a segment) when the
         # bf16 mirrors of all shards lie in ONE virtual range (used by the fused-pull tensor-core kernel)
         self.mirror_map = None
+        # worker-side key -> slot cache (enable_slot_cache): None = every pull probes the owner's key bucket
+        self.slot_cache, self.slot_cache_bits = None, 0
         if self.has_shadow and self.num_shards == 1 and self.dim == 128:
             self.mirror_map = (shard_ptrs[0][3], self.capacity, 0, 0)
 
@@ -117,17 +119,29 @@ class ShardedTable:
             gslot_out = torch.empty(n, dtype=torch.int32, device=keys.device)
         if rows_out is None and want_fp32:
             rows_out = torch.empty((n, self.dim), dtype=torch.float32, device=keys.device)
-        _lib.call("ssb_pull", self._view_ref(), keys.data_ptr(), n, _lib.ptr(n_dev), gslot_out.data_ptr(),
+        _lib.call("ssb_pull_cached", self._view_ref(), keys.data_ptr(), n, _lib.ptr(n_dev), gslot_out.data_ptr(),
                   _lib.ptr(rows_out), _lib.ptr(rows_bf16), _lib.ptr(grads_zero), 1 if insert else 0,
-                  self.stats.data_ptr(), _lib.stream_ptr())
+                  self.stats.data_ptr(), _lib.ptr(self.slot_cache), self.slot_cache_bits, _lib.stream_ptr())
         return rows_out, gslot_out
+
+    def enable_slot_cache(self, expected_keys, max_bits=26):
+        """Give this worker a direct-mapped key -> (shard, slot) cache of >= 2x ``expected_keys`` entries
+        (8 bytes each, own device memory). Keys it has pulled before then skip the probe of the owner's
+        key bucket — for a remote owner that is one of the two dependent NVLink round trips of a pull.
+        Slots never move and are never freed (table.cu header), so entries cannot go stale."""
+        bits = max(10, min(int(max_bits), (2 * max(int(expected_keys), 1) - 1).bit_length()))
+        if self.slot_cache is None or self.slot_cache_bits != bits:
+            self.slot_cache = torch.full((1 << bits,), -1, dtype=torch.int64, device=self.device)
+            self.slot_cache_bits = bits
+        return self.slot_cache
 
     def resolve(self, keys, insert=True):
         """Keys -> global slots without gathering the rows."""
         n = keys.numel()
         gslot = torch.empty(n, dtype=torch.int32, device=keys.device)
-        _lib.call("ssb_pull", self._view_ref(), keys.data_ptr(), n, None, gslot.data_ptr(), None, None, None,
-                  1 if insert else 0, self.stats.data_ptr(), _lib.stream_ptr())
+        _lib.call("ssb_pull_cached", self._view_ref(), keys.data_ptr(), n, None, gslot.data_ptr(), None, None, None,
+                  1 if insert else 0, self.stats.data_ptr(), _lib.ptr(self.slot_cache), self.slot_cache_bits,
+                  _lib.stream_ptr())
         return gslot
 
     def gather_slots(self, gslot, rows_out=None, n_dev=None, n=None):

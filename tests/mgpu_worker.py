@@ -77,6 +77,24 @@ def main():
     assert torch.allclose(final, w, rtol=1e-4, atol=1e-6), "AdaGrad over peer memory differs"
     out["push_ok"] = True
 
+    # ---- 2a. worker-side slot cache over peer memory: same slots / rows as the probing pull, and a
+    #          cached pull sees what other ranks pushed in between (the cache holds slots, not values)
+    dist.barrier()
+    cache = table.enable_slot_cache(len(keys))
+    for rep in range(2):
+        rows_c, gslot_c = table.pull(u32_tensor(common, dev))
+        assert torch.equal(gslot_c, cslot) and torch.equal(rows_c, final), "cached pull differs (rep %d)" % rep
+    assert int((cache != -1).sum().item()) > 0.7 * len(common)
+    torch.cuda.synchronize(); dist.barrier()
+    table.push_sgd(cslot, torch.full((len(common), dim), 1.0, device=dev), lr=0.125, zero_grads=False)
+    torch.cuda.synchronize(); dist.barrier()
+    rows_c2, _ = table.pull(u32_tensor(common, dev))
+    assert torch.allclose(rows_c2, final - 0.125 * world, rtol=1e-6, atol=1e-6), "cached pull missed remote updates"
+    w = w - 0.125 * world                       # keep the oracle of the next sections in step
+    final = rows_c2
+    table.slot_cache, table.slot_cache_bits = None, 0
+    out["slot_cache_ok"] = True
+
     # ---- 2b. inbox push (one-way shipment, owner applies): same AdaGrad result as the oracle
     from swiftsnails_b200.parallel.cluster import attach_inbox
 
@@ -150,6 +168,25 @@ def main():
         losses.append(wk.mean_loss())
     assert all(np.isfinite(losses)) and np.mean(losses[-5:]) < 0.9 * np.mean(losses[:3]), losses
     out["w2v_loss_first_last"] = [losses[0], losses[-1]]
+    # ---- 4b. the worker-side slot cache does not change training: lock-step runs (barrier after every
+    #          step) with and without it give the same loss curve up to the order of concurrent updates
+    curves = []
+    for use_cache in (False, True):
+        dist.barrier()
+        cfg_c = Word2VecConfig(vocab=3000, dim=128, window=3, negatives=5, neg_pool=16, sent_len=50, tokens_per_step=4096,
+                               lr=0.05, optimizer="adagrad", tile_impl="tcgen05", seed=1 + rank, slot_cache=use_cache)
+        tc_ = make_table(2 * cfg_c.vocab, cfg_c.dim, dev, with_state=True, init_scale=1.0 / cfg_c.dim, frag_num=64)
+        wc = Word2VecWorker(cfg_c, tc_, dev)
+        assert (tc_.slot_cache is not None) == use_cache
+        curve = []
+        for s in range(12):
+            wc.reset_loss()
+            wc.step(u32_tensor(base[s * cfg_c.tokens_per_step:(s + 1) * cfg_c.tokens_per_step], dev))
+            curve.append(wc.mean_loss())
+            torch.cuda.synchronize(); dist.barrier()
+        curves.append(curve)
+    assert np.allclose(curves[0], curves[1], rtol=2e-2), curves
+    out["slot_cache_w2v_max_rel_diff"] = float(np.max(np.abs(np.array(curves[0]) - np.array(curves[1])) / np.array(curves[0])))
     # ---- 5. fused pull: TMA gather straight from the peer-mapped bf16 row mirrors vs the cache path
     from swiftsnails_b200.ops import sgns as sgns_ops
     from swiftsnails_b200.ops.dedup import Deduper

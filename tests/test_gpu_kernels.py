@@ -99,6 +99,59 @@ def test_pull_insert_init_and_gather(device, dim, num_shards):
     assert t.size() == len(keys)
 
 
+@pytest.mark.parametrize("num_shards", [1, 4])
+def test_pull_slot_cache_matches_uncached(device, num_shards):
+    """ssb_pull_cached: with a worker-side key->slot cache the pull returns exactly what the probing pull
+    returns — on the filling pass, on an all-hit pass, with a tiny cache that thrashes, after pushes, and
+    for keys inserted later."""
+    from swiftsnails_b200.ops._util import to_u32_numpy
+    from swiftsnails_b200.ops.table import ShardedTable
+
+    dim = 128
+    plain = ShardedTable.local(16384, dim, device, num_shards=num_shards, frag_num=64, seed=7, init_scale=0.5)
+    keys = np.unique(_keys(5000, seed=21))
+    kd = _dev(keys, device)
+    rows0, gslot0 = plain.pull(kd)
+    for expected in (len(keys), 64):                       # roomy cache / thrashing cache (1024 entries min)
+        t = ShardedTable.local(16384, dim, device, num_shards=num_shards, frag_num=64, seed=7, init_scale=0.5)
+        cache = t.enable_slot_cache(expected)
+        assert cache.numel() == 1 << t.slot_cache_bits and bool((cache == -1).all())
+        for rep in range(3):                               # fill, then hit
+            rows, gslot = t.pull(kd)
+            assert torch.equal(rows, rows0)
+            # slot numbering depends on insertion races, so compare through the keys: every slot holds its key
+            g = to_u32_numpy(gslot)
+            assert len(np.unique(g)) == len(keys)
+            assert np.array_equal(g // t.capacity, t.hashfrag.to_shard(keys))
+        filled = int((cache != -1).sum().item())
+        assert filled > 0 and filled <= len(keys)
+        if expected == len(keys):
+            assert filled > 0.7 * len(keys)                 # direct-mapped: a few keys share an index
+        ck = (cache[cache != -1] >> 32).cpu().numpy().astype(np.uint32)
+        assert np.isin(ck, keys).all()
+        # cached slots are the table's slots: gather by the cached pull's slots == rows
+        assert torch.equal(t.gather_slots(gslot), rows0)
+        # updates are seen through the cache (it caches slots, not values)
+        grads = torch.randn(len(keys), dim, device=device)
+        t.push_sgd(gslot, grads.clone(), lr=0.5, zero_grads=False)
+        rows1, gslot1 = t.pull(kd)
+        assert torch.equal(gslot1, gslot)
+        assert torch.allclose(rows1, rows0 - 0.5 * grads, atol=1e-6)
+        # keys that arrive later are inserted and then cached; absent keys with insert=False are not cached
+        more = np.setdiff1d(np.unique(_keys(1500, seed=22)), keys)
+        absent = np.setdiff1d(np.unique(_keys(500, seed=23)), np.concatenate([keys, more]))
+        _, ga = t.pull(_dev(absent, device), insert=False)
+        assert np.all(to_u32_numpy(ga) == 0xFFFFFFFF)
+        r_a, g_a = t.pull(_dev(more, device))
+        r_b, g_b = t.pull(_dev(more, device))
+        assert torch.equal(r_a, r_b) and torch.equal(g_a, g_b)
+        assert t.size() == len(keys) + len(more)
+        _, ga2 = t.pull(_dev(absent, device), insert=False)
+        assert np.all(to_u32_numpy(ga2) == 0xFFFFFFFF)
+        # resolve() shares the cache
+        assert torch.equal(t.resolve(kd), gslot)
+
+
 def test_pull_duplicate_keys_same_batch(device):
     """Concurrent warps inserting the same key must agree on one slot (claim protocol)."""
     from swiftsnails_b200.ops._util import to_u32_numpy
