@@ -364,7 +364,12 @@ push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
 template <bool kAdaGrad>
 __global__ void __launch_bounds__(256)
 push_bf16_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot,
-                 const __nv_bfloat16* __restrict__ grads, int64_t n, const uint32_t* __restrict__ n_dev, float lr, float eps) {
+                 const __nv_bfloat16* __restrict__ grads, int64_t n, const uint32_t* __restrict__ n_dev, float lr, float eps,
+                 int64_t seg_stride) {
+  // blockIdx.y = inbox segment (one per sender): segment y holds rows [y * seg_stride, y * seg_stride + n_dev[y])
+  if (n_dev) n_dev += blockIdx.y;
+  gslot += (size_t)blockIdx.y * seg_stride;
+  grads += (size_t)blockIdx.y * seg_stride * v.dim;
   const int lane = threadIdx.x & 31;
   const uint32_t ne = effective_n(n, n_dev);
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
@@ -405,6 +410,22 @@ __global__ void flags_signal_kernel(const __grid_constant__ SsbInboxView ib, int
   __threadfence_system();
   if ((int)threadIdx.x < num_shards) st_release_sys(ib.flags[threadIdx.x] + self, value);
 }
+// Private-region inboxes: every sender owns a sub-region of each owner's inbox, so space is claimed
+// with LOCAL atomics on `cursor[owner]` and the row counts are published once per step with plain
+// peer stores (no remote atomic ever serialises on an owner's counter). value != 0 also raises the
+// hand-off flags.
+__global__ void inbox_publish_kernel(const __grid_constant__ SsbInboxView ib, int num_shards, int self,
+                                     uint32_t* __restrict__ cursor, uint32_t value) {
+  const int o = threadIdx.x;
+  if (o < num_shards) {
+    const uint32_t c = cursor[o];
+    cursor[o] = 0;
+    if (o != self) *((volatile uint32_t*)ib.count[o]) = c < ib.capacity ? c : ib.capacity;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (value != 0 && o < num_shards) st_release_sys(ib.flags[o] + self, value);
+}
 __global__ void flags_wait_kernel(const uint32_t* __restrict__ my_flags, int num_shards, uint32_t value) {
   if ((int)threadIdx.x < num_shards) {
     uint32_t it = 0;
@@ -431,7 +452,8 @@ template <bool kAdaGrad, bool kBf16>
 __global__ void __launch_bounds__(256)
 push_send_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__ SsbInboxView ib,
                  const uint32_t* __restrict__ gslot, const float* __restrict__ grads, int64_t n,
-                 const uint32_t* __restrict__ n_dev, int self_shard, float lr, float eps, uint32_t* __restrict__ overflow) {
+                 const uint32_t* __restrict__ n_dev, int self_shard, float lr, float eps, uint32_t* __restrict__ overflow,
+                 uint32_t* __restrict__ cursor) {
   __shared__ uint32_t cnt[SSB_MAX_SHARDS], base[SSB_MAX_SHARDS];
   __shared__ uint32_t row_slot[kSendRows];
   __shared__ uint16_t row_owner[kSendRows], row_rank[kSendRows];
@@ -454,8 +476,8 @@ push_send_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__
       row_owner[threadIdx.x] = o; row_rank[threadIdx.x] = rk; row_slot[threadIdx.x] = sl;
     }
     __syncthreads();
-    if (threadIdx.x < v.num_shards && cnt[threadIdx.x])
-      base[threadIdx.x] = atomicAdd(ib.count[threadIdx.x], cnt[threadIdx.x]);   // remote claim, once per (block, owner)
+    if (threadIdx.x < v.num_shards && cnt[threadIdx.x])   // claim once per (block, owner): local cursor (private regions) or remote counter
+      base[threadIdx.x] = cursor ? atomicAdd(cursor + threadIdx.x, cnt[threadIdx.x]) : atomicAdd(ib.count[threadIdx.x], cnt[threadIdx.x]);
     __syncthreads();
     for (int k = warp; k < kSendRows; k += 8) {
       const uint32_t r = r0 + k;
@@ -633,14 +655,24 @@ int ssb_push_adagrad(const SsbTableView* view, const uint32_t* gslot, float* gra
   return 0;
 }
 
+int ssb_push_send2(const SsbTableView* view, const SsbInboxView* inbox, const uint32_t* gslot, const float* grads,
+                   int64_t n, const uint32_t* n_dev, int32_t self_shard, float lr, float eps, int32_t adagrad,
+                   int32_t bf16_rows, uint32_t* overflow, uint32_t* cursor, void* stream);
+
 int ssb_push_send(const SsbTableView* view, const SsbInboxView* inbox, const uint32_t* gslot, const float* grads,
                   int64_t n, const uint32_t* n_dev, int32_t self_shard, float lr, float eps, int32_t adagrad,
                   int32_t bf16_rows, uint32_t* overflow, void* stream) {
+  return ssb_push_send2(view, inbox, gslot, grads, n, n_dev, self_shard, lr, eps, adagrad, bf16_rows, overflow, nullptr, stream);
+}
+
+int ssb_push_send2(const SsbTableView* view, const SsbInboxView* inbox, const uint32_t* gslot, const float* grads,
+                   int64_t n, const uint32_t* n_dev, int32_t self_shard, float lr, float eps, int32_t adagrad,
+                   int32_t bf16_rows, uint32_t* overflow, uint32_t* cursor, void* stream) {
   if (int e = check_view(view)) return e;
   if (!inbox || inbox->capacity == 0 || (view->dim & 3) != 0) return (int)cudaErrorInvalidValue;
   if (n <= 0) return 0;
   int blocks = ssb::grid_for(n, ssb::kSendRows, ssb::kNumSMs * 8);
-#define SSB_SEND(A, B) ssb::push_send_kernel<A, B><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, overflow)
+#define SSB_SEND(A, B) ssb::push_send_kernel<A, B><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, overflow, cursor)
   if (adagrad) { if (bf16_rows) SSB_SEND(true, true); else SSB_SEND(true, false); }
   else { if (bf16_rows) SSB_SEND(false, true); else SSB_SEND(false, false); }
 #undef SSB_SEND
@@ -648,15 +680,28 @@ int ssb_push_send(const SsbTableView* view, const SsbInboxView* inbox, const uin
   return 0;
 }
 
+int ssb_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, const void* grads_bf16, int64_t seg_rows,
+                      int32_t num_segs, const uint32_t* counts, float lr, float eps, int32_t adagrad, void* stream) {
+  if (int e = check_view(view)) return e;
+  if ((view->dim & 3) != 0 || num_segs < 1 || num_segs > SSB_MAX_SHARDS || (num_segs > 1 && !counts)) return (int)cudaErrorInvalidValue;
+  if (seg_rows <= 0) return 0;
+  dim3 grid(ssb::grid_for(seg_rows, 8, ssb::kNumSMs * 8 / (num_segs > 1 ? 2 : 1)), num_segs);
+  if (adagrad)
+    ssb::push_bf16_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(*view, gslot, (const __nv_bfloat16*)grads_bf16, seg_rows, counts, lr, eps, seg_rows);
+  else
+    ssb::push_bf16_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(*view, gslot, (const __nv_bfloat16*)grads_bf16, seg_rows, counts, lr, eps, seg_rows);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
 int ssb_push_bf16(const SsbTableView* view, const uint32_t* gslot, const void* grads_bf16, int64_t n, const uint32_t* n_dev,
                   float lr, float eps, int32_t adagrad, void* stream) {
-  if (int e = check_view(view)) return e;
-  if ((view->dim & 3) != 0) return (int)cudaErrorInvalidValue;
-  if (n <= 0) return 0;
-  if (adagrad)
-    ssb::push_bf16_kernel<true><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, (const __nv_bfloat16*)grads_bf16, n, n_dev, lr, eps);
-  else
-    ssb::push_bf16_kernel<false><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, (const __nv_bfloat16*)grads_bf16, n, n_dev, lr, eps);
+  return ssb_push_bf16_seg(view, gslot, grads_bf16, n, 1, n_dev, lr, eps, adagrad, stream);
+}
+
+int ssb_inbox_publish(const SsbInboxView* inbox, int32_t num_shards, int32_t self, uint32_t* cursor, uint32_t value, void* stream) {
+  if (!inbox || !cursor || num_shards < 1 || num_shards > SSB_MAX_SHARDS) return (int)cudaErrorInvalidValue;
+  ssb::inbox_publish_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*inbox, num_shards, self, cursor, value);
   SSB_LAUNCH_CHECK();
   return 0;
 }

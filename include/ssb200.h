@@ -125,6 +125,22 @@ typedef struct SsbInboxView {
 int ssb_push_send(const SsbTableView *view, const SsbInboxView *inbox, const uint32_t *gslot,
                   const float *grads, int64_t n, const uint32_t *n_dev, int32_t self_shard, float lr,
                   float eps, int32_t adagrad, int32_t bf16_rows, uint32_t *overflow, void *stream);
+/* Private-region form: `inbox` describes THIS sender's sub-region of every owner's inbox (rows / slots
+ * offset to it, capacity = rows per sub-region, count[o] = where owner o expects this sender's row
+ * count). Space is claimed with local atomics on cursor[SSB_MAX_SHARDS] (device memory, zero before
+ * the first call); ssb_inbox_publish then stores the counts to the owners with plain peer stores,
+ * resets the cursor and, when value != 0, raises the hand-off flags. No remote atomic is issued. */
+int ssb_push_send2(const SsbTableView *view, const SsbInboxView *inbox, const uint32_t *gslot,
+                   const float *grads, int64_t n, const uint32_t *n_dev, int32_t self_shard, float lr,
+                   float eps, int32_t adagrad, int32_t bf16_rows, uint32_t *overflow, uint32_t *cursor,
+                   void *stream);
+int ssb_inbox_publish(const SsbInboxView *inbox, int32_t num_shards, int32_t self, uint32_t *cursor,
+                      uint32_t value, void *stream);
+/* Owner-side apply of num_segs sub-regions in one launch: segment y = rows [y*seg_rows, y*seg_rows +
+ * counts[y]) of gslot / grads_bf16. */
+int ssb_push_bf16_seg(const SsbTableView *view, const uint32_t *gslot, const void *grads_bf16,
+                      int64_t seg_rows, int32_t num_segs, const uint32_t *counts, float lr, float eps,
+                      int32_t adagrad, void *stream);
 /* Owner-side apply when the inbox rows are bf16 (bf16_rows=1 above): fp32 update from bf16 gradients. */
 int ssb_push_bf16(const SsbTableView *view, const uint32_t *gslot, const void *grads_bf16, int64_t n,
                   const uint32_t *n_dev, float lr, float eps, int32_t adagrad, void *stream);

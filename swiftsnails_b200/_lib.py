@@ -69,6 +69,9 @@ _KERNEL_SIGS = {
     "ssb_push_sgd": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _i32, _vp], 1),
     "ssb_push_adagrad": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _f32, _i32, _vp], 1),
     "ssb_push_send": ([C.POINTER(SsbTableView), C.POINTER(SsbInboxView), _vp, _vp, _i64, _vp, _i32, _f32, _f32, _i32, _i32, _vp, _vp], 1),
+    "ssb_push_send2": ([C.POINTER(SsbTableView), C.POINTER(SsbInboxView), _vp, _vp, _i64, _vp, _i32, _f32, _f32, _i32, _i32, _vp, _vp, _vp], 1),
+    "ssb_inbox_publish": ([C.POINTER(SsbInboxView), _i32, _i32, _vp, _u32, _vp], 1),
+    "ssb_push_bf16_seg": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _i32, _vp, _f32, _f32, _i32, _vp], 1),
     "ssb_push_bf16": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _f32, _i32, _vp], 1),
     "ssb_flags_signal": ([C.POINTER(SsbInboxView), _i32, _i32, _u32, _vp], 1),
     "ssb_flags_wait": ([_vp, _i32, _u32, _vp], 1),

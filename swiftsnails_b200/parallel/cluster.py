@@ -81,22 +81,28 @@ def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, f
 
 class Inbox:
     """Owner-side gradient inboxes for the one-way multi-GPU push (csrc/kernels/table.cu,
-    push_send_kernel): every rank owns two inboxes (step parity) in peer-mapped memory; a push
-    ships (slot, grad row) to the owners, hand-off flags in peer memory tell each owner when every
-    sender has finished (no collective on the hot path), then the owner applies its inbox to its
-    own shard at local-HBM speed and clears it.  This is the reference's "send (key, grad)* to the
+    push_send_kernel): every rank owns two inboxes (step parity) in peer-mapped memory, each split
+    into one private sub-region per sender.  A push ships (slot, grad row) into the sender's own
+    sub-region on each owner — space is claimed with local atomics, no remote atomic exists on this
+    path — then publishes its row counts and raises hand-off flags in peer memory; an owner waits
+    for every sender's flag (no collective on the hot path) and applies all sub-regions to its own
+    shard in one launch at local-HBM speed.  This is the reference's "send (key, grad)* to the
     server, the server applies" (global_push_access.h:123-149, system/server/init.h:116-132) carried
     by NVLink stores instead of ZeroMQ frames.  ``bf16_rows`` ships the gradient rows as bf16 (half
     the NVLink bytes; the update stays fp32 on fp32 rows and accumulators).  ``barrier`` selects the
-    hand-off: "flags" (default) or "nccl" (a 4-byte all-reduce)."""
+    hand-off: "flags" (default) or "nccl" (a 4-byte all-reduce).  ``capacity`` = rows per owner
+    inbox; a sender may use ``capacity // world`` of them (excess rows are counted in ``overflow``
+    and dropped)."""
 
     def __init__(self, table: ShardedTable, capacity: int, device, bf16_rows: bool = False, barrier: str = "flags"):
         import ctypes as C
 
         import torch.distributed as dist
 
-        self.table, self.device, self.capacity = table, device, int(capacity)
+        self.table, self.device = table, device
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.seg_rows = max(64, (int(capacity) + self.world - 1) // self.world)     # rows per (owner, sender)
+        self.capacity = self.seg_rows * self.world
         self.bf16_rows, self.barrier = bool(bf16_rows), barrier
         D = table.dim
         esz = 2 if self.bf16_rows else 4
@@ -110,23 +116,28 @@ class Inbox:
         seg.zero_()
         self.views, self.rows_l, self.slots_l, self.count_l = [], [], [], []
         for par in range(2):
+            # the view a SENDER uses: its private sub-region on every owner
             v = _lib.SsbInboxView()
             for r in range(self.world):
                 b = self.pm.segment_ptr(r) + par * per
-                v.rows[r], v.slots[r], v.count[r] = b, b + slots_off, b + count_off
+                v.rows[r] = b + self.rank * self.seg_rows * D * esz
+                v.slots[r] = b + slots_off + self.rank * self.seg_rows * 4
+                v.count[r] = b + count_off + self.rank * 4
                 v.flags[r] = self.pm.segment_ptr(r) + flags_off
-            v.capacity = self.capacity
+            v.capacity = self.seg_rows
             self.views.append(v)
+            # what the OWNER applies: all sub-regions of its own inbox
             base = par * per
             rows = seg[base:base + rows_b]
             self.rows_l.append(rows.view(torch.bfloat16 if self.bf16_rows else torch.float32).view(self.capacity, D))
             self.slots_l.append(seg[base + slots_off:base + slots_off + self.capacity * 4].view(torch.int32))
-            self.count_l.append(seg[base + count_off:base + count_off + 4].view(torch.int32))
+            self.count_l.append(seg[base + count_off:base + count_off + 4 * self.world].view(torch.int32))
         self.flags_l = seg[flags_off:flags_off + 4 * self.world].view(torch.int32)
         shard = table.owned[0]
         self.local = ShardedTable(HashFrag(1, 1), table.capacity, D, [shard.ptrs()], device, seed=table.seed,
                                   init_scale=table.init_scale, owned=[shard])
         self.overflow = torch.zeros(1, dtype=torch.int32, device=device)
+        self.cursor = torch.zeros(16, dtype=torch.int32, device=device)     # rows claimed per owner this step
         self.token = torch.zeros(1, dtype=torch.int32, device=device)
         self.parity = 0
         self.step = 0
@@ -143,24 +154,30 @@ class Inbox:
         self.parity ^= 1
         self.step += 1
         sp = _lib.stream_ptr()
-        _lib.call("ssb_push_send", self.table._view_ref(), C.byref(self.views[par]), gslot.data_ptr(), grads.data_ptr(), n,
+        view = C.byref(self.views[par])
+        _lib.call("ssb_push_send2", self.table._view_ref(), view, gslot.data_ptr(), grads.data_ptr(), n,
                   _lib.ptr(n_dev), self.rank, float(lr), float(eps), 1 if adagrad else 0, 1 if self.bf16_rows else 0,
-                  self.overflow.data_ptr(), sp)
+                  self.overflow.data_ptr(), self.cursor.data_ptr(), sp)
         if self.barrier == "flags":
-            _lib.call("ssb_flags_signal", C.byref(self.views[par]), self.world, self.rank, self.step, sp)
+            _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), self.step, sp)
             _lib.call("ssb_flags_wait", self.flags_l.data_ptr(), self.world, self.step, sp)
         else:
+            _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), 0, sp)
             dist.all_reduce(self.token)      # every rank's shipment has landed in my inbox
         if self.bf16_rows:
-            _lib.call("ssb_push_bf16", self.local._view_ref(), self.slots_l[par].data_ptr(), self.rows_l[par].data_ptr(),
-                      self.capacity, self.count_l[par].data_ptr(), float(lr), float(eps), 1 if adagrad else 0, sp)
-        elif adagrad:
-            self.local.push_adagrad(self.slots_l[par], self.rows_l[par], lr, eps, n_dev=self.count_l[par],
-                                    zero_grads=False, n=self.capacity)
+            _lib.call("ssb_push_bf16_seg", self.local._view_ref(), self.slots_l[par].data_ptr(), self.rows_l[par].data_ptr(),
+                      self.seg_rows, self.world, self.count_l[par].data_ptr(), float(lr), float(eps), 1 if adagrad else 0, sp)
         else:
-            self.local.push_sgd(self.slots_l[par], self.rows_l[par], lr, n_dev=self.count_l[par], zero_grads=False,
-                                n=self.capacity)
-        self.count_l[par].zero_()
+            S = self.seg_rows
+            for r in range(self.world):
+                if r == self.rank:
+                    continue                 # own rows were applied directly by the send kernel
+                sl, rw, cn = self.slots_l[par][r * S:(r + 1) * S], self.rows_l[par][r * S:(r + 1) * S], self.count_l[par][r:r + 1]
+                if adagrad:
+                    self.local.push_adagrad(sl, rw, lr, eps, n_dev=cn, zero_grads=False, n=S)
+                else:
+                    self.local.push_sgd(sl, rw, lr, n_dev=cn, zero_grads=False, n=S)
+        # no clearing: every sender overwrites its count on its next publish (also with 0 rows)
 
 
 def attach_inbox(table: ShardedTable, capacity: int, bf16_rows: bool = False, barrier: str = "flags"):
