@@ -52,7 +52,7 @@ def parse_args():
     ap.add_argument("--prepopulate", type=int, default=1, help="create all 2*vocab rows before timing (steady-state table)")
     ap.add_argument("--pipeline", type=int, default=1, help="overlap dedup+pull of step i+1 with SGNS+push of step i (2 streams)")
     ap.add_argument("--tc-mode", type=int, default=1, help="tcgen05 kernel mode bits (1 = TMA gather4; 2 = perf experiment: skip gradient reds)")
-    ap.add_argument("--slot-cache", type=int, default=1, help="worker-side key->slot cache (starts empty after the table is populated; fills from the warm-up steps on)")
+    ap.add_argument("--slot-cache", type=int, default=-1, help="worker-side key->slot cache (starts empty after the table is populated; fills from the warm-up steps on); -1 = auto: on from 2 GPUs")
     ap.add_argument("--ref-tokens", type=int, default=60_000, help="tokens per worker for the reference arm")
     return ap.parse_args()
 
@@ -92,7 +92,7 @@ def run_ours(args):
     cfg = Word2VecConfig(vocab=args.vocab, dim=args.dim, window=args.window, negatives=args.negatives,
                          neg_pool=args.neg_pool, tokens_per_step=args.tokens_per_step, lr=args.lr,
                          optimizer=args.optimizer, seed=1 + rank, tile_impl=tile_impl, zipf_s=args.zipf_s,
-                         slot_cache=bool(args.slot_cache) and args.impl == "ours")
+                         slot_cache=(args.impl == "ours" and (world > 1 if args.slot_cache < 0 else bool(args.slot_cache))))
     # 2*vocab keys (input + output vectors) spread over `world` shards at load factor 0.5
     rows_per_shard = (2 * cfg.vocab + world - 1) // world
     use_inbox = args.impl == "ours" and args.inbox and world > 1 and cfg.optimizer == "adagrad"

@@ -44,26 +44,46 @@ def raw_summary(rep):
     return out
 
 
-def stalls(rep, top=25):
-    rows = ncu_csv(rep, "source")
-    res, cur, hdr = [], None, None
+def base_name(kernel):
+    """'void ssb::push_kernel<1>(SsbTableView, ...)' -> 'push_kernel'"""
+    k = kernel.split("(")[0]
+    k = re.sub(r"<.*", "", k).strip()
+    return k.split("::")[-1].split(" ")[-1]
+
+
+def stalls_by_source_line(rep, kernel, top=22):
+    """Warp-stall samples of one kernel aggregated per CUDA source line (needs -lineinfo + --import-source on):
+    [(share %, 'file:line', source text, 'reason=n, reason=n')]"""
+    p = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass", "--kernel-name",
+                        "regex:" + kernel], capture_output=True, text=True)
+    rows = list(csv.reader(io.StringIO(p.stdout)))
+    fname, hdr, agg = None, None, {}
     for r in rows:
-        if "Source" in r and "Address" in r:
-            hdr = {h: i for i, h in enumerate(r)}
-            cur = []
-            res.append(cur)
+        if r and r[0] == "File Path":
+            fname = os.path.basename(r[1])
             continue
-        if hdr is None or len(r) < len(hdr):
+        if r and r[0] == "Line No":
+            hdr = r
+            continue
+        if not hdr or len(r) < 8 or r[2] != "-" or not r[0].isdigit():
             continue
         try:
-            v = float(r[hdr["Warp Stall Sampling (All Samples)"]])
+            n = int(r[hdr.index("# Samples")])
         except ValueError:
             continue
-        cur.append((v, r[hdr["Source"]], r[hdr["Instructions Executed"]]))
+        if n == 0:
+            continue
+        key = (fname, int(r[0]))
+        ent = agg.setdefault(key, [0, r[1], collections.Counter()])
+        ent[0] += n
+        for i, h in enumerate(hdr):
+            if h.startswith("stall_") and "Not Issued" not in h and i < len(r) and r[i].isdigit():
+                ent[2][h[6:]] += int(r[i])
+    tot = sum(e[0] for e in agg.values()) or 1
     out = []
-    for k in res:
-        tot = sum(v for v, _, _ in k) or 1.0
-        out.append([(100 * v / tot, s, e) for v, s, e in sorted(k, key=lambda x: -x[0])[:top]])
+    for (f, ln), (n, src, reasons) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+        out.append((100.0 * n / tot, "%s:%d" % (f, ln), " ".join(src.split())[:96],
+                    ", ".join("%s=%d" % (k, v) for k, v in reasons.most_common(2))))
     return out
 
 
@@ -89,7 +109,7 @@ def main():
     for rep in reps:
         tag = os.path.basename(rep)[:-8]
         summ = raw_summary(rep)
-        st = stalls(rep)
+        st_cache = {}
         with open(os.path.join(OUT, tag + ".md"), "w") as f:
             f.write("# ncu --set full summary: %s\n\n(captured with `--clock-control none --import-source on` on a B200; "
                     "durations under ncu are cold-cache and serialised — compare shares, not absolutes)\n\n" % tag)
@@ -98,11 +118,17 @@ def main():
                 for k in WANT:
                     if k in d:
                         f.write("| %s | %s |\n" % (k, d[k]))
-                if i < len(st):
-                    f.write("\nTop warp-stall samples (share of all samples, SASS, executions):\n\n```\n")
-                    for share, src, ex in st[i]:
-                        f.write("%5.1f%%  x%-8s %s\n" % (share, ex, src[:110]))
-                    f.write("```\n\n")
+                bn = base_name(d["kernel"])
+                if bn not in st_cache:
+                    st_cache[bn] = stalls_by_source_line(rep, bn)
+                    if st_cache[bn]:
+                        f.write("\nWarp-stall samples per CUDA source line (share of the kernel's samples; top two stall reasons; "
+                                "all launches of this kernel in the report):\n\n```\n")
+                        for share, loc, src, why in st_cache[bn]:
+                            f.write("%5.1f%%  %-18s %-96s [%s]\n" % (share, loc, src, why))
+                        f.write("```\n\n")
+                else:
+                    f.write("\n(stall samples: see the first launch of this kernel above)\n\n")
     hist, full = sass_evidence()
     keys = ["UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "UTCBAR", "SYNCS", "REDG", "ATOMG", "ATOMS", "RED",
             "HMMA", "LDGSTS", "LDG", "STG", "MUFU"]

@@ -18,6 +18,7 @@
 // warp that never waits, so this cannot deadlock). No deletion, no rehash: capacity is fixed,
 // which is also what makes caching (shard, slot) on the worker legal.
 #include <cuda_bf16.h>
+#include <cstdlib>
 #include "common.cuh"
 
 namespace ssb {
@@ -180,102 +181,136 @@ __device__ __forceinline__ void pull_emit(const SsbTableView& v, uint32_t key, b
   }
 }
 
-__global__ void __launch_bounds__(256)
-pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ keys, int64_t n,
-            const uint32_t* __restrict__ n_dev, uint32_t* __restrict__ gslot_out,
-            float* __restrict__ rows_out, __nv_bfloat16* __restrict__ rows_bf16, float* __restrict__ grads_zero,
-            int insert, uint32_t* __restrict__ stats, unsigned long long* __restrict__ slot_cache, int cache_bits) {
-  const int lane = threadIdx.x & 31;
-  const uint32_t ne = effective_n(n, n_dev);
-  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+struct PullArgs {
+  uint32_t ne;
+  uint32_t* gslot_out;
+  float* rows_out;
+  __nv_bfloat16* rows_bf16;
+  float* grads_zero;
+  int insert;
+  uint32_t* stats;
+  unsigned long long* slot_cache;
+  int cache_bits;       // negative: dense key space, entry index = key & mask (no two keys share an entry)
+};
+
+__device__ __forceinline__ uint32_t cache_index(uint32_t key, int cache_bits) {
+  return cache_bits < 0 ? (key & ((1u << -cache_bits) - 1u)) : slot_cache_index(key, cache_bits);
+}
+
+// One group of kPullK keys [w0, w0 + kPullK): cslot[k] = global slot from the worker's slot cache or
+// SSB_INVALID_SLOT. All of key / cslot are warp-uniform.
+__device__ __forceinline__ void pull_group(const SsbTableView& v, const PullArgs& a, uint32_t w0, const uint32_t (&key)[kPullK],
+                                           const uint32_t (&cslot)[kPullK], int lane) {
   const int D = v.dim;
-  const bool want = rows_out || rows_bf16;
+  const bool want = a.rows_out || a.rows_bf16;
   const bool fast_rows = want && (D & 3) == 0;
-  const bool from_shadow = !rows_out && rows_bf16 && v.shadow[0] != nullptr && (D & 3) == 0;
+  const bool from_shadow = !a.rows_out && a.rows_bf16 && v.shadow[0] != nullptr && (D & 3) == 0;
   const uint32_t nb = v.capacity / SSB_BUCKET;
-  for (uint32_t w0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * kPullK; w0 < ne; w0 += warps * kPullK) {
-    uint32_t key[kPullK], kv[kPullK], bucket[kPullK], cslot[kPullK];
-    int owner[kPullK];
-    bool valid[kPullK];
-    // phase 0: the worker's own key -> (shard, slot) cache (local memory). A hit replaces the probe of
-    // the owner's key bucket — a dependent round trip over NVLink when the owner is a peer — by one
-    // 8-byte local load. Slots never move and are cached only once published, so an entry stays true.
+  uint32_t kv[kPullK], bucket[kPullK];   // bucket[k] holds the SLOT (within the owner) for cache hits
+  int owner[kPullK];
+  bool valid[kPullK];
+  unsigned cached = 0;                   // bit k: key k was resolved by the slot cache
+  // phase 1: independent first-bucket probes for the keys the cache did not resolve
 #pragma unroll
-    for (int k = 0; k < kPullK; ++k) {
-      const uint32_t w = w0 + k;
-      key[k] = (w < ne) ? __ldg(keys + w) : SSB_EMPTY_KEY;
-      valid[k] = key[k] < SSB_LOCKED_KEY;
-      cslot[k] = SSB_INVALID_SLOT;
+  for (int k = 0; k < kPullK; ++k) {
+    valid[k] = key[k] < SSB_LOCKED_KEY && w0 + k < a.ne;
+    kv[k] = SSB_EMPTY_KEY;
+    if (valid[k] && cslot[k] != SSB_INVALID_SLOT) {
+      cached |= 1u << k;
+      owner[k] = (int)(cslot[k] / v.capacity);
+      bucket[k] = cslot[k] - (uint32_t)owner[k] * v.capacity;
+      continue;
     }
-    if (slot_cache) {
-      // lane 0 reads, the warp shares: every lane must act on the same snapshot of an entry that
-      // another warp (a different key with the same index) may overwrite at any time
-      uint32_t ck[kPullK], cs[kPullK];
+    owner[k] = valid[k] ? owner_of(key[k], v.frag_map, v.frag_num) : 0;
+    if (owner[k] < 0 || owner[k] >= v.num_shards) { owner[k] = 0; valid[k] = valid[k] && false; }
+    bucket[k] = reduce_range(slot_hash(key[k]), nb);
+    if (valid[k]) kv[k] = ld_relaxed_sys(v.keys[owner[k]] + (size_t)bucket[k] * SSB_BUCKET + lane);
+  }
+  // phase 2: resolve hits, issue their row reads together
+  Probe p[kPullK];
+  float4 pre[kPullK];
 #pragma unroll
-      for (int k = 0; k < kPullK; ++k) {
-        unsigned long long ce = ~0ull;
-        if (lane == 0 && valid[k]) ce = *((const volatile unsigned long long*)(slot_cache + slot_cache_index(key[k], cache_bits)));
-        ck[k] = (uint32_t)(ce >> 32);
-        cs[k] = (uint32_t)ce;
-      }
-      const uint32_t total_slots = v.capacity * (uint32_t)v.num_shards;
+  for (int k = 0; k < kPullK; ++k) pre[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+  bool fast[kPullK];
 #pragma unroll
-      for (int k = 0; k < kPullK; ++k) {
-        ck[k] = __shfl_sync(0xffffffffu, ck[k], 0);
-        cs[k] = __shfl_sync(0xffffffffu, cs[k], 0);
-        if (valid[k] && ck[k] == key[k] && cs[k] < total_slots) cslot[k] = cs[k];
-      }
-    }
-    // phase 1: independent first-bucket probes for the keys the cache did not resolve
-#pragma unroll
-    for (int k = 0; k < kPullK; ++k) {
-      if (cslot[k] != SSB_INVALID_SLOT) {
-        owner[k] = (int)(cslot[k] / v.capacity);
-        bucket[k] = 0;
-        kv[k] = SSB_EMPTY_KEY;
-        continue;
-      }
-      owner[k] = valid[k] ? owner_of(key[k], v.frag_map, v.frag_num) : 0;
-      if (owner[k] < 0 || owner[k] >= v.num_shards) { owner[k] = 0; valid[k] = valid[k] && false; }
-      bucket[k] = reduce_range(slot_hash(key[k]), nb);
-      kv[k] = valid[k] ? ld_relaxed_sys(v.keys[owner[k]] + (size_t)bucket[k] * SSB_BUCKET + lane) : SSB_EMPTY_KEY;
-    }
-    // phase 2: resolve hits, issue their row reads together
-    Probe p[kPullK];
-    float4 pre[kPullK];
-#pragma unroll
-    for (int k = 0; k < kPullK; ++k) pre[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-    bool fast[kPullK];
-#pragma unroll
-    for (int k = 0; k < kPullK; ++k) {
-      p[k].owner = owner[k]; p[k].slot = SSB_INVALID_SLOT; p[k].is_new = false;
-      const bool cached = cslot[k] != SSB_INVALID_SLOT;     // warp-uniform
-      unsigned m = __ballot_sync(0xffffffffu, valid[k] && kv[k] == key[k]);
-      fast[k] = cached || m != 0;
-      if (fast[k]) {
-        p[k].slot = cached ? cslot[k] - (uint32_t)owner[k] * v.capacity : bucket[k] * SSB_BUCKET + (__ffs(m) - 1);
-        if (from_shadow) {
-          if (lane * 4 < D) {
-            uint2 pk = ld_shadow_u2(reinterpret_cast<const __nv_bfloat16*>(v.shadow[owner[k]]) + (size_t)p[k].slot * D + lane * 4);
-            pre[k].x = __uint_as_float(pk.x); pre[k].y = __uint_as_float(pk.y);
-          }
-        } else if (fast_rows && lane * 4 < D) {
-          pre[k] = ld_row_f4(v.rows[owner[k]] + (size_t)p[k].slot * D + lane * 4);
+  for (int k = 0; k < kPullK; ++k) {
+    p[k].owner = owner[k]; p[k].slot = SSB_INVALID_SLOT; p[k].is_new = false;
+    const bool hit = (cached >> k) & 1u;
+    unsigned m = __ballot_sync(0xffffffffu, valid[k] && kv[k] == key[k]);
+    fast[k] = hit || m != 0;
+    if (fast[k]) {
+      p[k].slot = hit ? bucket[k] : bucket[k] * SSB_BUCKET + (__ffs(m) - 1);
+      if (from_shadow) {
+        if (lane * 4 < D) {
+          uint2 pk = ld_shadow_u2(reinterpret_cast<const __nv_bfloat16*>(v.shadow[owner[k]]) + (size_t)p[k].slot * D + lane * 4);
+          pre[k].x = __uint_as_float(pk.x); pre[k].y = __uint_as_float(pk.y);
         }
+      } else if (fast_rows && lane * 4 < D) {
+        pre[k] = ld_row_f4(v.rows[owner[k]] + (size_t)p[k].slot * D + lane * 4);
       }
     }
-    // phase 3: slow path for the rest (miss in first bucket, locked slot, insert), then emit
+  }
+  // phase 3: slow path for the rest (miss in first bucket, locked slot, insert), then emit
 #pragma unroll
-    for (int k = 0; k < kPullK; ++k) {
-      const uint32_t w = w0 + k;
-      if (w >= ne) break;
-      if (!fast[k] && valid[k]) p[k] = probe_insert(v, key[k], insert != 0, lane);
-      pull_emit(v, key[k], valid[k], p[k], w, lane, rows_out, rows_bf16, grads_zero, gslot_out, stats,
-                fast[k] && fast_rows, pre[k]);
-      // remember the slot (after pull_emit: a row this warp created has been published by now)
-      if (slot_cache && lane == 0 && valid[k] && cslot[k] == SSB_INVALID_SLOT && p[k].slot != SSB_INVALID_SLOT)
-        slot_cache[slot_cache_index(key[k], cache_bits)] =
-            ((unsigned long long)key[k] << 32) | ((uint32_t)p[k].owner * v.capacity + p[k].slot);
+  for (int k = 0; k < kPullK; ++k) {
+    const uint32_t w = w0 + k;
+    if (w >= a.ne) break;
+    if (!fast[k] && valid[k]) p[k] = probe_insert(v, key[k], a.insert != 0, lane);
+    pull_emit(v, key[k], valid[k], p[k], w, lane, a.rows_out, a.rows_bf16, a.grads_zero, a.gslot_out, a.stats,
+              fast[k] && fast_rows, pre[k]);
+    // remember the slot (after pull_emit: a row this warp created has been published by now)
+    if (a.slot_cache && lane == 0 && valid[k] && !((cached >> k) & 1u) && p[k].slot != SSB_INVALID_SLOT)
+      a.slot_cache[cache_index(key[k], a.cache_bits)] =
+          ((unsigned long long)key[k] << 32) | ((uint32_t)p[k].owner * v.capacity + p[k].slot);
+  }
+}
+
+// kCached = false: every key probes its owner's bucket (K probes, then K row reads, in flight together).
+// kCached = true: a warp takes 32 keys at a time; each LANE looks one key up in the worker's own
+// key -> (shard, slot) cache (local memory, one dependent access per 32 keys instead of one per key),
+// then the warp walks the 32 keys in groups of K: hits go straight to their row reads — for a remote
+// owner ONE NVLink round trip per key instead of two — misses take the probing path and are remembered.
+// Slots never move and are cached only once published, so an entry stays true.
+template <bool kCached>
+__global__ void __launch_bounds__(256, 4)
+pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ keys, int64_t n,
+            const uint32_t* __restrict__ n_dev, const PullArgs args) {
+  const int lane = threadIdx.x & 31;
+  PullArgs a = args;
+  a.ne = effective_n(n, n_dev);
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const uint32_t warp_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (!kCached) {
+    a.slot_cache = nullptr;
+    for (uint32_t w0 = warp_id * kPullK; w0 < a.ne; w0 += warps * kPullK) {
+      uint32_t key[kPullK], cslot[kPullK];
+#pragma unroll
+      for (int k = 0; k < kPullK; ++k) {
+        key[k] = (w0 + k < a.ne) ? __ldg(keys + w0 + k) : SSB_EMPTY_KEY;
+        cslot[k] = SSB_INVALID_SLOT;
+      }
+      pull_group(v, a, w0, key, cslot, lane);
+    }
+  } else {
+    const uint32_t total_slots = v.capacity * (uint32_t)v.num_shards;
+    for (uint32_t c0 = warp_id * 32; c0 < a.ne; c0 += warps * 32) {
+      const uint32_t my_key = (c0 + lane < a.ne) ? __ldg(keys + c0 + lane) : SSB_EMPTY_KEY;
+      uint32_t my_slot = SSB_INVALID_SLOT;
+      if (my_key < SSB_LOCKED_KEY) {
+        const unsigned long long ce = *((const volatile unsigned long long*)(a.slot_cache + cache_index(my_key, a.cache_bits)));
+        if ((uint32_t)(ce >> 32) == my_key && (uint32_t)ce < total_slots) my_slot = (uint32_t)ce;
+      }
+#pragma unroll 1
+      for (int g = 0; g < 32; g += kPullK) {
+        if (c0 + g >= a.ne) break;
+        uint32_t key[kPullK], cslot[kPullK];
+#pragma unroll
+        for (int k = 0; k < kPullK; ++k) {
+          key[k] = __shfl_sync(0xffffffffu, my_key, g + k);
+          cslot[k] = __shfl_sync(0xffffffffu, my_slot, g + k);
+        }
+        pull_group(v, a, c0 + g, key, cslot, lane);
+      }
     }
   }
 }
@@ -609,11 +644,14 @@ int ssb_pull_cached(const SsbTableView* view, const uint32_t* keys, int64_t n, c
                     uint32_t* gslot, float* rows_out, void* rows_bf16, float* grads_zero, int insert,
                     uint32_t* stats, uint64_t* slot_cache, int32_t cache_bits, void* stream) {
   if (int e = check_view(view)) return e;
-  if (slot_cache && (cache_bits < 4 || cache_bits > 31)) return (int)cudaErrorInvalidValue;
+  if (slot_cache && ((cache_bits < 0 ? -cache_bits : cache_bits) < 4 || (cache_bits < 0 ? -cache_bits : cache_bits) > 31))
+    return (int)cudaErrorInvalidValue;
   if (n <= 0) return 0;
-  ssb::pull_kernel<<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, keys, n, n_dev, gslot, rows_out,
-                                                                  (__nv_bfloat16*)rows_bf16, grads_zero, insert, stats,
-                                                                  (unsigned long long*)slot_cache, cache_bits);
+  ssb::PullArgs a{0u, gslot, rows_out, (__nv_bfloat16*)rows_bf16, grads_zero, insert, stats, (unsigned long long*)slot_cache, cache_bits};
+  if (slot_cache)
+    ssb::pull_kernel<true><<<ssb::grid_for(n, 32, ssb::kNumSMs * 8), 256, 0, (cudaStream_t)stream>>>(*view, keys, n, n_dev, a);
+  else
+    ssb::pull_kernel<false><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, keys, n, n_dev, a);
   SSB_LAUNCH_CHECK();
   return 0;
 }

@@ -95,7 +95,7 @@ class ShardedTable:
         # bf16 mirrors of all shards lie in ONE virtual range (used by the fused-pull tensor-core kernel)
         self.mirror_map = None
         # worker-side key -> slot cache (enable_slot_cache): None = every pull probes the owner's key bucket
-        self.slot_cache, self.slot_cache_bits = None, 0
+        self.slot_cache, self.slot_cache_bits, self.slot_cache_dense = None, 0, False
         if self.has_shadow and self.num_shards == 1 and self.dim == 128:
             self.mirror_map = (shard_ptrs[0][3], self.capacity, 0, 0)
 
@@ -121,18 +121,24 @@ class ShardedTable:
             rows_out = torch.empty((n, self.dim), dtype=torch.float32, device=keys.device)
         _lib.call("ssb_pull_cached", self._view_ref(), keys.data_ptr(), n, _lib.ptr(n_dev), gslot_out.data_ptr(),
                   _lib.ptr(rows_out), _lib.ptr(rows_bf16), _lib.ptr(grads_zero), 1 if insert else 0,
-                  self.stats.data_ptr(), _lib.ptr(self.slot_cache), self.slot_cache_bits, _lib.stream_ptr())
+                  self.stats.data_ptr(), _lib.ptr(self.slot_cache), self._cache_bits_arg(), _lib.stream_ptr())
         return rows_out, gslot_out
 
-    def enable_slot_cache(self, expected_keys, max_bits=26):
-        """Give this worker a direct-mapped key -> (shard, slot) cache of >= 2x ``expected_keys`` entries
-        (8 bytes each, own device memory). Keys it has pulled before then skip the probe of the owner's
-        key bucket — for a remote owner that is one of the two dependent NVLink round trips of a pull.
-        Slots never move and are never freed (table.cu header), so entries cannot go stale."""
-        bits = max(10, min(int(max_bits), (2 * max(int(expected_keys), 1) - 1).bit_length()))
-        if self.slot_cache is None or self.slot_cache_bits != bits:
+    def _cache_bits_arg(self):
+        return -self.slot_cache_bits if self.slot_cache_dense else self.slot_cache_bits
+
+    def enable_slot_cache(self, expected_keys, max_bits=26, dense=False):
+        """Give this worker a direct-mapped key -> (shard, slot) cache (8-byte entries, own device memory).
+        Keys it has pulled before then skip the probe of the owner's key bucket — for a remote owner one
+        of the two dependent NVLink round trips of a pull. ``dense=True``: the keys are small integers
+        ``< expected_keys`` (word ids), the entry index is the key itself and no two keys share an entry;
+        otherwise >= 2x ``expected_keys`` entries indexed by a multiplicative hash (keys that collide
+        evict each other). Slots never move and are never freed (table.cu header), so entries cannot go stale."""
+        want = max(int(expected_keys), 1) if dense else 2 * max(int(expected_keys), 1)
+        bits = max(10, min(int(max_bits), (want - 1).bit_length()))
+        if self.slot_cache is None or self.slot_cache_bits != bits or self.slot_cache_dense != bool(dense):
             self.slot_cache = torch.full((1 << bits,), -1, dtype=torch.int64, device=self.device)
-            self.slot_cache_bits = bits
+            self.slot_cache_bits, self.slot_cache_dense = bits, bool(dense)
         return self.slot_cache
 
     def resolve(self, keys, insert=True):
@@ -140,7 +146,7 @@ class ShardedTable:
         n = keys.numel()
         gslot = torch.empty(n, dtype=torch.int32, device=keys.device)
         _lib.call("ssb_pull_cached", self._view_ref(), keys.data_ptr(), n, None, gslot.data_ptr(), None, None, None,
-                  1 if insert else 0, self.stats.data_ptr(), _lib.ptr(self.slot_cache), self.slot_cache_bits,
+                  1 if insert else 0, self.stats.data_ptr(), _lib.ptr(self.slot_cache), self._cache_bits_arg(),
                   _lib.stream_ptr())
         return gslot
 

@@ -92,7 +92,7 @@ def main():
     assert torch.allclose(rows_c2, final - 0.125 * world, rtol=1e-6, atol=1e-6), "cached pull missed remote updates"
     w = w - 0.125 * world                       # keep the oracle of the next sections in step
     final = rows_c2
-    table.slot_cache, table.slot_cache_bits = None, 0
+    table.slot_cache, table.slot_cache_bits, table.slot_cache_dense = None, 0, False
     out["slot_cache_ok"] = True
 
     # ---- 2b. inbox push (one-way shipment, owner applies): same AdaGrad result as the oracle

@@ -112,9 +112,9 @@ def test_pull_slot_cache_matches_uncached(device, num_shards):
     keys = np.unique(_keys(5000, seed=21))
     kd = _dev(keys, device)
     rows0, gslot0 = plain.pull(kd)
-    for expected in (len(keys), 64):                       # roomy cache / thrashing cache (1024 entries min)
+    for expected, dense in ((len(keys), False), (64, False), (64, True)):   # roomy / thrashing (1024 entries) / key & mask index
         t = ShardedTable.local(16384, dim, device, num_shards=num_shards, frag_num=64, seed=7, init_scale=0.5)
-        cache = t.enable_slot_cache(expected)
+        cache = t.enable_slot_cache(expected, dense=dense)
         assert cache.numel() == 1 << t.slot_cache_bits and bool((cache == -1).all())
         for rep in range(3):                               # fill, then hit
             rows, gslot = t.pull(kd)
@@ -125,7 +125,7 @@ def test_pull_slot_cache_matches_uncached(device, num_shards):
             assert np.array_equal(g // t.capacity, t.hashfrag.to_shard(keys))
         filled = int((cache != -1).sum().item())
         assert filled > 0 and filled <= len(keys)
-        if expected == len(keys):
+        if expected == len(keys) and not dense:
             assert filled > 0.7 * len(keys)                 # direct-mapped: a few keys share an index
         ck = (cache[cache != -1] >> 32).cpu().numpy().astype(np.uint32)
         assert np.isin(ck, keys).all()
@@ -150,6 +150,30 @@ def test_pull_slot_cache_matches_uncached(device, num_shards):
         assert np.all(to_u32_numpy(ga2) == 0xFFFFFFFF)
         # resolve() shares the cache
         assert torch.equal(t.resolve(kd), gslot)
+
+
+def test_pull_slot_cache_dense_ids(device):
+    """Dense word ids with the identity index: every key gets its own entry, second pull is all hits."""
+    from swiftsnails_b200.ops.table import ShardedTable
+
+    t = ShardedTable.local(16384, 128, device, num_shards=2, frag_num=64, seed=3, init_scale=0.5, with_shadow=True)
+    ids = np.random.default_rng(1).permutation(6000).astype(np.uint32)
+    cache = t.enable_slot_cache(6000, dense=True)
+    rows_a, gslot_a = t.pull(_dev(ids, device))
+    assert int((cache != -1).sum().item()) == 6000
+    inserts = int(t.stats[0].item())
+    out16 = torch.empty(6000, 128, dtype=torch.bfloat16, device=device)
+    gz = torch.ones(6000, 128, device=device)
+    rows_b, gslot_b = t.pull(_dev(ids, device), rows_bf16=out16, grads_zero=gz)      # fp32 + bf16 + grad reset, all from cache hits
+    assert torch.equal(rows_a, rows_b) and torch.equal(gslot_a, gslot_b) and int(t.stats[0].item()) == inserts
+    assert torch.equal(out16, rows_a.to(torch.bfloat16)) and float(gz.abs().max()) == 0.0
+    out16b = torch.zeros_like(out16)
+    t.pull(_dev(ids, device), rows_bf16=out16b, want_fp32=False)                      # bf16-only: served from the bf16 mirror
+    assert torch.equal(out16b, out16)
+    # odd sizes: n not a multiple of 32 or of the group size
+    for n in (1, 3, 31, 33, 4097):
+        r, g = t.pull(_dev(ids[:n], device))
+        assert torch.equal(r, rows_a[:n]) and torch.equal(g, gslot_a[:n])
 
 
 def test_pull_duplicate_keys_same_batch(device):
