@@ -140,7 +140,17 @@ def main():
             h = hist[k]
             cnt = [sum(v for m, v in h.items() if m.split(".")[0] == key or m.startswith(key + ".")) for key in keys]
             f.write("| `%s` | %s | %d |\n" % (k[:70], " | ".join(str(c) if c else "" for c in cnt), sum(h.values())))
-    for k, lines in full.items():
+    # one SASS listing per kernel (cuobjdump text, encodings already stripped by the regex above)
+    sass_dir = os.path.join(OUT, "sass")
+    os.makedirs(sass_dir, exist_ok=True)
+    for old in os.listdir(sass_dir):
+        os.remove(os.path.join(sass_dir, old))
+    dem = subprocess.run(["cu++filt"] + list(full), capture_output=True, text=True).stdout.splitlines()
+    for (k, lines), d in zip(full.items(), dem if len(dem) == len(full) else list(full)):
+        name = re.sub(r"\(.*", "", re.sub(r"\((bool|int|unsigned int)\)", "", d)).replace("void ", "").replace("ssb::", "").replace("::", "_")
+        name = re.sub(r"[<>, ]+", "_", name).strip("_")
+        with open(os.path.join(sass_dir, name + ".sass"), "w") as f:
+            f.write("\t\tFunction : %s\n" % k + "\n".join(lines) + "\n")
         if "sgns_block_tc" in k:
             with open(os.path.join(OUT, "sgns_block_tc_kernel.sass"), "w") as f:
                 f.write("\n".join(lines) + "\n")

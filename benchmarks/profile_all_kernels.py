@@ -29,7 +29,13 @@ uniq, inv, nu = ded(keys)                                                       
 rows, gslot = t.pull(uniq, n_dev=nu)                                                # pull_kernel (inserts)
 rows, gslot = t.pull(uniq, n_dev=nu)                                                # pull_kernel (hits)
 t.gather_slots(gslot, n_dev=nu)                                                     # gather_slots_kernel
+t.enable_slot_cache(N)
+t.pull(uniq, n_dev=nu)                                                              # pull_kernel<cached> (fills the slot cache)
+t.pull(uniq, n_dev=nu)                                                              # pull_kernel<cached> (all hits)
+t.slot_cache, t.slot_cache_bits, t.slot_cache_dense = None, 0, False
 g = torch.randn(N, D, device=dev)
+_lib.call("ssb_push_bf16", t._view_ref(), gslot.data_ptr(), g.to(torch.bfloat16).data_ptr(), N, nu.data_ptr(), 0.01, 1e-8, 1,
+          _lib.stream_ptr())                                                         # push_bf16_kernel<AdaGrad> (inbox apply)
 t.push_sgd(gslot, g, 0.01, n_dev=nu, zero_grads=False)                              # push_kernel<SGD>
 t.push_adagrad(gslot, g, 0.01, n_dev=nu, zero_grads=False)                          # push_kernel<AdaGrad>
 smp.sample(N)                                                                       # neg_sample_kernel
