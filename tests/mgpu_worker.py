@@ -181,7 +181,15 @@ def main():
         curve = []
         for s in range(12):
             wc.reset_loss()
-            wc.step(u32_tensor(base[s * cfg_c.tokens_per_step:(s + 1) * cfg_c.tokens_per_step], dev))
+            sb = wc.sets[0]
+            sb.step_idx = wc.step_idx
+            # phase by phase with a barrier in between, so no rank pulls while another one pushes: what a
+            # pull sees is then the same in both runs (only the order of concurrent pushes differs)
+            wc._comm(sb, u32_tensor(base[s * cfg_c.tokens_per_step:(s + 1) * cfg_c.tokens_per_step], dev))
+            torch.cuda.synchronize(); dist.barrier()
+            wc._compute(sb)
+            wc._push(sb)
+            wc.step_idx += 1
             curve.append(wc.mean_loss())
             torch.cuda.synchronize(); dist.barrier()
         curves.append(curve)
