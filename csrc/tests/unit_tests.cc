@@ -1,8 +1,9 @@
 // unit_tests.cc — C++ unit tests of the host core (run by tests/test_host_core.py).
 // Mirrors the reference's test pyramid (ref: /root/reference/src/unitest/*):
 // buffer, string, queue, hashmap, rwlock, barrier, config, file, vec, message, channel,
-// async exec, sparse table, access methods, hashfrag, route and the self-loopback transfer
-// test over real TCP — but every case asserts (the reference's mostly log).
+// async exec, sparse table, access methods, hashfrag, shell, route and the self-loopback transfer
+// test over real TCP — but every case asserts (the reference's mostly log) — plus regressions
+// for the route hand-out race (late node, reply to a requester the route does not know yet).
 #include <fstream>
 #include <set>
 #include "../core/swiftsnails.h"
@@ -311,6 +312,52 @@ TEST(transfer_self_loopback) {  // ref: core/transfer/transfer_test.h:13-80 — 
   EXPECT(done.block(10000));   // explicit completion instead of the reference's sleep(1 s)
   EXPECT(ok.load() == 50 && t.pending_responses() == 0);
   t.shutdown();
+}
+
+TEST(shell) {  // ref: utils/shell_test.h:7-18 (runs a command, reads its output, checks the status)
+  EXPECT(GlobalShell::get_command_output("printf 'a\\nb\\n' | wc -l").find("2") != std::string::npos);
+  EXPECT(GlobalShell::execute("true") == 0);
+  EXPECT(GlobalShell::execute("false | cat") != 0);   // pipefail, as in the reference
+}
+
+TEST(route_waits_for_late_node) {
+  // lookups of an id that is not registered yet wait (bounded) instead of aborting
+  ServerWorkerRoute r;
+  r.set_unknown_node_wait_ms(2000);
+  EXPECT(!r.wait_for_node(5, 20));
+  std::thread late([&] { std::this_thread::sleep_for(std::chrono::milliseconds(60)); r.register_node(5, "tcp://127.0.0.1:16005"); });
+  Timer t;
+  EXPECT(r.address(5) == "tcp://127.0.0.1:16005");
+  late.join();
+  EXPECT(r.has_node(5));
+}
+
+TEST(transfer_reply_to_not_yet_routed_requester) {
+  // Regression for the start-up race: the master hands the route out node by node, so a server can
+  // get a request from a worker that is not in its route yet. The reply must be held back until the
+  // route knows the requester (here: 80 ms later) instead of aborting the server.
+  Transfer<ServerWorkerRoute> server, worker;
+  for (auto* t : {&server, &worker}) { t->listen(); t->init_async_channel(2); t->set_thread_num(1); t->service_start(); }
+  server.set_client_id(1);
+  worker.set_client_id(77);
+  worker.route().register_node(1, server.recv_addr());
+  server.message_class().add(1, [](std::shared_ptr<Request> req, Request& rsp) { int32_t a; req->cont >> a; rsp.cont << (int32_t)(a * 2); });
+  CounterBarrier done(8);
+  std::atomic<int> ok{0};
+  for (int i = 0; i < 8; ++i) {   // more requests than handler threads: deferred replies must not starve the pool
+    Request req;
+    req.meta.message_class = 1;
+    req.cont << (int32_t)(21 + i);
+    req.call_back_handler = [&, i](std::shared_ptr<Request> rsp) { int32_t v; rsp->cont >> v; if (v == 2 * (21 + i)) ++ok; done.count_down(); };
+    worker.send(std::move(req), 1);
+  }
+  std::this_thread::sleep_for(std::chrono::milliseconds(80));
+  EXPECT(ok.load() == 0);                                   // nothing can have been answered yet
+  server.route().register_node(77, worker.recv_addr());     // "the route arrives"
+  EXPECT(done.block(10000));
+  EXPECT(ok.load() == 8);
+  worker.shutdown();
+  server.shutdown();
 }
 
 int main(int argc, char** argv) {
