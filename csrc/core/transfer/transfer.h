@@ -147,25 +147,27 @@ class Transfer : public Listener {
       LOG(ERROR) << "no handler for message class " << request->meta.message_class << " (dropped)";
       return;
     }
-    async_channel_->push([this, handler, request] {
+    // pool threads get the channel as a raw pointer: the member is reset by shutdown() on another
+    // thread, and the channel outlives its own worker threads (its destructor joins them)
+    AsynExec::channel_t* ch = async_channel_.get();
+    ch->push([this, ch, handler, request] {
       auto response = std::make_shared<Request>();
       handler(request, *response);
       response->meta.message_class = -1;
       response->meta.message_id = request->meta.message_id;
       response->meta.client_id = request->meta.client_id;
       // an empty response defers the reply (ref: transfer.h:173-177)
-      if (response->cont.size() > 0) deliver_response(response, request->meta.client_id, 0);
+      if (response->cont.size() > 0) deliver_response(ch, response, request->meta.client_id, 0);
     });
   }
   // The requester may not be in this node's route yet: the master hands the route table out node by
   // node, so a worker that already has it can reach a server whose copy is still queued behind this
   // very request. Blocking here could starve that route message of a pool thread, so the reply is
   // re-queued (1 ms apart, ~30 s at most) until the route knows the requester.
-  void deliver_response(std::shared_ptr<Request> response, int to_id, int attempt) {
-    if (!route_->has_node(to_id) && attempt < 30000 && async_channel_) {
+  void deliver_response(AsynExec::channel_t* ch, std::shared_ptr<Request> response, int to_id, int attempt) {
+    if (!route_->has_node(to_id) && attempt < 30000) {
       std::this_thread::sleep_for(std::chrono::milliseconds(1));
-      async_channel_->push([this, response, to_id, attempt] { deliver_response(response, to_id, attempt + 1); });
-      return;
+      if (ch->push([this, ch, response, to_id, attempt] { deliver_response(ch, response, to_id, attempt + 1); })) return;
     }
     send_response(std::move(*response), to_id);
   }
