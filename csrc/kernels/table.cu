@@ -315,6 +315,151 @@ pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
   }
 }
 
+// ---- pull, bulk-copy form (opt-in: SSB200_PULL_BULK=1) -----------------------------------------
+// The kernel above keeps every row it is waiting for in registers (a float4 per lane per key), and its
+// per-key state caps a warp at kPullK = 4 rows in flight: 128 rows per SM at 64 registers, which is what
+// bounds it (its time scales with 1 / resident warps: 3.7 TB/s of 6.5). Here a LANE resolves one key
+// (slot cache, else one pass over the key's first bucket with four 16-byte loads ... eight in total) and
+// starts ONE bulk copy (cp.async.bulk, the TMA engine's 1-D form) of its row into the warp's slice of
+// shared memory; the 32 copies of a warp complete on the warp's mbarrier. No register is held while a
+// row is in flight: 32 rows per warp, 384 per SM. Keys the fast path cannot resolve (not in the first
+// bucket, locked, to be inserted, illegal) go through probe_insert / pull_emit exactly as above while
+// the copies fly. Rows must be 16-byte multiples of at most 512 bytes (D % 4 == 0, D <= 128).
+constexpr int kBulkWarps = 4;
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bulk_mbar_init(unsigned long long* bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(bar)) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_mbar_expect(unsigned long long* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_mbar_wait(unsigned long long* bar, uint32_t parity) {   // bounded: traps instead of hanging
+  uint32_t done = 0;
+  for (uint32_t it = 0; it < (1u << 26); ++it) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(smem_addr(bar)), "r"(parity) : "memory");
+    if (done) return;
+  }
+  __trap();
+}
+__device__ __forceinline__ void bulk_copy_g2s(void* dst_smem, const void* src, uint32_t bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_addr(dst_smem)), "l"(src), "r"(bytes), "r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ uint4 ld_relaxed_sys_v4(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+
+template <bool kCached>
+__global__ void __launch_bounds__(kBulkWarps * 32)
+pull_bulk_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ keys, int64_t n,
+                 const uint32_t* __restrict__ n_dev, const PullArgs args) {
+  extern __shared__ __align__(128) uint8_t bulk_smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  PullArgs a = args;
+  a.ne = effective_n(n, n_dev);
+  if (!kCached) a.slot_cache = nullptr;
+  const int D = v.dim;
+  const bool from_shadow = !a.rows_out && a.rows_bf16 && v.shadow[0] != nullptr;
+  const uint32_t row_bytes = (uint32_t)D * (from_shadow ? 2u : 4u);
+  uint8_t* my_rows = bulk_smem + (size_t)warp * 32 * row_bytes;
+  unsigned long long* bar = reinterpret_cast<unsigned long long*>(bulk_smem + (size_t)kBulkWarps * 32 * row_bytes) + warp;
+  if (lane == 0) bulk_mbar_init(bar);
+  __syncwarp();
+  uint32_t phase = 0;
+  const uint32_t nb = v.capacity / SSB_BUCKET;
+  const uint32_t total_slots = v.capacity * (uint32_t)v.num_shards;
+  const uint32_t warps = gridDim.x * kBulkWarps;
+  for (uint32_t c0 = (blockIdx.x * kBulkWarps + warp) * 32; c0 < a.ne; c0 += warps * 32) {
+    const uint32_t w = c0 + lane;
+    const uint32_t key = (w < a.ne) ? __ldg(keys + w) : SSB_EMPTY_KEY;
+    uint32_t gs = SSB_INVALID_SLOT;                 // global slot of MY key once the fast path has it
+    if (key < SSB_LOCKED_KEY) {
+      if (kCached) {
+        const unsigned long long ce = *((const volatile unsigned long long*)(a.slot_cache + cache_index(key, a.cache_bits)));
+        if ((uint32_t)(ce >> 32) == key && (uint32_t)ce < total_slots) gs = (uint32_t)ce;
+      }
+      if (gs == SSB_INVALID_SLOT) {
+        const int o = owner_of(key, v.frag_map, v.frag_num);
+        if (o >= 0 && o < v.num_shards) {
+          const uint32_t b = reduce_range(slot_hash(key), nb);
+          const uint4* bp = reinterpret_cast<const uint4*>(v.keys[o] + (size_t)b * SSB_BUCKET);
+          int idx = -1;
+#pragma unroll
+          for (int q = 0; q < SSB_BUCKET / 4; ++q) {
+            // relaxed, as in pull_kernel's fast path (an acquire costs an L1 invalidate per load): a row is
+            // written before its key is published with st.release.sys, and the copy below is issued on an
+            // address that depends on the key word read here and is served from L2 / HBM, never from L1
+            const uint4 kq = ld_relaxed_sys_v4(bp + q);
+            if (kq.x == key) idx = q * 4;
+            if (kq.y == key) idx = q * 4 + 1;
+            if (kq.z == key) idx = q * 4 + 2;
+            if (kq.w == key) idx = q * 4 + 3;
+          }
+          if (idx >= 0) {
+            gs = (uint32_t)o * v.capacity + b * SSB_BUCKET + (uint32_t)idx;
+            if (kCached) a.slot_cache[cache_index(key, a.cache_bits)] = ((unsigned long long)key << 32) | gs;
+          }
+        }
+      }
+    }
+    const unsigned fast = __ballot_sync(0xffffffffu, gs != SSB_INVALID_SLOT);
+    if (fast) {
+      if (lane == 0) bulk_mbar_expect(bar, (uint32_t)__popc(fast) * row_bytes);
+      __syncwarp();
+      if (gs != SSB_INVALID_SLOT) {
+        const uint32_t o = gs / v.capacity, sl = gs - o * v.capacity;
+        const uint8_t* src = from_shadow ? reinterpret_cast<const uint8_t*>(v.shadow[o]) + (size_t)sl * row_bytes
+                                         : reinterpret_cast<const uint8_t*>(v.rows[o]) + (size_t)sl * row_bytes;
+        bulk_copy_g2s(my_rows + (size_t)lane * row_bytes, src, row_bytes, bar);
+      }
+    }
+    // everything the fast path did not resolve: the probing path, one key at a time, while the copies fly
+    unsigned todo = __ballot_sync(0xffffffffu, w < a.ne && gs == SSB_INVALID_SLOT);
+    while (todo) {
+      const int src_lane = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const uint32_t k = __shfl_sync(0xffffffffu, key, src_lane);
+      const bool vld = k < SSB_LOCKED_KEY;
+      Probe p;
+      p.owner = 0; p.slot = SSB_INVALID_SLOT; p.is_new = false;
+      if (vld) p = probe_insert(v, k, a.insert != 0, lane);
+      pull_emit(v, k, vld, p, c0 + src_lane, lane, a.rows_out, a.rows_bf16, a.grads_zero, a.gslot_out, a.stats, false,
+                make_float4(0.f, 0.f, 0.f, 0.f));
+      if (kCached && lane == 0 && vld && p.slot != SSB_INVALID_SLOT)
+        a.slot_cache[cache_index(k, a.cache_bits)] = ((unsigned long long)k << 32) | ((uint32_t)p.owner * v.capacity + p.slot);
+    }
+    if (fast) {
+      bulk_mbar_wait(bar, phase);
+      phase ^= 1;
+      unsigned m = fast;
+      while (m) {
+        const int r = __ffs(m) - 1;
+        m &= m - 1;
+        const uint32_t g = __shfl_sync(0xffffffffu, gs, r);
+        const size_t wr = (size_t)(c0 + r);
+        const uint8_t* sr = my_rows + (size_t)r * row_bytes;
+        for (int j = lane * 4; j < D; j += 128) {
+          if (from_shadow) {
+            *reinterpret_cast<uint2*>(a.rows_bf16 + wr * D + j) = *reinterpret_cast<const uint2*>(sr + (size_t)j * 2);
+          } else {
+            const float4 val = *reinterpret_cast<const float4*>(sr + (size_t)j * 4);
+            if (a.rows_out) *reinterpret_cast<float4*>(a.rows_out + wr * D + j) = val;
+            if (a.rows_bf16) *reinterpret_cast<uint2*>(a.rows_bf16 + wr * D + j) = pack_bf16x4(val);
+          }
+          if (a.grads_zero) *reinterpret_cast<float4*>(a.grads_zero + wr * D + j) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (lane == 0) a.gslot_out[wr] = g;
+      }
+      __syncwarp();   // every lane has read its share of the slice before the next chunk's copies land in it
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256)
 gather_slots_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot, int64_t n,
                     const uint32_t* __restrict__ n_dev, float* __restrict__ rows_out) {
@@ -651,10 +796,27 @@ int ssb_pull_cached(const SsbTableView* view, const uint32_t* keys, int64_t n, c
     return (int)cudaErrorInvalidValue;
   if (n <= 0) return 0;
   ssb::PullArgs a{0u, gslot, rows_out, (__nv_bfloat16*)rows_bf16, grads_zero, insert, stats, (unsigned long long*)slot_cache, cache_bits};
-  if (slot_cache)
+  static const int use_bulk = [] { const char* e = getenv("SSB200_PULL_BULK"); return e ? atoi(e) : 0; }();
+  const bool from_shadow = !rows_out && rows_bf16 && view->shadow[0] != nullptr;
+  const uint32_t row_bytes = (uint32_t)view->dim * (from_shadow ? 2u : 4u);
+  if (use_bulk && (rows_out || rows_bf16) && (view->dim & 3) == 0 && row_bytes % 16 == 0 && row_bytes <= 512) {
+    const size_t smem = (size_t)ssb::kBulkWarps * 32 * row_bytes + 64;
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaError_t e1 = cudaFuncSetAttribute(ssb::pull_bulk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ssb::kBulkWarps * 32 * 512 + 64);
+      cudaError_t e2 = cudaFuncSetAttribute(ssb::pull_bulk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ssb::kBulkWarps * 32 * 512 + 64);
+      if (e1 != cudaSuccess) return (int)e1;
+      if (e2 != cudaSuccess) return (int)e2;
+      attr_set = true;
+    }
+    const int blocks = ssb::grid_for(n, ssb::kBulkWarps * 32, ssb::kNumSMs * 3);
+    if (slot_cache) ssb::pull_bulk_kernel<true><<<blocks, ssb::kBulkWarps * 32, smem, (cudaStream_t)stream>>>(*view, keys, n, n_dev, a);
+    else ssb::pull_bulk_kernel<false><<<blocks, ssb::kBulkWarps * 32, smem, (cudaStream_t)stream>>>(*view, keys, n, n_dev, a);
+  } else if (slot_cache) {
     ssb::pull_kernel<true><<<ssb::grid_for(n, 32, ssb::kNumSMs * 8), 256, 0, (cudaStream_t)stream>>>(*view, keys, n, n_dev, a);
-  else
+  } else {
     ssb::pull_kernel<false><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, keys, n, n_dev, a);
+  }
   SSB_LAUNCH_CHECK();
   return 0;
 }
