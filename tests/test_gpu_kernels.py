@@ -471,3 +471,20 @@ def test_bf16_row_mirror_stays_in_step(device):
     bf = torch.empty(len(more), 128, dtype=torch.bfloat16, device=device)
     t.pull(u32_tensor(more, device), rows_bf16=bf, want_fp32=False, insert=False)
     assert torch.equal(bf, fp32.to(torch.bfloat16))
+
+
+def test_pull_bulk_copy_variant_passes_the_pull_tests(device):
+    """SSB200_PULL_BULK=1 routes pulls through pull_bulk_kernel (cp.async.bulk rows into shared memory,
+    lane-per-key resolve). The switch is read once per process, so the pull / slot-cache / push tests are
+    re-run in a child process with it set."""
+    import os
+    import subprocess
+    import sys
+
+    env = dict(os.environ, SSB200_PULL_BULK="1")
+    here = os.path.abspath(__file__)
+    p = subprocess.run([sys.executable, "-m", "pytest", here, "-q", "-x", "-m", "gpu", "-p", "no:cacheprovider",
+                        "-k", "(pull or slot or push) and not bulk_copy_variant"],
+                       capture_output=True, text=True, timeout=900, env=env, cwd=os.path.dirname(os.path.dirname(here)))
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-2000:]
+    assert " passed" in p.stdout
