@@ -202,3 +202,44 @@ def test_corpus_loader(native_built, tmp_path):
     assert list(sent0[:3]) == [0, 1, 2] and all(sent0[3:] == PAD)          # padded to sent_len
     assert list(allt[5:10]) == [10, 11, 12, 13, PAD]
     assert list(allt[50:53]) == [0, 1, 2]                                   # second epoch starts over
+
+
+def test_periodic_backup_files(native_built, tmp_path):
+    """every `param_backup_period` push requests a server writes
+    <param_backup_root>/param-<node id>-<counter>.txt in the dump format (one file name per server, D10)."""
+    import glob
+
+    from swiftsnails_b200.parallel.launcher import launch_local_cluster, parse_dump
+
+    root = str(tmp_path / "backups")
+    os.makedirs(root)
+    r = launch_local_cluster("bench", 2, 1, overrides={"dim": 4, "bench_keys": 500, "num_iters": 4, "bench_key_space": 2000,
+                                                       "frag_num": 50, "param_backup_period": 2, "param_backup_root": root},
+                             timeout=120)
+    assert r["master"][0] == 0, r["master"][2]
+    files = sorted(glob.glob(os.path.join(root, "param-*-*.txt")))
+    assert files, os.listdir(root)
+    nodes = {os.path.basename(f).split("-")[1] for f in files}
+    assert nodes == {"1", "2"}                                   # both servers, distinct file names
+    final = [parse_dump(s[1]) for s in r["servers"]]
+    for f in files:
+        with open(f) as fh:
+            d = parse_dump(fh.read())
+        assert d and all(len(v) == 4 for v in d.values())
+        assert any(set(d) <= set(fd) for fd in final)            # a backup is a snapshot of one server's keys
+
+
+def test_master_start_up_timeout(native_built, tmp_path):
+    """registration has a deadline. A master that never sees its nodes gives up after
+    `master_time_out` seconds instead of waiting forever."""
+    import time
+
+    from swiftsnails_b200.parallel.launcher import BIN_DIR, write_configs
+
+    wd = str(tmp_path)
+    write_configs(wd, 1, 1, overrides={"master_time_out": 1})
+    t0 = time.time()
+    p = subprocess.run([os.path.join(BIN_DIR, "swift_master"), "-config", "master.conf"], cwd=wd, capture_output=True,
+                       text=True, timeout=60)
+    assert p.returncode != 0 and time.time() - t0 < 30
+    assert "time" in (p.stderr + p.stdout).lower()
