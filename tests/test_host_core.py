@@ -243,3 +243,41 @@ def test_master_start_up_timeout(native_built, tmp_path):
                        text=True, timeout=60)
     assert p.returncode != 0 and time.time() - t0 < 30
     assert "time" in (p.stderr + p.stdout).lower()
+
+
+def test_dead_server_is_reported_not_hung(native_built, tmp_path):
+    """SURVEY §5.3 (new framework): pull/push waits have a deadline (`rpc_timeout`), so a worker whose
+    server died says so and exits instead of blocking forever in a barrier as the reference does."""
+    import time
+
+    from swiftsnails_b200.parallel.launcher import BIN_DIR, write_configs
+
+    wd = str(tmp_path)
+    write_configs(wd, 1, 1, overrides={"dim": 32, "bench_keys": 20000, "bench_key_space": 200000, "num_iters": 100000,
+                                       "rpc_timeout": 2, "frag_num": 10})
+    logs = {n: open(os.path.join(wd, n + ".log"), "w") for n in ("master", "server", "worker")}
+    env = dict(os.environ, SSB200_LOCAL_IP="127.0.0.1")
+    procs = {}
+    try:
+        procs["master"] = subprocess.Popen([os.path.join(BIN_DIR, "swift_master"), "-config", "master.conf"], cwd=wd,
+                                           stdout=logs["master"], stderr=subprocess.STDOUT, env=env)
+        time.sleep(0.2)
+        procs["server"] = subprocess.Popen([os.path.join(BIN_DIR, "swift_server"), "-config", "node.conf"], cwd=wd,
+                                           stdout=subprocess.DEVNULL, stderr=logs["server"], env=env)
+        procs["worker"] = subprocess.Popen([os.path.join(BIN_DIR, "swift_worker"), "-config", "node.conf", "-app", "bench"],
+                                           cwd=wd, stdout=logs["worker"], stderr=subprocess.STDOUT, env=env)
+        time.sleep(1.5)                                  # registration done, the worker is pulling / pushing
+        assert procs["worker"].poll() is None, "worker finished before the fault was injected"
+        procs["server"].kill()
+        rc = procs["worker"].wait(timeout=40)
+        assert rc != 0
+    finally:
+        for p in procs.values():
+            if p.poll() is None:
+                p.kill()
+            p.wait()
+        for f in logs.values():
+            f.close()
+    with open(os.path.join(wd, "worker.log")) as f:
+        out = f.read()
+    assert "timed out" in out and "server is not answering" in out, out[-1500:]
