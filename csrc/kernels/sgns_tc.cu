@@ -196,6 +196,9 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// kDiag (mode bit 4, experimental): epilogue 1 walks each row's context band by diagonal instead of by
+// column block — see the comment at the epilogue.
+template <bool kDiag>
 __global__ void __maxnreg__(64)
 sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict__ grads,
                      const uint32_t* __restrict__ inv_in, const uint32_t* __restrict__ inv_out,
@@ -447,47 +450,105 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
           sig = __frcp_rn(t);
           logt = 0.6931471805599453f * __log2f(t);
         };
-        if (part < 3) {
-          float v[16];
-          const int c0 = q * 32 + part * 16;          // band window of this lane quarter: [32q, 32q+48)
-          tmem_ld16(lane_base + kTmemS + c0, v);
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            if (col_ok(c0 + j)) {
-              float sg, lt;
-              sig_logt(v[j], sg, lt);
-              g_add(c0 + j, sg - 1.0f);
-              loss_acc += lt;
-              pair_acc += 1.f;
-            }
-          }
-        }
-        {
-          // negatives: weight m_i * K / 16 each, m_i = number of valid contexts of centre i. The 16
-          // negatives are split 4/2/4/6 over the column parts to even out the band work (the
-          // middle band block holds most of a row's valid contexts, part 3 has no band block).
-          float m_i = 0.f;
-          if (row_ok) {
-            if (chk_rows) {
-#pragma unroll
-              for (int c = 0; c <= 2 * kHalo; ++c) m_i += col_ok(i + c) ? 1.f : 0.f;
-            } else {
-              m_i = (float)max(c_hi - c_lo, 0);
-            }
-          }
-          const int n_lo = (part == 0) ? 0 : (part == 1) ? 4 : (part == 2) ? 6 : 10;
-          const int n_hi = (part == 0) ? 4 : (part == 1) ? 6 : (part == 2) ? 10 : 16;
-          float v[16];
-          tmem_ld16(lane_base + kTmemS + kCtx, v);
-          const float w = m_i * neg_k * (1.0f / kNeg);
-          if (m_i > 0.f) {
-#pragma unroll
+        if constexpr (!kDiag) {
+          if (part < 3) {
+            float v[16];
+            const int c0 = q * 32 + part * 16;          // band window of this lane quarter: [32q, 32q+48)
+            tmem_ld16(lane_base + kTmemS + c0, v);
+  #pragma unroll
             for (int j = 0; j < 16; ++j) {
-              if (j >= n_lo && j < n_hi && misc->on_row[b][kCtx + j] != SSB_INVALID_SLOT) {
+              if (col_ok(c0 + j)) {
                 float sg, lt;
                 sig_logt(v[j], sg, lt);
-                g_add(kCtx + j, w * sg);
-                loss_acc += w * (v[j] + lt);
+                g_add(c0 + j, sg - 1.0f);
+                loss_acc += lt;
+                pair_acc += 1.f;
+              }
+            }
+          }
+          {
+            // negatives: weight m_i * K / 16 each, m_i = number of valid contexts of centre i. The 16
+            // negatives are split 4/2/4/6 over the column parts to even out the band work (the
+            // middle band block holds most of a row's valid contexts, part 3 has no band block).
+            float m_i = 0.f;
+            if (row_ok) {
+              if (chk_rows) {
+  #pragma unroll
+                for (int c = 0; c <= 2 * kHalo; ++c) m_i += col_ok(i + c) ? 1.f : 0.f;
+              } else {
+                m_i = (float)max(c_hi - c_lo, 0);
+              }
+            }
+            const int n_lo = (part == 0) ? 0 : (part == 1) ? 4 : (part == 2) ? 6 : 10;
+            const int n_hi = (part == 0) ? 4 : (part == 1) ? 6 : (part == 2) ? 10 : 16;
+            float v[16];
+            tmem_ld16(lane_base + kTmemS + kCtx, v);
+            const float w = m_i * neg_k * (1.0f / kNeg);
+            if (m_i > 0.f) {
+  #pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                if (j >= n_lo && j < n_hi && misc->on_row[b][kCtx + j] != SSB_INVALID_SLOT) {
+                  float sg, lt;
+                  sig_logt(v[j], sg, lt);
+                  g_add(kCtx + j, w * sg);
+                  loss_acc += w * (v[j] + lt);
+                }
+              }
+            }
+          }
+} else {
+          // Diagonal form. In the column-block form above a warp runs the sigmoid path for each of its 16
+          // columns with only the ~1/3 of its lanes whose band contains that column. Here the band warps
+          // hold the whole 48-column window of their lane quarter (indexed per lane, so it lives in local
+          // memory) and step through the OFFSETS a = 1..window on one side of the centre: lane i looks at
+          // column i + 8 -/+ a, so every lane whose window reaches that far works in the same iteration.
+          // part 0: left side, part 1: right side, parts 2 and 3: eight negatives each.
+          if (part < 2) {
+            float v[48];
+            const int cq = q * 32;
+            {
+              float t16[16];
+#pragma unroll
+              for (int blk = 0; blk < 3; ++blk) {
+                tmem_ld16(lane_base + kTmemS + cq + blk * 16, t16);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[blk * 16 + j] = t16[j];
+              }
+            }
+            const int sgn = (part == 0) ? -1 : 1;
+            for (int a = 1; a <= window; ++a) {
+              const int c = self_c + sgn * a;            // in [cq, cq + 48) for every lane: lane + 8 -/+ a, a <= 8
+              if (col_ok(c)) {
+                float sg, lt;
+                sig_logt(v[c - cq], sg, lt);
+                g_add(c, sg - 1.0f);
+                loss_acc += lt;
+                pair_acc += 1.f;
+              }
+            }
+          } else {
+            float m_i = 0.f;
+            if (row_ok) {
+              if (chk_rows) {
+#pragma unroll
+                for (int c = 0; c <= 2 * kHalo; ++c) m_i += col_ok(i + c) ? 1.f : 0.f;
+              } else {
+                m_i = (float)max(c_hi - c_lo, 0);
+              }
+            }
+            const int n_lo = (part == 2) ? 0 : 8, n_hi = n_lo + 8;
+            float v[16];
+            tmem_ld16(lane_base + kTmemS + kCtx, v);
+            const float w = m_i * neg_k * (1.0f / kNeg);
+            if (m_i > 0.f) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                if (j >= n_lo && j < n_hi && misc->on_row[b][kCtx + j] != SSB_INVALID_SLOT) {
+                  float sg, lt;
+                  sig_logt(v[j], sg, lt);
+                  g_add(kCtx + j, w * sg);
+                  loss_acc += w * (v[j] + lt);
+                }
               }
             }
           }
@@ -651,15 +712,22 @@ static int launch_block_tc(const void* params, float* grads, int64_t n_rows, int
   }
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(sgns_block_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(sgns_block_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(sgns_block_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
   int64_t tiles = (n_tok + kM - 1) / kM;
   int blocks = (int)(tiles < ssb::kNumSMs ? tiles : ssb::kNumSMs);
-  sgns_block_tc_kernel<<<blocks, kThreads, kSmemBytes, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)params, grads, inv_in, inv_out, (int)n_tok, sent_len, window, seed, offset, neg_idx, neg_k,
-      loss_out, tmap, mode, debug, dm);
+  if (mode & 4)
+    sgns_block_tc_kernel<true><<<blocks, kThreads, kSmemBytes, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)params, grads, inv_in, inv_out, (int)n_tok, sent_len, window, seed, offset, neg_idx, neg_k,
+        loss_out, tmap, mode, debug, dm);
+  else
+    sgns_block_tc_kernel<false><<<blocks, kThreads, kSmemBytes, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)params, grads, inv_in, inv_out, (int)n_tok, sent_len, window, seed, offset, neg_idx, neg_k,
+        loss_out, tmap, mode, debug, dm);
   SSB_LAUNCH_CHECK();
   return 0;
 }

@@ -91,3 +91,25 @@ def test_fused_pull_direct_mode_matches_cache_mode(device):
     # so two runs agree to bf16 rounding of those entries, not bit for bit
     err, scale = (g1 - g2).abs().max().item(), g1.abs().max().item()
     assert err < 1e-2 * scale, (err, scale)
+
+
+def _diag_child():
+    """Runs in a child process: the experimental diagonal epilogue (mode bit 4) on the standard cases."""
+    dev = torch.device("cuda", 0)
+    for n_tok, U, sent_len, window in [(128, 300, 1000, 5), (1000, 500, 37, 5), (5000, 64, 100, 8), (300, 2000, 50, 1)]:
+        _run(dev, 5, n_tok, U, sent_len, window)
+    print("DIAG_OK")
+
+
+def test_sgns_block_tc_diagonal_epilogue_experimental(device):
+    """Mode bit 4 (`bench.py --tc-mode 5`): the diagonal form of epilogue 1 gives the same gradients and
+    loss as the oracle. Run in a child process so that a fault in the experimental instantiation cannot
+    poison this process's CUDA context."""
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r); import test_gpu_sgns_tc as t; t._diag_child()" % (
+        root, os.path.join(root, "tests"))
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, cwd=root)
+    assert p.returncode == 0 and "DIAG_OK" in p.stdout, p.stdout[-1500:] + p.stderr[-1500:]
