@@ -166,6 +166,14 @@ void* ssb_corpus_open(const char* path, int batch_tokens, int sent_len, uint32_t
   std::fclose(f);
   return new CorpusLoader(path, batch_tokens, sent_len, pad_id, epochs);
 }
+void* ssb_corpus_open_split(const char* path, int batch_tokens, int sent_len, uint32_t pad_id, int epochs, int split_n,
+                            int split_i) {
+  FILE* f = std::fopen(path, "r");
+  if (!f) return nullptr;
+  std::fclose(f);
+  if (split_n < 1 || split_i < 0 || split_i >= split_n) return nullptr;
+  return new CorpusLoader(path, batch_tokens, sent_len, pad_id, epochs, 4, split_n, split_i);
+}
 long ssb_corpus_next(void* h, uint32_t* out) { return static_cast<CorpusLoader*>(h)->next(out); }
 void ssb_corpus_close(void* h) { delete static_cast<CorpusLoader*>(h); }
 

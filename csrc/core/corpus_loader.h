@@ -13,9 +13,15 @@ namespace ssb {
 class CorpusLoader {
  public:
   // sentences are padded/cut to `sent_len` tokens; pad_id marks padding (SSB_EMPTY_KEY = skipped by dedup)
-  CorpusLoader(const std::string& path, int batch_tokens, int sent_len, uint32_t pad_id, int epochs, int queue_depth = 4)
-      : path_(path), batch_(batch_tokens), sent_len_(sent_len), pad_(pad_id), epochs_(epochs), queue_(queue_depth) {
+  // split_n > 1: this reader keeps only the non-empty lines whose index % split_n == split_i — the
+  // disjoint per-worker data split that Hadoop streaming gives the reference's workers
+  // (tools/hadoop-worker.sh:8-21), without having to cut the file up first.
+  CorpusLoader(const std::string& path, int batch_tokens, int sent_len, uint32_t pad_id, int epochs, int queue_depth = 4,
+               int split_n = 1, int split_i = 0)
+      : path_(path), batch_(batch_tokens), sent_len_(sent_len), pad_(pad_id), epochs_(epochs),
+        split_n_(split_n < 1 ? 1 : split_n), split_i_(split_i), queue_(queue_depth) {
     CHECK_GT(batch_, 0);
+    CHECK(split_i_ >= 0 && split_i_ < split_n_) << "split index " << split_i_ << " outside [0, " << split_n_ << ")";
     CHECK_GT(sent_len_, 0);
     CHECK_EQ(batch_ % sent_len_, 0) << "batch_tokens must be a multiple of sent_len";
     thread_ = std::thread([this] { run(); });
@@ -49,11 +55,19 @@ class CorpusLoader {
       FILE* f = std::fopen(path_.c_str(), "r");
       if (!f) { LOG(ERROR) << "cannot open corpus " << path_; break; }
       LineFileReader reader;
+      long line_no = 0;
       while (!stop_.load()) {
         char* line = reader.getline(f);
         if (!line) break;
         int n = 0;
         char* p = line;
+        if (split_n_ > 1) {
+          // index non-empty lines only, so every reader sees the same numbering
+          char* q = p;
+          while (*q == ' ' || *q == '\t' || *q == '\r' || *q == '\n') ++q;
+          if (*q == '\0') continue;
+          if (line_no++ % split_n_ != split_i_) continue;
+        }
         while (n < sent_len_) {
           char* end = nullptr;
           unsigned long v = std::strtoul(p, &end, 10);
@@ -86,6 +100,7 @@ class CorpusLoader {
   int batch_, sent_len_;
   uint32_t pad_;
   int epochs_;
+  int split_n_, split_i_;
   queue_with_capacity<std::vector<uint32_t>> queue_;
   std::thread thread_;
   std::atomic<bool> stop_{false}, done_{false};

@@ -47,6 +47,9 @@ int ssb_cpu_table_dump(void *t, const char *path);
  * fixed-size token batches (sentences padded to sent_len with pad_id). next() returns the number
  * of real tokens in the batch or -1 at the end. ref: utils/file.h:14-33 (scan_file_by_line). */
 void *ssb_corpus_open(const char *path, int batch_tokens, int sent_len, uint32_t pad_id, int epochs);
+/* Same, keeping only the non-empty lines whose index % split_n == split_i (per-worker data split). */
+void *ssb_corpus_open_split(const char *path, int batch_tokens, int sent_len, uint32_t pad_id, int epochs,
+                            int split_n, int split_i);
 long ssb_corpus_next(void *h, uint32_t *out);
 void ssb_corpus_close(void *h);
 

@@ -318,23 +318,28 @@ class Word2VecTrainer:
         self._m_rate.mark(self.cfg.tokens_per_step)
         return prev
 
-    def train_file(self, path, epochs=1, log_every=0):
+    def train_file(self, path, epochs=1, log_every=0, split=None, max_steps=None):
         """Train from a text corpus (one sentence of integer word ids per line — the reference's data
         format, tools/gen_word2vec_data.py). Sentences are cut / padded to ``cfg.sent_len``; a native
         background reader (utils/corpus.py) fills pinned batches while the GPU works.
+        ``split=(n, i)`` reads worker i's share of the lines; ``max_steps`` stops after that many
+        minibatches (with the inbox push every rank has to run the same number of steps).
         Returns (tokens_trained, last_mean_loss)."""
         from ..utils.corpus import CorpusLoader
 
         self.worker.has_padding = True
-        loader = CorpusLoader(path, self.cfg.tokens_per_step, self.cfg.sent_len, epochs=epochs)
+        loader = CorpusLoader(path, self.cfg.tokens_per_step, self.cfg.sent_len, epochs=epochs, split=split)
         total, step = 0, 0
         for buf, n_real in loader:
+            if max_steps is not None and step >= max_steps:
+                break
             loss = self.train_step(buf)
             total += n_real
             step += 1
             if log_every and step % log_every == 0 and loss is not None:
                 print("step %d  tokens %d  loss/pair %.4f" % (step, total, loss))
         loader.close()
+        self.steps_done = step
         return total, self.finish()
 
     def finish(self):

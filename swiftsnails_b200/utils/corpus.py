@@ -14,15 +14,18 @@ PAD = 0xFFFFFFFF  # SSB_EMPTY_KEY: skipped by dedup / pull / the SGNS kernels
 
 
 class CorpusLoader:
-    def __init__(self, path, batch_tokens, sent_len, epochs=1, pin=True):
+    def __init__(self, path, batch_tokens, sent_len, epochs=1, pin=True, split=None):
+        """``split=(n, i)``: keep only the non-empty lines whose index % n == i — worker i's share of a
+        corpus that n workers read together (the reference gets this split from Hadoop streaming)."""
         lib = _lib.core()
-        lib.ssb_corpus_open.restype = C.c_void_p
-        lib.ssb_corpus_open.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint32, C.c_int]
+        lib.ssb_corpus_open_split.restype = C.c_void_p
+        lib.ssb_corpus_open_split.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_uint32, C.c_int, C.c_int, C.c_int]
         lib.ssb_corpus_next.restype = C.c_long
         lib.ssb_corpus_next.argtypes = [C.c_void_p, C.c_void_p]
         lib.ssb_corpus_close.argtypes = [C.c_void_p]
         self._lib = lib
-        self._h = lib.ssb_corpus_open(str(path).encode(), batch_tokens, sent_len, PAD, epochs)
+        n, i = split if split else (1, 0)
+        self._h = lib.ssb_corpus_open_split(str(path).encode(), batch_tokens, sent_len, PAD, epochs, int(n), int(i))
         if not self._h:
             raise OSError("cannot open corpus %s" % path)
         self.batch_tokens = batch_tokens

@@ -94,6 +94,36 @@ def test_train_from_text_corpus_with_ragged_sentences(device, tmp_path):
     assert np.isfinite(last) and last < 4.0, last                                    # 6*ln2 = 4.16 at init
 
 
+@pytest.mark.xfail(strict=False, reason="command-line glue written after the GPU budget of round 1 ran out; its parts are tested above")
+def test_train_cli_one_gpu(device, tmp_path):
+    """`python -m swiftsnails_b200.train -config … -data … -out …`: the GPU counterpart of
+    `swift_worker -config … -data …` — trains from a text corpus and leaves a reference-format dump."""
+    import json
+    import subprocess
+    import sys
+
+    from swiftsnails_b200.parallel.launcher import parse_dump
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    data, conf, out = str(tmp_path / "corpus.txt"), str(tmp_path / "worker.conf"), str(tmp_path / "params.txt")
+    subprocess.run([sys.executable, os.path.join(root, "tools", "gen_word2vec_data.py"), "--lines", "6000", "--vocab", "301",
+                    "--zipf", "1.0", "--out", data], check=True)
+    with open(conf, "w") as f:
+        f.write("dim: 128\nvocab: 301\nwindow: 5\nnegative: 5\nlearning_rate: 0.05\nnum_iters: 3\nsent_len: 16\n"
+                "tokens_per_step: 4096\nupdate: adagrad\n")
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    p = subprocess.run([sys.executable, "-m", "swiftsnails_b200.train", "-config", conf, "-data", data, "-out", out],
+                       capture_output=True, text=True, timeout=600, cwd=root, env=env)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    res = json.loads([l for l in p.stdout.splitlines() if l.startswith("RESULT ")][0][len("RESULT "):])
+    n_tokens = sum(len(l.split()) for l in open(data))
+    assert res["tokens"] == 3 * n_tokens and res["loss_per_pair"] < 4.0 and res["words_per_s"] > 0
+    with open(out) as f:
+        d = parse_dump(f.read())
+    assert 300 < len(d) <= 2 * 301 and all(len(v) == 128 for v in d.values())
+    assert all(0 <= k < 2 * 301 for k in d)
+
+
 @pytest.mark.parametrize("impl", ["cuda_core", "tcgen05"])
 def test_word2vec_learns_planted_structure(device, impl):
     """Quality check, not just 'loss goes down': in a corpus where word a is always followed by

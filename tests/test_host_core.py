@@ -281,3 +281,48 @@ def test_dead_server_is_reported_not_hung(native_built, tmp_path):
     with open(os.path.join(wd, "worker.log")) as f:
         out = f.read()
     assert "timed out" in out and "server is not answering" in out, out[-1500:]
+
+
+def test_corpus_loader_split_and_cli_helpers(native_built, tmp_path):
+    """Per-worker data split of the native loader (lines with index % n == i, empty lines not counted)
+    and the host-side helpers of `python -m swiftsnails_b200.train` (config -> model config, step count)."""
+    from swiftsnails_b200.train import count_sentences, parse_args, total_steps, word2vec_config
+    from swiftsnails_b200.utils.config import ConfigParser
+    from swiftsnails_b200.utils.corpus import PAD, CorpusLoader
+
+    lines = []
+    for i in range(23):
+        lines.append(" ".join(str(100 * i + j) for j in range(1 + i % 3)))
+        if i % 5 == 0:
+            lines.append("")                                    # empty lines do not take an index
+    p = tmp_path / "c.txt"
+    p.write_text("\n".join(lines) + "\n")
+    assert count_sentences(str(p)) == 23
+    seen = []
+    for rank in range(3):
+        ld = CorpusLoader(str(p), batch_tokens=8, sent_len=4, epochs=1, pin=False, split=(3, rank))
+        first = []
+        for buf, n in ld:
+            a = buf.numpy().view(np.uint32).reshape(-1, 4)
+            first += [int(r[0]) // 100 for r in a if r[0] != PAD]
+        ld.close()
+        assert first == list(range(rank, 23, 3))                # worker `rank` gets sentences rank, rank+3, ...
+        seen += first
+    assert sorted(seen) == list(range(23))                      # disjoint and complete
+
+    conf = tmp_path / "w.conf"
+    conf.write_text("dim: 128\nvocab: 301\nwindow: 3\nnegative: 3\nlearning_rate: 0.1\nnum_iters: 2\n"
+                    "sent_len: 4\ntokens_per_step: 10\nupdate: adagrad\n")
+    cfg = word2vec_config(ConfigParser(str(conf)))
+    assert (cfg.vocab, cfg.window, cfg.negatives, cfg.lr, cfg.optimizer) == (301, 3, 3, 0.1, "adagrad")
+    assert cfg.tokens_per_step == 8 and cfg.tile_impl == "tcgen05"          # whole sentences per minibatch
+    # 23 sentences, 3 workers: the smallest share is 7 per pass, 2 sentences per minibatch
+    assert total_steps(23, 3, cfg, epochs=1) == 4 and total_steps(23, 3, cfg, epochs=2) == 7
+    assert total_steps(2, 3, cfg) == 0
+    # every worker really has that many minibatches
+    for rank in range(3):
+        ld = CorpusLoader(str(p), batch_tokens=8, sent_len=4, epochs=2, pin=False, split=(3, rank))
+        assert sum(1 for _ in ld) >= total_steps(23, 3, cfg, epochs=2)
+        ld.close()
+    a = parse_args(["-config", "x.conf", "-data", "d.txt", "-out", "o.txt"])
+    assert (a.config, a.data, a.out, a.app) == ("x.conf", "d.txt", "o.txt", "word2vec")
