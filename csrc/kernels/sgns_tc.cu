@@ -710,13 +710,15 @@ static int launch_block_tc(const void* params, float* grads, int64_t n_rows, int
     int e = make_row_tmap(&tmap, params, (uint64_t)n_rows, box_rows > 0 ? (uint32_t)box_rows : 1u);
     if (e) return e;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[64] = {false};   // the attribute is per device: a process may drive several
+  int dev_id = 0;
+  if (cudaGetDevice(&dev_id) != cudaSuccess || dev_id < 0 || dev_id >= 64) return (int)cudaErrorInvalidDevice;
+  if (!attr_set[dev_id]) {
     cudaError_t e = cudaFuncSetAttribute(sgns_block_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return (int)e;
     e = cudaFuncSetAttribute(sgns_block_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return (int)e;
-    attr_set = true;
+    attr_set[dev_id] = true;
   }
   int64_t tiles = (n_tok + kM - 1) / kM;
   int blocks = (int)(tiles < ssb::kNumSMs ? tiles : ssb::kNumSMs);

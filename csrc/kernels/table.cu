@@ -801,7 +801,10 @@ int ssb_pull_cached(const SsbTableView* view, const uint32_t* keys, int64_t n, c
   const uint32_t row_bytes = (uint32_t)view->dim * (from_shadow ? 2u : 4u);
   if (use_bulk && (rows_out || rows_bf16) && (view->dim & 3) == 0 && row_bytes % 16 == 0 && row_bytes <= 512) {
     const size_t smem = (size_t)ssb::kBulkWarps * 32 * row_bytes + 64;
-    static bool attr_set = false;
+    static bool attr_set_dev[64] = {false};   // the attribute is per device
+    int dev_id = 0;
+    if (cudaGetDevice(&dev_id) != cudaSuccess || dev_id < 0 || dev_id >= 64) return (int)cudaErrorInvalidDevice;
+    bool& attr_set = attr_set_dev[dev_id];
     if (!attr_set) {
       cudaError_t e1 = cudaFuncSetAttribute(ssb::pull_bulk_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ssb::kBulkWarps * 32 * 512 + 64);
       cudaError_t e2 = cudaFuncSetAttribute(ssb::pull_bulk_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ssb::kBulkWarps * 32 * 512 + 64);
