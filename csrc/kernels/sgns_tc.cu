@@ -1,4 +1,5 @@
-// sgns_tc.cu — K5: the word2vec SGNS step on 5th-generation tensor cores (tcgen05 / TMEM / TMA).
+// sgns_tc.cu — K5: the word2vec SGNS step on 5th-generation tensor cores (tcgen05 / TMEM / TMA),
+// pipelined across tiles.
 //
 // The reference's worker computes, per (centre, context, negatives) sample, dot products on
 // `Vec` (utils/vec1.h:97-104) + sigmoid, and accumulates into cache.grads() between
@@ -9,234 +10,208 @@
 // all lie in the 144-token window [t0-8, t0+136), so the tile's positive logits are a band of
 // one dense GEMM and the whole forward + backward is three tensor-core GEMMs:
 //
-//   S    [128 x 160] = In[128 x D] . ON[160 x D]^T        ON = 144 context rows ++ 16 negatives
-//   G    [128 x 160] = dL/dS  (band mask, window shrink, sigmoid — epilogue on TMEM)
-//   dIn  [128 x D  ] = G . ON                              (A = G K-major,   B = ON MN-major)
-//   dON^T[D   x 160] = In^T . G                            (A = In MN-major, B = G  MN-major)
+//   S     [128 x 160] = In[128 x D] . ON[160 x D]^T       ON = 144 context rows ++ 16 negatives
+//   G     [128 x 160] = dL/dS  (band mask, window shrink, sigmoid — epilogue 1, from TMEM)
+//   dIn^T [D   x 128] = ON^T . G^T                         (A = ON MN-major, B = G  K-major)
+//   dON^T [D   x 160] = In^T . G                           (A = In MN-major, B = G  MN-major, N padded to 192)
 //
-// Rows are gathered from the worker's bf16 cache (written by the pull kernel next to the fp32
-// table) by row index straight into 128B-swizzled shared memory (TMA tile::gather4, or a plain
-// vector-load path used for bring-up and as fallback), feed `tcgen05.mma.kind::f16` (bf16 in,
-// fp32 accumulate), accumulators live in TMEM (448 of 512 columns), and gradients leave in fp32
-// through `red` into the cache's grad buffer: 288 row reads + 288 row reductions per 128 tokens
-// instead of ~1500 each for per-pair processing.  bf16 (not tf32) because every operand is
-// used both K-major and MN-major, and 32-bit MN-major operands need a different swizzle
-// (SWIZZLE_128B_BASE32B) than their K-major use — 16-bit operands take plain SWIZZLE_128B both ways.
-#include <cuda.h>
-#include <cuda_bf16.h>
-#include <cstring>
-#include "common.cuh"
+// Both gradients come out TRANSPOSED — a TMEM lane is an embedding dimension, a TMEM column a row of
+// the gradient — so a warp that reads one column with `tcgen05.ld` holds 32 consecutive floats of one
+// gradient row: epilogue 2 reduces them into the cache's grad buffer with one coalesced 128-byte `red`
+// per (row, lane quarter), straight from registers, with no shared-memory transpose.
+//
+// Pipeline (one persistent CTA per SM, 22 warps, roles never meet at a CTA-wide barrier inside the loop):
+//
+//   warp 16      producer   row indices, tile-local dedup, TMA tile::gather4 of In/ON rows (2 stages)
+//   warp 17      MMA issue  one thread issues S(t+1) and the gradient MMAs of tile t as their inputs
+//                           become ready (whichever first), commits completion to mbarriers
+//   warps 0-7    epilogue 1 S (TMEM) -> sigmoid / loss -> G (bf16, swizzled shared memory)
+//   warps 8-15   epilogue 2 dIn^T / dON^T (TMEM) -> `red` into the gradient buffer
+//
+// so that, in steady state, S-MMA and epilogue 1 of tile t+1 and the TMA gather of tile t+2 run under
+// epilogue 2 of tile t. TMEM: S 160 + dIn^T 128 + dON^T 192 = 480 of 512 columns, each single-buffered:
+// S is released as soon as epilogue 1 has it in registers, the gradient accumulators when epilogue 2
+// has issued its last `red`.
+//
+// Rows are gathered from the worker's bf16 cache (written by the pull kernel next to the fp32 table)
+// — or, in direct mode, from the peer-mapped bf16 mirror of the table itself — by row index straight
+// into 128B-swizzled shared memory. bf16 (not tf32) because every operand is used both K-major and
+// MN-major, and 32-bit MN-major operands need a different swizzle (SWIZZLE_128B_BASE32B) than their
+// K-major use — 16-bit operands take plain SWIZZLE_128B both ways. Accumulation and gradients are fp32.
+#include "tc_common.cuh"
 
 namespace ssb {
 namespace tc {
 
-constexpr int kD = 128;          // embedding dim
-constexpr int kM = 128;          // centre tokens per tile
-constexpr int kHalo = 8;         // max window
-constexpr int kCtx = kM + 2 * kHalo;   // 144 context rows
-constexpr int kNeg = 16;
-constexpr int kN = kCtx + kNeg;  // 160
-constexpr int kConsumerWarps = 16;
-constexpr int kConsumers = kConsumerWarps * 32;   // 512 epilogue / MMA-issue threads
-constexpr int kThreads = kConsumers + 32;         // + 1 producer warp (TMA)
+int launch_block_tc_serial(const TcArgs& a, const CUtensorMap& tmap, void* stream);   // sgns_tc_serial.cu
 
-// bf16 operands: a "column block" is 64 elements = 128 bytes wide.
-constexpr uint32_t kInBlk = kM * 128;   // bytes of one [128 rows x 128 B] column block of In / G
-constexpr uint32_t kOnBlk = kN * 128;   // bytes of one [160 rows x 128 B] column block of ON
-constexpr int kInBlks = kD / 64;        // 2
-constexpr int kGBlks = 4;               // 160 columns used; padded to 256 so the second dON MMA stays in bounds
-constexpr uint32_t kInBytes = kInBlks * kInBlk;   // 32768
-constexpr uint32_t kOnBytes = kInBlks * kOnBlk;   // 40960
+constexpr int kE1Warps = 8;                       // warps 0..7 : lane quarter = warp % 4, band side = warp / 4
+constexpr int kE2Warps = 8;                       // warps 8..15: lane quarter = warp % 4, column half = (warp / 4) % 2
+constexpr int kProducerWarp = kE1Warps + kE2Warps;   // 16
+constexpr int kMmaWarp = kProducerWarp + 1;          // 17
+constexpr int kGatherWarp0 = kMmaWarp + 1;           // 18..21: cp.async gather warps (mode bit 32; idle otherwise)
+constexpr int kGatherWarps = 4;
+constexpr int kThreads = (kGatherWarp0 + kGatherWarps) * 32;   // 704
+constexpr int kE1Threads = kE1Warps * 32;            // 256
+
+constexpr int kGCols = 192;                          // G is [128 x 192] bf16: 160 used, padded to whole 64-column blocks
+constexpr int kGBlks = kGCols / 64;                  // 3
+constexpr uint32_t kGBytes = kGBlks * kInBlk;        // 49152
 constexpr uint32_t kOffIn = 0;                               // 2 stages
 constexpr uint32_t kOffOn = kOffIn + 2 * kInBytes;           // 65536, 2 stages
 constexpr uint32_t kOffG = kOffOn + 2 * kOnBytes;            // 147456
-constexpr uint32_t kOffMisc = kOffG + kGBlks * kInBlk;       // 212992
-constexpr uint32_t kSmemBytes = kOffMisc + 8192;
+constexpr uint32_t kOffMisc = kOffG + kGBytes;               // 196608
+constexpr uint32_t kOffDedup = kOffMisc + 10240;             // 206848
+constexpr uint32_t kSmemBytes = kOffDedup + 12288;           // 219136
 
-// TMEM columns: S (160) | dIn (128) | dON rows 0..127 (128); dON rows 128..255 aliases S.
-constexpr uint32_t kTmemS = 0, kTmemDIn = 160, kTmemDOnA = 288, kTmemDOnB = 0, kTmemCols = 512;
+// TMEM columns
+constexpr uint32_t kTmemS = 0, kTmemDIn = 160, kTmemDOn = 288, kTmemCols = 512;
+static_assert(kTmemDOn + kGCols <= kTmemCols, "TMEM budget");
 
 struct Misc {
-  uint32_t in_row[2][kM];
-  uint32_t on_row[2][kN];
-  uint32_t in_tab[2][kM];       // direct mode: row of the (peer-mapped) bf16 table mirror to gather from
+  uint32_t in_tab[2][kM];          // per stage: row to gather for each centre token (cache row, or table-mirror row in direct mode)
   uint32_t on_tab[2][kN];
-  uint32_t out_rows[kM + kN];   // gradient destination rows of the current tile (INVALID = skip)
-  uint8_t lead_in[2][kM];       // first position in the tile holding the same row (tile-local dedup)
-  uint8_t lead_on[2][kN];
-  unsigned long long full_bar[2];
-  unsigned long long empty_bar[2];
-  unsigned long long lead_bar[2];
-  uint32_t ctx_has_invalid[2];  // a context row inside the batch is INVALID (padding key): count m_i the slow way
-  unsigned long long mma_bar;
+  uint16_t row_lead[2][kM];        // per stage, per centre row: lead | dup << 8                         (producer warp)
+  uint16_t row_win[2][kM];         // per stage, per centre row: c_lo | c_hi << 8 (c_lo > c_hi: no contexts) (helper warps)
+  uint16_t col_meta[2][kN];        // per stage, per ON column: lead | dup << 8 | invalid << 9
+  uint32_t out_rows[3][kM + kN];   // per tile (it % 3): gradient destination rows, leaders only (INVALID = skip)
+  unsigned long long full_bar[2];  // operand rows landed (producer TMA / gather warps -> MMA)
+  unsigned long long empty_bar[2]; // gradient MMAs retired: stage free (MMA -> producer)
+  unsigned long long lead_bar[2];  // row_lead / col_meta ready (producer -> epilogue 1)
+  unsigned long long win_bar[2];   // row_win ready (helper warps -> epilogue 1)
+  unsigned long long rows_bar[3];  // out_rows[it % 3] ready (producer -> epilogue 2)
+  unsigned long long idx_bar[2];   // gather indices published, stage free (producer -> cp.async gather warps)
+  unsigned long long g_full[2];    // G written (epilogue 1 -> MMA); by tile parity
+  unsigned long long s_full;       // S in TMEM (MMA -> epilogue 1)
+  unsigned long long s_free;       // S read into registers (epilogue 1 -> MMA)
+  unsigned long long g_free;       // gradient MMAs retired: G may be rewritten (MMA -> helper warps)
+  unsigned long long g_zero;       // G zeroed for the next tile (helper warps -> epilogue 1)
+  unsigned long long d_full;       // dIn^T / dON^T in TMEM (MMA -> epilogue 2)
+  unsigned long long d_free;       // accumulators read into registers (epilogue 2 -> MMA)
+  uint32_t ctx_has_invalid[2];     // a context row inside the batch is INVALID (padding key): count m_i the slow way
   uint32_t tmem_base;
-  float loss[kConsumerWarps];
-  float pairs[kConsumerWarps];
+  float loss[kE1Warps];
+  float pairs[kE1Warps];
 };
-static_assert(sizeof(Misc) <= 8192, "misc region too large");
+static_assert(sizeof(Misc) <= 10240, "misc region too large");
 
-// ---- PTX wrappers -----------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+// scratch of the producer's tile-local dedup: two small open-addressing sets (id -> first position, count)
+struct DedupScratch {
+  uint32_t key_in[256], pos_in[256];   // pos: first position of the id (atomicMin); cnt: its occurrences
+  uint32_t key_on[512], pos_on[512];
+  uint32_t cnt_in[256], cnt_on[512];
+};
+static_assert(sizeof(DedupScratch) <= 12288, "dedup scratch too large");
 
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-// Bounded wait: a lost arrival traps (reported as a launch failure) instead of hanging the GPU.
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
-  uint32_t done = 0;
-  for (uint32_t it = 0; it < (1u << 26); ++it) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-    if (done) return;
-  }
-  __trap();
-}
-__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
-}
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+__device__ __forceinline__ bool mbar_test(unsigned long long* bar, uint32_t parity) {
+  uint32_t done;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(done)
+      : "r"(smem_u32(bar)), "r"(parity)
       : "memory");
+  return done != 0;
 }
-__device__ __forceinline__ void umma_commit(unsigned long long* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+// arrive without release semantics: the arriving thread's earlier global reductions need not have been
+// performed before the barrier flips (a releasing arrive waits for them to drain)
+__device__ __forceinline__ void mbar_arrive_relaxed(unsigned long long* bar, uint32_t after) {
+  asm volatile("mbarrier.arrive.relaxed.cta.shared::cta.b64 _, [%0];  // %1" ::"r"(smem_u32(bar)), "r"(after) : "memory");
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
-  uint32_t r[16];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr)
-      : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+
+// first position of each id among n positions (p = lane + 32 k) and whether the id occurs more than once,
+// through a shared-memory hash set: claim a slot for the id (CAS), atomicMin the position and count the
+// occurrence in it, read both back. The K first-probe CAS of a lane are issued together (independent
+// shared-memory atomics pipeline); only ids whose first slot is taken by another id walk on.
+// identity: no folding (every position is its own leader).
+template <int K, int kSlots>
+__device__ __forceinline__ void tile_leaders(const uint32_t (&id)[K], uint32_t* keys, uint32_t* pos, uint32_t* cnt,
+                                             uint32_t (&lead)[K], uint32_t (&dup)[K], int lane, bool identity) {
+  uint32_t h[K], old[K];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float (&v)[4]) {
-  uint32_t r[4];
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr) : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+  for (int k = 0; k < K; ++k) {
+    h[k] = (id[k] * 0x9E3779B1u) >> 16 & (kSlots - 1);
+    old[k] = id[k];
+    if (!identity && id[k] != SSB_INVALID_SLOT) old[k] = atomicCAS(keys + h[k], 0xFFFFFFFFu, id[k]);
+  }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) v[i] = __uint_as_float(r[i]);
-}
-__device__ __forceinline__ void tma_gather4(uint32_t dst_smem, const CUtensorMap* map, unsigned long long* bar,
-                                            int col, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes"
-      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
-      ::"r"(dst_smem), "l"((uint64_t)map), "r"(smem_u32(bar)), "r"(col), "r"(r0), "r"(r1), "r"(r2), "r"(r3)
-      : "memory");
-}
-
-// ---- descriptors ------------------------------------------------------------------------------
-// Shared-memory matrix descriptor, 128-byte swizzle (layout_type 2), version 1 (Blackwell).
-__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
-  return d;
-}
-// Instruction descriptor: D=f32, A=B=bf16, dense.
-__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
-         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+  for (int k = 0; k < K; ++k) {
+    if (identity || id[k] == SSB_INVALID_SLOT) { h[k] = 0xFFFFFFFFu; continue; }
+    if (old[k] != 0xFFFFFFFFu && old[k] != id[k]) {        // first slot belongs to another id: linear probing
+      uint32_t s = h[k];
+      h[k] = 0xFFFFFFFFu;
+#pragma unroll 1
+      for (int probes = 1; probes < kSlots; ++probes) {
+        s = (s + 1) & (kSlots - 1);
+        const uint32_t o = atomicCAS(keys + s, 0xFFFFFFFFu, id[k]);
+        if (o == 0xFFFFFFFFu || o == id[k]) { h[k] = s; break; }
+      }
+    }
+    if (h[k] != 0xFFFFFFFFu) { atomicMin(pos + h[k], (uint32_t)(lane + 32 * k)); atomicAdd(cnt + h[k], 1u); }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const uint32_t p = lane + 32 * k;
+    lead[k] = h[k] != 0xFFFFFFFFu ? pos[h[k]] : p;
+    dup[k] = (h[k] != 0xFFFFFFFFu && cnt[h[k]] > 1u) ? 1u : 0u;
+  }
 }
 
-// byte offset of element (row r, bf16 column c) inside an [R rows] matrix stored as column blocks
-// of 64 bf16, each block [R x 128 B] with the 128-byte swizzle (16-byte chunk index ^= row % 8).
-__device__ __forceinline__ uint32_t swz_off(uint32_t r, uint32_t c, uint32_t blk_bytes) {
-  uint32_t cb = c >> 6, ch = (c & 63) >> 3, e = c & 7;
-  return cb * blk_bytes + r * 128 + ((ch ^ (r & 7)) << 4) + (e << 1);
-}
-
-// Direct ("fused pull") mode: the TMA gathers operand rows straight from the peer-mapped bf16 mirror of
-// the sharded table — local HBM or a peer's over NVLink — instead of from the worker's cache. All
-// shards sit side by side in one virtual range (parallel/peer.py), so ONE tensor map with a 256-byte
-// row pitch describes the whole distributed table: row = shard * shard_rows + mirror_row_off + slot.
-struct DirectMap {
-  const uint32_t* gslot;      // cache row -> global slot (shard * capacity + slot); nullptr = cache mode
-  uint32_t capacity;          // slots per shard
-  uint32_t shard_rows;        // 256-byte rows per shard segment
-  uint32_t mirror_row_off;    // first mirror row inside a segment
-};
-
-// ---- the kernel -------------------------------------------------------------------------------
-// Warp roles: warps 0..15 = consumers (thread 0 issues the MMAs, all 512 threads run the TMEM
-// epilogues: warp w owns TMEM lanes 32*(w%4).. and column part w/4), warp 16 = producer
-// (row indices + TMA gather4 of the NEXT tile while the current one is computed; 2 stages).
-// mode 0: producer copies rows with vector loads + swizzled st.shared; mode 1: TMA tile::gather4.
-__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory"); }
-__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-
-// kDiag (mode bit 4, experimental): epilogue 1 walks each row's context band by diagonal instead of by
-// column block — see the comment at the epilogue.
-template <bool kDiag>
 __global__ void __maxnreg__(64)
-sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict__ grads,
-                     const uint32_t* __restrict__ inv_in, const uint32_t* __restrict__ inv_out,
-                     int n_tok, int sent_len, int window, uint64_t seed, uint64_t offset,
-                     const uint32_t* __restrict__ neg_idx, float neg_k, float* __restrict__ loss_out,
-                     const __grid_constant__ CUtensorMap tmap, int mode, float* __restrict__ debug, const DirectMap dm) {
+sgns_block_tc_kernel(const __grid_constant__ TcArgs a, const __grid_constant__ CUtensorMap tmap) {
   extern __shared__ __align__(1024) uint8_t smem[];
   Misc* misc = reinterpret_cast<Misc*>(smem + kOffMisc);
   const uint32_t sbase = smem_u32(smem);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n_tok = a.n_tok;
   const int n_tiles = (n_tok + kM - 1) / kM;
+  const uint32_t n_my = ((uint32_t)n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;   // tiles of this CTA (>= 1)
+  const int mode = a.mode;
 
   if (tid == 0) {
-    mbar_init(&misc->full_bar[0], 1);
-    mbar_init(&misc->full_bar[1], 1);
+    // TMA gather: one arrival (expect_tx) + byte count; cp.async gather: one deferred arrival per gather thread
+    const uint32_t full_count = (mode & 32) ? kGatherWarps * 32 : 1;
+    mbar_init(&misc->full_bar[0], full_count);
+    mbar_init(&misc->full_bar[1], full_count);
+    mbar_init(&misc->idx_bar[0], 1);
+    mbar_init(&misc->idx_bar[1], 1);
     mbar_init(&misc->empty_bar[0], 1);
     mbar_init(&misc->empty_bar[1], 1);
     mbar_init(&misc->lead_bar[0], 1);
     mbar_init(&misc->lead_bar[1], 1);
-    mbar_init(&misc->mma_bar, 1);
+    mbar_init(&misc->win_bar[0], kGatherWarps);
+    mbar_init(&misc->win_bar[1], kGatherWarps);
+    mbar_init(&misc->rows_bar[0], 1);
+    mbar_init(&misc->rows_bar[1], 1);
+    mbar_init(&misc->rows_bar[2], 1);
+    mbar_init(&misc->g_full[0], kE1Warps);
+    mbar_init(&misc->g_full[1], kE1Warps);
+    mbar_init(&misc->s_full, 1);
+    mbar_init(&misc->s_free, kE1Warps);
+    mbar_init(&misc->g_free, 1);
+    mbar_init(&misc->g_zero, kGatherWarps);
+    mbar_init(&misc->d_full, 1);
+    mbar_init(&misc->d_free, kE2Warps);
     fence_barrier_init();
   }
   if (warp == 0) tmem_alloc(&misc->tmem_base, kTmemCols);
-  // G starts all-zero; each tile rewrites only the band windows and the negative columns
-  for (uint32_t i = tid; i < kGBlks * kInBlk / 16; i += kThreads)
-    reinterpret_cast<float4*>(smem + kOffG)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-  fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = misc->tmem_base;
 
-  if (warp == kConsumerWarps) {
+  if (warp == kProducerWarp) {
     // =========================== producer warp ===========================================
-    // Per tile: (wait for the stage) -> publish the row indices -> start the gather (TMA) ->
-    // prefetch the NEXT tile's indices into registers -> tile-local dedup -> signal lead_bar.
-    // The dedup and the index prefetch run while the TMA engine fills the stage.
-    uint32_t ri[4], ro[5], ti[4], to[5];
+    // Per tile: (wait for the stage) -> publish the gather indices -> start the gather (TMA, or hand over to
+    // the cp.async warps) -> everything the epilogues need that depends only on the indices: tile-local dedup
+    // (leaders, duplicate flags), each centre's shrunk window and sentence bounds as a column range, the
+    // gradient destination rows -> signal lead_bar -> prefetch the NEXT tile's indices into registers.
+    DedupScratch* ds = reinterpret_cast<DedupScratch*>(smem + kOffDedup);
+    const DirectMap dm = a.dm;
+    uint32_t ri[4], ro[5], ti[4], to[5];      // this tile
+    uint32_t nri[4], nro[5], nti[4], nto[5];  // next tile (prefetched while this one is processed)
     auto tab_row = [&](uint32_t cache_row) -> uint32_t {
       if (dm.gslot == nullptr || cache_row == SSB_INVALID_SLOT) return cache_row;
       const uint32_t g = __ldg(dm.gslot + cache_row);
@@ -249,7 +224,7 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const int g = t0 + lane + 32 * k;
-        ri[k] = (tile < n_tiles && g < n_tok) ? __ldg(inv_in + g) : SSB_INVALID_SLOT;
+        nri[k] = (tile < n_tiles && g < n_tok) ? __ldg(a.inv_in + g) : SSB_INVALID_SLOT;
       }
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
@@ -258,24 +233,32 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
         if (tile < n_tiles) {
           if (r < kCtx) {
             const int g = t0 - kHalo + r;
-            if (g >= 0 && g < n_tok) v = __ldg(inv_out + g);
+            if (g >= 0 && g < n_tok) v = __ldg(a.inv_out + g);
           } else {
-            v = __ldg(neg_idx + (size_t)tile * kNeg + (r - kCtx));
+            v = __ldg(a.neg_idx + (size_t)tile * kNeg + (r - kCtx));
           }
         }
-        ro[k] = v;
+        nro[k] = v;
       }
 #pragma unroll
-      for (int k = 0; k < 4; ++k) ti[k] = tab_row(ri[k]);
+      for (int k = 0; k < 4; ++k) nti[k] = tab_row(nri[k]);
 #pragma unroll
-      for (int k = 0; k < 5; ++k) to[k] = tab_row(ro[k]);
+      for (int k = 0; k < 5; ++k) nto[k] = tab_row(nro[k]);
+    };
+    auto take_idx = [&]() {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { ri[k] = nri[k]; ti[k] = nti[k]; }
+#pragma unroll
+      for (int k = 0; k < 5; ++k) { ro[k] = nro[k]; to[k] = nto[k]; }
     };
     load_idx(blockIdx.x);
-    uint32_t it = 0;
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+    for (uint32_t it = 0; it < n_my; ++it) {
+      const int tile = blockIdx.x + it * gridDim.x;
       const int b = it & 1;
       const int t0 = tile * kM;
-      if (it >= 2) mbar_wait(&misc->empty_bar[b], ((it >> 1) - 1) & 1);   // stage freed by the MMAs of tile it-2
+      take_idx();
+      load_idx(tile + gridDim.x);   // next tile's indices: in flight during everything below
+      if (it >= 2) mbar_wait(&misc->empty_bar[b], ((it >> 1) - 1) & 1);   // stage freed by the gradient MMAs of tile it-2
       bool bad = false;
       if (dm.gslot != nullptr) {
         // Masked-out positions still feed the MMAs (weight 0 in G), so they must gather FINITE data:
@@ -295,11 +278,10 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
         for (int k = 0; k < 5; ++k) if (to[k] == SSB_INVALID_SLOT) to[k] = fb;
       }
 #pragma unroll
-      for (int k = 0; k < 4; ++k) { misc->in_row[b][lane + 32 * k] = ri[k]; misc->in_tab[b][lane + 32 * k] = ti[k]; }
+      for (int k = 0; k < 4; ++k) misc->in_tab[b][lane + 32 * k] = ti[k];
 #pragma unroll
       for (int k = 0; k < 5; ++k) {
         const int r = lane + 32 * k;
-        misc->on_row[b][r] = ro[k];
         misc->on_tab[b][r] = to[k];
         const int g = t0 - kHalo + r;
         bad = bad || (r < kCtx && g >= 0 && g < n_tok && ro[k] == SSB_INVALID_SLOT);
@@ -308,7 +290,11 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
       if (lane == 0) misc->ctx_has_invalid[b] = any_bad ? 1u : 0u;
       __syncwarp();
       const uint32_t in_base = kOffIn + b * kInBytes, on_base = kOffOn + b * kOnBytes;
-      if (mode & 1) {
+      if (mode & 32) {
+        if (lane == 0) mbar_arrive(&misc->idx_bar[b]);     // the gather warps take it from here
+      } else if (mode & 16) {
+        if (lane == 0) mbar_arrive(&misc->full_bar[b]);    // perf experiment: no gather at all (operands are garbage)
+      } else if (mode & 1) {
         if (lane == 0) mbar_expect_tx(&misc->full_bar[b], (kM + kN) * kD * 2);
         __syncwarp();
         // 72 groups of 4 rows (32 In + 40 ON), each 2 column blocks; spread over the lanes
@@ -325,14 +311,14 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
           tma_gather4(dst + blk, &tmap, &misc->full_bar[b], 64, i0, i1, i2, i3);
         }
       } else {
-        // half a warp per row: 16 lanes x 16 B = 256 B of bf16
+        // bring-up / fallback path: half a warp per row: 16 lanes x 16 B = 256 B of bf16
         for (int r = lane >> 4; r < kM + kN; r += 2) {
           const bool is_in = r < kM;
           const uint32_t rr = is_in ? r : r - kM;
           const int l16 = lane & 15;
           uint32_t row = is_in ? misc->in_tab[b][rr] : misc->on_tab[b][rr];
           uint4 v = make_uint4(0u, 0u, 0u, 0u);
-          if (row != SSB_INVALID_SLOT) v = *reinterpret_cast<const uint4*>(params + (size_t)row * kD + l16 * 8);
+          if (row != SSB_INVALID_SLOT) v = *reinterpret_cast<const uint4*>(a.params + (size_t)row * kD + l16 * 8);
           uint32_t off = (is_in ? in_base : on_base) + swz_off(rr, l16 * 8, is_in ? kInBlk : kOnBlk);
           *reinterpret_cast<uint4*>(smem + off) = v;
         }
@@ -340,306 +326,355 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
         __syncwarp();
         if (lane == 0) mbar_arrive(&misc->full_bar[b]);
       }
-      // tile-local dedup: lead[p] = first position with the same row id. Duplicate positions fold
-      // their dL/dS entries into the leader's row/column of G, so every distinct row gets ONE
-      // gradient reduction per tile (hot words would otherwise serialise on the same address).
+      // tile-local dedup: lead = first position with the same row id. Duplicate positions fold their dL/dS
+      // entries into the leader's row / column of G, so every distinct row gets ONE gradient reduction per
+      // tile (hot words would otherwise serialise on the same address in L2).
+      uint32_t lead_i[4], dup_i[4], lead_o[5], dup_o[5];
       {
-        int ld[5];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) ld[k] = lane + 32 * k;
-        for (int j = 0; j < kM; ++j) {
-          const uint32_t x = misc->in_row[b][j];
-#pragma unroll
-          for (int k = 0; k < 4; ++k) if (ri[k] == x) ld[k] = min(ld[k], j);
+        const bool identity = (mode & 64) != 0;     // perf experiment: no tile-local dedup
+        if (!identity) {
+          uint4* z = reinterpret_cast<uint4*>(ds);
+          constexpr int kOnes = (int)(offsetof(DedupScratch, cnt_in) / 16), kAll = (int)(sizeof(DedupScratch) / 16);
+          for (int x = lane; x < kOnes; x += 32) z[x] = make_uint4(~0u, ~0u, ~0u, ~0u);
+          for (int x = kOnes + lane; x < kAll; x += 32) z[x] = make_uint4(0u, 0u, 0u, 0u);
+          __syncwarp();
         }
+        tile_leaders<4, 256>(ri, ds->key_in, ds->pos_in, ds->cnt_in, lead_i, dup_i, lane, identity);
+        tile_leaders<5, 512>(ro, ds->key_on, ds->pos_on, ds->cnt_on, lead_o, dup_o, lane, identity);
+      }
+      uint32_t* orow = misc->out_rows[it % 3];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) misc->lead_in[b][lane + 32 * k] = (uint8_t)ld[k];
+      for (int k = 0; k < 4; ++k) {
+        const int p = lane + 32 * k;
+        misc->row_lead[b][p] = (uint16_t)(lead_i[k] | (dup_i[k] << 8));
+        orow[p] = (lead_i[k] == (uint32_t)p) ? ri[k] : SSB_INVALID_SLOT;
+      }
 #pragma unroll
-        for (int k = 0; k < 5; ++k) ld[k] = lane + 32 * k;
-        for (int j = 0; j < kN; ++j) {
-          const uint32_t x = misc->on_row[b][j];
-#pragma unroll
-          for (int k = 0; k < 5; ++k) if (ro[k] == x) ld[k] = min(ld[k], j);
-        }
-#pragma unroll
-        for (int k = 0; k < 5; ++k) misc->lead_on[b][lane + 32 * k] = (uint8_t)ld[k];
+      for (int k = 0; k < 5; ++k) {
+        const int c = lane + 32 * k;
+        misc->col_meta[b][c] = (uint16_t)(lead_o[k] | (dup_o[k] << 8) | (ro[k] == SSB_INVALID_SLOT ? 0x200u : 0u));
+        orow[kM + c] = (lead_o[k] == (uint32_t)c) ? ro[k] : SSB_INVALID_SLOT;
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(&misc->lead_bar[b]);
-      load_idx(tile + gridDim.x);   // next tile's indices, in flight while the consumers work
+      if (lane == 0) { mbar_arrive(&misc->lead_bar[b]); mbar_arrive(&misc->rows_bar[it % 3]); }
     }
-  } else {
-    // =========================== consumer warps ==========================================
-    const int q = warp & 3, part = warp >> 2;       // TMEM lane quarter, column part
-    const int i = q * 32 + lane;                    // tile row = TMEM lane
-    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
-    uint32_t mma_phase = 0, it = 0;
-    float loss_acc = 0.f, pair_acc = 0.f;
-
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
-      const int b = it & 1;
-      const int t0 = tile * kM;
+  } else if (warp == kMmaWarp) {
+    // =========================== MMA issue ================================================
+    // The whole warp walks the loop (so it stays converged up to the teardown barrier); lane 0 polls
+    // the barriers, issues the MMAs and commits.
+    constexpr uint32_t idesc_s = make_idesc(kM, kN, 0, 0);
+    constexpr uint32_t idesc_din = make_idesc(kD, kM, 1, 0);
+    constexpr uint32_t idesc_don = make_idesc(kD, kGCols, 1, 1);
+    const uint32_t g_s = sbase + kOffG;
+    auto issue_s = [&](uint32_t it) {
+      const uint32_t b = it & 1;
       const uint32_t in_s = sbase + kOffIn + b * kInBytes, on_s = sbase + kOffOn + b * kOnBytes;
-      mbar_wait(&misc->full_bar[b], (it >> 1) & 1);
-
-      // ---- S = In . ON^T --------------------------------------------------------------------
-      if (tid == 0) {
-        tc_fence_after();
-        constexpr uint32_t idesc = make_idesc(kM, kN, 0, 0);
 #pragma unroll
-        for (int s = 0; s < kD / 16; ++s) {
-          uint64_t a = make_desc(in_s + (s >> 2) * kInBlk + (s & 3) * 32, 16, 1024);
-          uint64_t bd = make_desc(on_s + (s >> 2) * kOnBlk + (s & 3) * 32, 16, 1024);
-          umma_bf16(tmem + kTmemS, a, bd, idesc, s > 0);
-        }
-        umma_commit(&misc->mma_bar);
+      for (int s = 0; s < kD / 16; ++s) {
+        const uint64_t ad = make_desc(in_s + (s >> 2) * kInBlk + (s & 3) * 32, 16, 1024);
+        const uint64_t bd = make_desc(on_s + (s >> 2) * kOnBlk + (s & 3) * 32, 16, 1024);
+        umma_bf16(tmem + kTmemS, ad, bd, idesc_s, s > 0);
       }
-      mbar_wait(&misc->mma_bar, mma_phase);
-      mma_phase ^= 1;
+      umma_commit(&misc->s_full);
+    };
+    auto issue_grads = [&](uint32_t it) {
+      const uint32_t b = it & 1;
+      const uint32_t in_s = sbase + kOffIn + b * kInBytes, on_s = sbase + kOffOn + b * kOnBytes;
+      // dIn^T [D x 128 tokens] = ON^T . G^T : K = 160 context/negative rows, 16 per step
+#pragma unroll
+      for (int s = 0; s < kN / 16; ++s) {
+        const uint64_t ad = make_desc(on_s + s * 2048, kOnBlk, 1024);                                   // ON, MN-major
+        const uint64_t bd = make_desc(g_s + (s >> 2) * kInBlk + (s & 3) * 32, 16, 1024);               // G rows = N, K-major
+        umma_bf16(tmem + kTmemDIn, ad, bd, idesc_din, s > 0);
+      }
+      // dON^T [D x 192] = In^T . G : K = 128 centre tokens, 16 per step
+#pragma unroll
+      for (int s = 0; s < kM / 16; ++s) {
+        const uint64_t ad = make_desc(in_s + s * 2048, kInBlk, 1024);                                   // In, MN-major
+        const uint64_t bd = make_desc(g_s + s * 2048, kInBlk, 1024);                                    // G, MN-major
+        umma_bf16(tmem + kTmemDOn, ad, bd, idesc_don, s > 0);
+      }
+      umma_commit(&misc->empty_bar[b]);   // the stage's In / ON are free once these MMAs retire
+      umma_commit(&misc->g_free);
+      umma_commit(&misc->d_full);
+    };
+    if (lane == 0) {
+      mbar_wait(&misc->full_bar[0], 0);
+      if (mode & 32) fence_proxy_async();   // rows written by cp.async (generic proxy) -> tensor core (async proxy)
       tc_fence_after();
-
-      // Gradient destination rows for epilogue 2, copied out of the stage's index arrays now (the
-      // producer may refill them as soon as the gradient MMAs retire). Non-leaders are skipped:
-      // their contribution has been folded into the leader's row / column of G.
-      mbar_wait(&misc->lead_bar[b], (it >> 1) & 1);
-      if (tid < kM) {
-        misc->out_rows[tid] = (misc->lead_in[b][tid] == tid) ? misc->in_row[b][tid] : SSB_INVALID_SLOT;
-      } else if (tid < kM + kN) {
-        const int c = tid - kM;
-        misc->out_rows[tid] = (misc->lead_on[b][c] == c) ? misc->on_row[b][c] : SSB_INVALID_SLOT;
-      }
-
-      // ---- epilogue 1: logits -> loss and dL/dS. Column part p owns band block p (16 of the 48
-      //      window columns; part 3 has none) and negatives [4p, 4p+4) -------------------------
-      {
-        const int gi = t0 + i;
-        const uint32_t my_in = misc->in_row[b][i];
-        const bool row_ok = my_in != SSB_INVALID_SLOT;
-        const uint32_t li = misc->lead_in[b][i];
-        int eff = 0;
-        if (row_ok) {
-          uint32_t r4[4];
-          Philox::gen(seed, offset + (uint64_t)gi, r4);
-          eff = window - (int)(r4[0] % (uint32_t)window);
+      issue_s(0);
+    }
+    __syncwarp();
+    uint32_t s_next = 1, g_next = 0, idle = 0;
+    while (g_next < n_my) {
+      int can_s = 0, can_g = 0;
+      if (lane == 0) {
+        // S of the next tile: its operands have landed and epilogue 1 has taken S of the previous tile
+        can_s = s_next < n_my && s_next <= g_next + 1 && mbar_test(&misc->full_bar[s_next & 1], (s_next >> 1) & 1) &&
+                mbar_test(&misc->s_free, (s_next - 1) & 1);
+        // gradient MMAs: G is written and epilogue 2 has taken the previous tile's accumulators
+        const bool gf = mbar_test(&misc->g_full[g_next & 1], (g_next >> 1) & 1);
+        const bool df = g_next == 0 || mbar_test(&misc->d_free, (g_next - 1) & 1);
+        can_g = gf && df;
+        // nothing to issue: sleep (in hardware, no issue slots) on the barrier the gradient MMAs still wait for
+        if (!can_s && !can_g) {
+          if (!gf) mbar_try(&misc->g_full[g_next & 1], (g_next >> 1) & 1, 300u);
+          else mbar_try(&misc->d_free, (g_next - 1) & 1, 300u);
         }
-        const int s_lo = (gi / sent_len) * sent_len;
-        const int tok_lo = max(s_lo, 0), tok_hi = min(s_lo + sent_len, n_tok);
-        // column c <-> token t0 - 8 + c ; centre i <-> column i + 8. Valid context columns of row i
-        // form one range [c_lo, c_hi] minus the centre itself (plus, rarely, INVALID rows inside it).
-        const int self_c = i + kHalo;
+      }
+      can_s = __shfl_sync(0xffffffffu, can_s, 0);
+      can_g = __shfl_sync(0xffffffffu, can_g, 0);
+      if (can_s) {
+        if (lane == 0) { if (mode & 32) fence_proxy_async(); tc_fence_after(); issue_s(s_next); }
+        ++s_next;
+      }
+      if (can_g) {
+        if (lane == 0) { tc_fence_after(); issue_grads(g_next); }
+        ++g_next;
+      }
+      __syncwarp();
+      if (can_s || can_g) { idle = 0; continue; }
+      if (++idle > (1u << 23)) __trap();   // bounded: a lost arrival is a launch failure, not a hang
+    }
+  } else if (warp >= kGatherWarp0) {
+    // =========================== helper warps ==============================================
+    // (a) mode bit 32: gather the tile's 288 rows with 16-byte cp.async.cg (L2 -> shared memory, no
+    // registers), 16 threads per 256-byte row, writing the 128-byte swizzle themselves; each thread's copies
+    // arrive on the stage's full barrier when they have landed (cp.async.mbarrier.arrive.noinc).
+    // (b) always: zero G for the next tile as soon as the gradient MMAs that read it have retired, so that
+    // epilogue 1 only has to drop its few non-zero entries in.
+    const int gt = tid - kGatherWarp0 * 32;
+    const uint32_t ch = gt & 15, r_off = gt >> 4;
+    const uint32_t sw_lo = (ch >> 3), sw_ch = ch & 7;
+    const char* src_base = reinterpret_cast<const char*>(a.params) + ch * 16;
+    const int window = a.window, sent_len = a.sent_len;
+    for (uint32_t it = 0; it < n_my; ++it) {
+      const int b = it & 1;
+      const int t0 = (blockIdx.x + it * gridDim.x) * kM;
+      // (c) helper thread gt owns centre row gt of the tile: its shrunk window (Philox, one draw per token
+      // position) and sentence bounds as the range of valid context columns [c_lo, c_hi] (column c <-> token
+      // t0 - 8 + c; the centre itself sits at column gt + 8). Needs nothing but the token's validity, read from
+      // global memory; issued here so the load is in flight during the gather.
+      const int gi = t0 + gt;
+      const uint32_t my_row = gi < n_tok ? __ldg(a.inv_in + gi) : SSB_INVALID_SLOT;
+      if (mode & 32) {
+        mbar_wait(&misc->idx_bar[b], (it >> 1) & 1);
+        const uint32_t in_dst = sbase + kOffIn + b * kInBytes + sw_lo * kInBlk;
+        const uint32_t on_dst = sbase + kOffOn + b * kOnBytes + sw_lo * kOnBlk;
+#pragma unroll 4
+        for (uint32_t r = r_off; r < (uint32_t)kM; r += 8) {
+          uint32_t row = misc->in_tab[b][r];
+          row = row == SSB_INVALID_SLOT ? 0u : row;
+          const uint32_t dst = in_dst + r * 128 + ((sw_ch ^ (r & 7)) << 4);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src_base + (size_t)row * (kD * 2)) : "memory");
+        }
+#pragma unroll 4
+        for (uint32_t r = r_off; r < (uint32_t)kN; r += 8) {
+          uint32_t row = misc->on_tab[b][r];
+          row = row == SSB_INVALID_SLOT ? 0u : row;
+          const uint32_t dst = on_dst + r * 128 + ((sw_ch ^ (r & 7)) << 4);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src_base + (size_t)row * (kD * 2)) : "memory");
+        }
+        asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&misc->full_bar[b])) : "memory");
+      }
+      {
+        // row_win[b] of tile it-2 was last read by epilogue 1 before g_full(it-2); this warp has seen
+        // g_free(it-2) (it zeroed G after it), so the slot is free
         int c_lo = 1, c_hi = 0;
-        if (row_ok) {
-          c_lo = max(gi - eff, tok_lo) - (t0 - kHalo);
+        if (my_row != SSB_INVALID_SLOT) {
+          uint32_t r4[4];
+          Philox::gen(a.seed, a.offset + (uint64_t)gi, r4);
+          const int eff = window - (int)(r4[0] % (uint32_t)window);
+          const int s_lo = (gi / sent_len) * sent_len;
+          const int tok_hi = min(s_lo + sent_len, n_tok);
+          c_lo = max(gi - eff, s_lo) - (t0 - kHalo);
           c_hi = min(gi + eff, tok_hi - 1) - (t0 - kHalo);
         }
-        const bool chk_rows = misc->ctx_has_invalid[b] != 0;
-        auto col_ok = [&](int c) -> bool {
-          return c >= c_lo && c <= c_hi && c != self_c && (!chk_rows || misc->on_row[b][c] != SSB_INVALID_SLOT);
-        };
-        // G[lead(i)][lead(c)] += g   (bf16x2 shared-memory reduction; G was zeroed by the previous tile)
-        auto g_add = [&](int c, float g) {
-          const uint32_t lc = misc->lead_on[b][c];
-          __nv_bfloat162 pk = (lc & 1) ? __floats2bfloat162_rn(0.f, g) : __floats2bfloat162_rn(g, 0.f);
-          const uint32_t addr = sbase + kOffG + swz_off(li, lc & ~1u, kInBlk);
-          asm volatile("red.shared::cta.add.noftz.bf16x2 [%0], %1;" ::"r"(addr), "r"(*reinterpret_cast<uint32_t*>(&pk)) : "memory");
-        };
-        // one exp per logit: t = 1 + e^-x ; sigmoid = 1/t ; -log sigmoid(x) = log t ; softplus(x) = x + log t
-        auto sig_logt = [](float x, float& sig, float& logt) {
-          x = fminf(fmaxf(x, -30.f), 30.f);
-          const float t = 1.0f + exp2f(-1.4426950408889634f * x);
-          sig = __frcp_rn(t);
-          logt = 0.6931471805599453f * __log2f(t);
-        };
-        if constexpr (!kDiag) {
-          if (part < 3) {
-            float v[16];
-            const int c0 = q * 32 + part * 16;          // band window of this lane quarter: [32q, 32q+48)
-            tmem_ld16(lane_base + kTmemS + c0, v);
-  #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              if (col_ok(c0 + j)) {
-                float sg, lt;
-                sig_logt(v[j], sg, lt);
-                g_add(c0 + j, sg - 1.0f);
-                loss_acc += lt;
-                pair_acc += 1.f;
-              }
-            }
-          }
-          {
-            // negatives: weight m_i * K / 16 each, m_i = number of valid contexts of centre i. The 16
-            // negatives are split 4/2/4/6 over the column parts to even out the band work (the
-            // middle band block holds most of a row's valid contexts, part 3 has no band block).
-            float m_i = 0.f;
-            if (row_ok) {
-              if (chk_rows) {
-  #pragma unroll
-                for (int c = 0; c <= 2 * kHalo; ++c) m_i += col_ok(i + c) ? 1.f : 0.f;
-              } else {
-                m_i = (float)max(c_hi - c_lo, 0);
-              }
-            }
-            const int n_lo = (part == 0) ? 0 : (part == 1) ? 4 : (part == 2) ? 6 : 10;
-            const int n_hi = (part == 0) ? 4 : (part == 1) ? 6 : (part == 2) ? 10 : 16;
-            float v[16];
-            tmem_ld16(lane_base + kTmemS + kCtx, v);
-            const float w = m_i * neg_k * (1.0f / kNeg);
-            if (m_i > 0.f) {
-  #pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                if (j >= n_lo && j < n_hi && misc->on_row[b][kCtx + j] != SSB_INVALID_SLOT) {
-                  float sg, lt;
-                  sig_logt(v[j], sg, lt);
-                  g_add(kCtx + j, w * sg);
-                  loss_acc += w * (v[j] + lt);
-                }
-              }
-            }
-          }
-} else {
-          // Diagonal form. In the column-block form above a warp runs the sigmoid path for each of its 16
-          // columns with only the ~1/3 of its lanes whose band contains that column. Here the band warps
-          // hold the whole 48-column window of their lane quarter (indexed per lane, so it lives in local
-          // memory) and step through the OFFSETS a = 1..window on one side of the centre: lane i looks at
-          // column i + 8 -/+ a, so every lane whose window reaches that far works in the same iteration.
-          // part 0: left side, part 1: right side, parts 2 and 3: eight negatives each.
-          if (part < 2) {
-            float v[48];
-            const int cq = q * 32;
-            {
-              float t16[16];
-#pragma unroll
-              for (int blk = 0; blk < 3; ++blk) {
-                tmem_ld16(lane_base + kTmemS + cq + blk * 16, t16);
-#pragma unroll
-                for (int j = 0; j < 16; ++j) v[blk * 16 + j] = t16[j];
-              }
-            }
-            const int sgn = (part == 0) ? -1 : 1;
-            for (int a = 1; a <= window; ++a) {
-              const int c = self_c + sgn * a;            // in [cq, cq + 48) for every lane: lane + 8 -/+ a, a <= 8
-              if (col_ok(c)) {
-                float sg, lt;
-                sig_logt(v[c - cq], sg, lt);
-                g_add(c, sg - 1.0f);
-                loss_acc += lt;
-                pair_acc += 1.f;
-              }
-            }
-          } else {
-            float m_i = 0.f;
-            if (row_ok) {
-              if (chk_rows) {
-#pragma unroll
-                for (int c = 0; c <= 2 * kHalo; ++c) m_i += col_ok(i + c) ? 1.f : 0.f;
-              } else {
-                m_i = (float)max(c_hi - c_lo, 0);
-              }
-            }
-            const int n_lo = (part == 2) ? 0 : 8, n_hi = n_lo + 8;
-            float v[16];
-            tmem_ld16(lane_base + kTmemS + kCtx, v);
-            const float w = m_i * neg_k * (1.0f / kNeg);
-            if (m_i > 0.f) {
-#pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                if (j >= n_lo && j < n_hi && misc->on_row[b][kCtx + j] != SSB_INVALID_SLOT) {
-                  float sg, lt;
-                  sig_logt(v[j], sg, lt);
-                  g_add(kCtx + j, w * sg);
-                  loss_acc += w * (v[j] + lt);
-                }
-              }
-            }
-          }
-        }
-        fence_proxy_async();
-        tc_fence_before();
+        misc->row_win[b][gt] = (uint16_t)((uint32_t)c_lo | ((uint32_t)c_hi << 8));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&misc->win_bar[b]);
       }
-      consumer_sync();
-      if (debug && tile == 0)
-        for (uint32_t k = tid; k < kGBlks * kInBlk / 2; k += kConsumers)
-          debug[k] = __bfloat162float(reinterpret_cast<__nv_bfloat16*>(smem + kOffG)[k]);
-
-      // ---- dIn = G . ON ;  dON = G^T . In (rows 0..127 and 128..255) ---------------------------
-      if (tid == 0) {
-        tc_fence_after();
-        constexpr uint32_t idesc2 = make_idesc(kM, kD, 0, 1);
-#pragma unroll
-        for (int s = 0; s < kN / 16; ++s) {     // K = 160 context/negative rows, 16 per step
-          uint64_t a = make_desc(sbase + kOffG + (s >> 2) * kInBlk + (s & 3) * 32, 16, 1024);
-          uint64_t bd = make_desc(on_s + s * 2048, kOnBlk, 1024);
-          umma_bf16(tmem + kTmemDIn, a, bd, idesc2, s > 0);
-        }
-        constexpr uint32_t idesc3 = make_idesc(128, kD, 1, 1);
-#pragma unroll
-        for (int s = 0; s < kM / 16; ++s) {     // K = 128 centre tokens, 16 per step
-          uint64_t bd = make_desc(in_s + s * 2048, kInBlk, 1024);
-          uint64_t a0 = make_desc(sbase + kOffG + s * 2048, kInBlk, 1024);
-          uint64_t a1 = make_desc(sbase + kOffG + 2 * kInBlk + s * 2048, kInBlk, 1024);
-          umma_bf16(tmem + kTmemDOnA, a0, bd, idesc3, s > 0);
-          umma_bf16(tmem + kTmemDOnB, a1, bd, idesc3, s > 0);
-        }
-        umma_commit(&misc->empty_bar[b]);   // the stage's In / ON are free once these MMAs retire
-        umma_commit(&misc->mma_bar);
-      }
-      mbar_wait(&misc->mma_bar, mma_phase);
-      mma_phase ^= 1;
-      tc_fence_after();
-
-      if (debug && tile == 0 && part == 0) {
-        float* d1 = debug + kGBlks * kInBlk / 2;
-        for (int blk = 0; blk < 26; ++blk) {   // 416 columns: dONb | pad | dIn | dONa
-          float vv[16];
-          tmem_ld16(lane_base + blk * 16, vv);
-          for (int j = 0; j < 16; ++j) d1[(size_t)i * 416 + blk * 16 + j] = vv[j];
-        }
-      }
-
-      // ---- epilogue 2: TMEM -> fp32 staging in shared memory (the G region is dead now) -> one
-      //      coalesced 512-byte vector red per gradient row. TMEM holds a row per lane; staging
-      //      transposes that into a row per warp so 32 lanes reduce 32 x 16 contiguous bytes.
+      if (it >= 1) mbar_wait(&misc->g_free, (it - 1) & 1);
+      for (uint32_t z = gt; z < kGBytes / 16; z += kGatherWarps * 32)
+        reinterpret_cast<float4*>(smem + kOffG)[z] = make_float4(0.f, 0.f, 0.f, 0.f);
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&misc->g_zero);
+    }
+  } else if (warp < kE1Warps) {
+    // =========================== epilogue 1: logits -> loss and dL/dS ======================
+    // Warp (q, side): rows 32q..32q+31 (row = TMEM lane), the `side` half of each row's context band
+    // (0: offsets -8..-1, 1: +1..+8) and negatives [8 side, 8 side + 8). The band of row i is centred
+    // on column i + 8, i.e. it is skewed by the lane index; the 40 columns a warp loads are rotated by
+    // `lane` in registers (5 select stages) so that offset a sits at a fixed register for every lane
+    // and the warp walks the band by diagonal with all in-window lanes active together. Everything that
+    // depends only on the indices (window, sentence bounds, leaders) was prepared by the producer warp;
+    // the 16 logits of a thread go through the sigmoid as 16 independent, branch-free chains.
+    const int q = warp & 3, side = warp >> 2;
+    const int i = q * 32 + lane;                    // tile row = TMEM lane
+    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+    const int window = a.window;
+    const int self_c = i + kHalo;
+    float loss_acc = 0.f, pair_acc = 0.f;
+    for (uint32_t it = 0; it < n_my; ++it) {
+      const int b = it & 1, par = it & 1;
+      float v[40], xn[8];
       {
-        float* stage = reinterpret_cast<float*>(smem + kOffG);      // [128 rows][128 fp32], 16 B chunks swizzled by row
-        const uint32_t tcol[3] = {kTmemDIn, kTmemDOnA, kTmemDOnB};
-        const int nrows[3] = {kM, kM, kN - kM};
-        const int row_base[3] = {0, kM, 2 * kM};                    // into misc->out_rows
+        mbar_wait(&misc->s_full, it & 1);
+        tc_fence_after();
+        uint32_t r0[16], r1[16], r2[8], r3[8];
+        const uint32_t cb = lane_base + kTmemS + q * 32 + 8 * side;
+        tmem_ld16_issue(cb, r0);
+        tmem_ld16_issue(cb + 16, r1);
+        tmem_ld8_issue(cb + 32, r2);
+        tmem_ld8_issue(lane_base + kTmemS + kCtx + 8 * side, r3);
+        tmem_wait_ld16(r0);
+        tmem_wait_ld16(r1);
+        tmem_wait_ld8(r2);
+        tmem_wait_ld8(r3);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&misc->s_free);   // S may be overwritten by the next tile's MMA
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-          if (k < 2 || q == 0) {                                    // dON rows 128..159 live in lanes 0..31 only
+        for (int j = 0; j < 16; ++j) { v[j] = __uint_as_float(r0[j]); v[16 + j] = __uint_as_float(r1[j]); }
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              float v[16];
-              tmem_ld16(lane_base + tcol[k] + part * 32 + h * 16, v);
-#pragma unroll
-              for (int x4 = 0; x4 < 4; ++x4) {
-                const int chunk = part * 8 + h * 4 + x4;
-                *reinterpret_cast<float4*>(stage + i * kD + ((chunk ^ (i & 7)) << 2)) =
-                    make_float4(v[4 * x4], v[4 * x4 + 1], v[4 * x4 + 2], v[4 * x4 + 3]);
-              }
-            }
-          }
-          tc_fence_before();
-          consumer_sync();
-          for (int r = warp; r < nrows[k]; r += kConsumerWarps) {
-            const uint32_t row = misc->out_rows[row_base[k] + r];
-            if (row == SSB_INVALID_SLOT) continue;
-            const float4 x = *reinterpret_cast<const float4*>(stage + r * kD + ((lane ^ (r & 7)) << 2));
-            if ((x.x != 0.f || x.y != 0.f || x.z != 0.f || x.w != 0.f) && !(mode & 2))
-              red_add_f4_gpu(grads + (size_t)row * kD + lane * 4, x);
-          }
-          consumer_sync();
-        }
-        // leave G zeroed for the next tile (columns 0..191; block 3 is never read back)
-        for (uint32_t z = tid; z < 3 * kInBlk / 16; z += kConsumers)
-          reinterpret_cast<float4*>(smem + kOffG)[z] = make_float4(0.f, 0.f, 0.f, 0.f);
-        fence_proxy_async();
+        for (int j = 0; j < 8; ++j) { v[32 + j] = __uint_as_float(r2[j]); xn[j] = __uint_as_float(r3[j]); }
       }
-      consumer_sync();
+      // rotate left by `lane`: afterwards v[j] = S[i][32 q + 8 side + lane + j], j = 0..8
+#define SSB_ROT(SH, CNT)                                               \
+      {                                                                \
+        const bool p_ = (lane & SH) != 0;                              \
+        _Pragma("unroll") for (int j = 0; j < CNT; ++j) v[j] = p_ ? v[j + SH] : v[j]; \
+      }
+      SSB_ROT(16, 24) SSB_ROT(8, 16) SSB_ROT(4, 12) SSB_ROT(2, 10) SSB_ROT(1, 9)
+#undef SSB_ROT
+
+      mbar_wait(&misc->win_bar[b], (it >> 1) & 1);      // row_win of this stage (helper warps)
+      mbar_wait(&misc->lead_bar[b], (it >> 1) & 1);     // row_lead / col_meta of this stage (producer warp)
+      const uint32_t rlead = misc->row_lead[b][i], rwin = misc->row_win[b][i];
+      const uint32_t li = rlead & 0xFFu;
+      const bool row_dup = (rlead & 0x100u) != 0;
+      const int c_lo = (int)(rwin & 0xFFu), c_hi = (int)(rwin >> 8);
+      // this side's reach: offsets 1..reach are inside [c_lo, c_hi] (0 for an invalid row: c_lo > c_hi)
+      const int reach = (c_hi >= c_lo) ? (side ? c_hi - self_c : self_c - c_lo) : 0;
+      const uint16_t* cm = misc->col_meta[b];
+      // column metadata of the 8 band offsets and the 8 negatives (static offsets from a per-thread base)
+      uint32_t mb[8], mn[8];
+#pragma unroll
+      for (int aa = 1; aa <= kHalo; ++aa) mb[aa - 1] = cm[side ? self_c + aa : self_c - aa];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) mn[j] = cm[kCtx + 8 * side + j];
+      // m_i = number of valid contexts of centre i (both sides): the range minus the centre, minus INVALID rows
+      float m_i = (float)max(c_hi - c_lo, 0);
+      if (misc->ctx_has_invalid[b] != 0 && c_hi >= c_lo) {
+        m_i = 0.f;
+        for (int c = c_lo; c <= c_hi; ++c) m_i += (c != self_c && !(cm[c] & 0x200u)) ? 1.f : 0.f;
+      }
+      const float w = m_i * a.neg_k * (1.0f / kNeg);
+      // 16 independent sigmoid chains; gb/gn = dL/dS entries (0 where masked)
+      float gb[8], gn[8];
+      uint32_t bmask = 0, nmask = 0;
+#pragma unroll
+      for (int aa = 1; aa <= kHalo; ++aa) {
+        gb[aa - 1] = 0.f;
+        if (aa <= window) {                      // uniform: offsets beyond the window are never valid
+          const float x = side ? v[aa] : v[kHalo - aa];
+          float sg, lt;
+          sig_logt(x, sg, lt);
+          const bool ok = aa <= reach && !(mb[aa - 1] & 0x200u);
+          gb[aa - 1] = sg - 1.0f;
+          bmask |= ok ? (1u << (aa - 1)) : 0u;
+          loss_acc += ok ? lt : 0.f;
+          pair_acc += ok ? 1.f : 0.f;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float sg, lt;
+        sig_logt(xn[j], sg, lt);
+        const bool ok = m_i > 0.f && !(mn[j] & 0x200u);
+        gn[j] = w * sg;
+        nmask |= ok ? (1u << j) : 0u;
+        loss_acc += ok ? w * (xn[j] + lt) : 0.f;
+      }
+      // G has been zeroed by the helper warps (after the previous tile's gradient MMAs retired); drop the
+      // entries in:  G[lead(i)][lead(c)] (+)= g. A cell has ONE writer unless the row id or the column id occurs
+      // more than once in the tile: those few cells take the bf16x2 shared-memory reduction (a CAS loop in SASS),
+      // all others a plain 2-byte store.
+      mbar_wait(&misc->g_zero, it & 1);
+      const uint32_t g_row = sbase + kOffG + li * 128, rx = li & 7;
+      auto g_put = [&](uint32_t meta, float g) {
+        const uint32_t lc = meta & 0xFFu;
+        const uint32_t cell = g_row + (lc >> 6) * kInBlk + ((((lc >> 3) & 7) ^ rx) << 4) + ((lc & 7) << 1);
+        if (row_dup || (meta & 0x100u)) {
+          __nv_bfloat162 pk = (lc & 1) ? __floats2bfloat162_rn(0.f, g) : __floats2bfloat162_rn(g, 0.f);
+          asm volatile("red.shared::cta.add.noftz.bf16x2 [%0], %1;" ::"r"(cell & ~3u), "r"(*reinterpret_cast<uint32_t*>(&pk)) : "memory");
+        } else {
+          const __nv_bfloat16 hv = __float2bfloat16_rn(g);
+          asm volatile("st.shared.b16 [%0], %1;" ::"r"(cell), "h"(*reinterpret_cast<const unsigned short*>(&hv)) : "memory");
+        }
+      };
+#pragma unroll
+      for (int aa = 1; aa <= kHalo; ++aa)
+        if (bmask & (1u << (aa - 1))) g_put(mb[aa - 1], gb[aa - 1]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (nmask & (1u << j)) g_put(mn[j], gn[j]);
+      fence_proxy_async();     // G is read by the tensor core through the async proxy
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&misc->g_full[par]);
     }
     loss_acc = warp_sum(loss_acc);
     pair_acc = warp_sum(pair_acc);
     if (lane == 0) { misc->loss[warp] = loss_acc; misc->pairs[warp] = pair_acc; }
+  } else {
+    // =========================== epilogue 2: gradients TMEM -> red ==========================
+    // Warp (q, half): embedding dims 32q..32q+31 (dim = TMEM lane) of the gradient rows in columns
+    // [64 half, 64 half + 64) of dIn^T and [80 half, 80 half + 80) of dON^T. One column = one gradient
+    // row; the warp's 32 lanes hold 32 consecutive floats of it: one coalesced 128-byte red.
+    const int q = warp & 3, half = (warp >> 2) & 1;
+    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+    float* gdst = a.grads + q * 32 + lane;
+    for (uint32_t it = 0; it < n_my; ++it) {
+      mbar_wait(&misc->rows_bar[it % 3], (it / 3) & 1);    // (long complete) acquire: out_rows of this tile are visible
+      const uint32_t* orow = misc->out_rows[it % 3];
+      mbar_wait(&misc->d_full, it & 1);
+      tc_fence_after();
+      // 9 chunks of 16 columns (4 of dIn^T, 5 of dON^T). The 16 destination rows of a chunk come in with four
+      // 16-byte shared-memory loads; the TMEM load of the next chunk is in flight while the current chunk's
+      // reductions issue (two register buffers). The accumulators are handed back to the MMA warp as soon as
+      // the LAST chunk is in registers — with a relaxed arrive, so that it does not wait for this warp's
+      // reductions to drain into L2 (at ~3.5 TB/s of L2 reduction throughput they are the slowest part of a tile).
+      auto chunk_col = [&](int c) -> uint32_t { return (c < 4) ? kTmemDIn + 64 * half + 16 * c : kTmemDOn + 80 * half + 16 * (c - 4); };
+      auto chunk_row0 = [&](int c) -> int { return (c < 4) ? 64 * half + 16 * c : kM + 80 * half + 16 * (c - 4); };
+      uint32_t xb[2][16];
+      tmem_ld16_issue(lane_base + chunk_col(0), xb[0]);
+#pragma unroll
+      for (int c = 0; c < 9; ++c) {
+        const uint4* o4 = reinterpret_cast<const uint4*>(orow + chunk_row0(c));
+        const uint4 q0 = o4[0], q1 = o4[1], q2 = o4[2], q3 = o4[3];
+        const uint32_t rows[16] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, q3.x, q3.y, q3.z, q3.w};
+        tmem_wait_ld16(xb[c & 1]);
+        if (c + 1 < 9) {
+          tmem_ld16_issue(lane_base + chunk_col(c + 1), xb[(c + 1) & 1]);
+        } else {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_relaxed(&misc->d_free, q3.w);   // q3.w: the row ids of this tile are in registers
+        }
+        if (!(mode & 2)) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "setp.ne.u32 p, %2, 0xffffffff;\n\t"
+                "@p red.relaxed.gpu.global.add.f32 [%0], %1;\n\t}"
+                ::"l"(gdst + (size_t)rows[j] * kD), "f"(__uint_as_float(xb[c & 1][j])), "r"(rows[j])
+                : "memory");
+          }
+        }
+      }
+    }
   }
 
   // ---- teardown -------------------------------------------------------------------------------
@@ -647,9 +682,9 @@ sgns_block_tc_kernel(const __nv_bfloat16* __restrict__ params, float* __restrict
   __syncthreads();
   if (tid == 0) {
     float l = 0.f, p = 0.f;
-    for (int w = 0; w < kConsumerWarps; ++w) { l += misc->loss[w]; p += misc->pairs[w]; }
-    if (l != 0.f) atomicAdd(loss_out, l);
-    if (p != 0.f) atomicAdd(loss_out + 1, p);
+    for (int w = 0; w < kE1Warps; ++w) { l += misc->loss[w]; p += misc->pairs[w]; }
+    if (l != 0.f) atomicAdd(a.loss_out, l);
+    if (p != 0.f) atomicAdd(a.loss_out + 1, p);
   }
   if (warp == 0) {
     tc_fence_after();
@@ -695,7 +730,10 @@ extern "C" {
 // grads: fp32 [n_rows, 128].
 // inv_in/inv_out [n_tok]: cache row of each token's input / output vector; neg_idx
 // [ceil(n_tok/128) * 16]: cache rows of each tile's negatives. window <= 8.
-// mode: 0 = vector-load gather, 1 = TMA tile::gather4.
+// mode bits: 1 = TMA tile::gather4 (0 = vector-load gather, bring-up path); 32 = cp.async gather by four
+// dedicated warps; 2 = perf experiment: skip the gradient reductions; 16 = perf experiment: skip the gather;
+// 64 = perf experiment: no tile-local dedup (every position reduces its own gradient row);
+// 8 = the round-1 serial kernel (sgns_tc_serial.cu; bit 4 = its diagonal epilogue).
 static int launch_block_tc(const void* params, float* grads, int64_t n_rows, int32_t dim, const uint32_t* inv_in,
                            const uint32_t* inv_out, int64_t n_tok, int32_t sent_len, int32_t window, uint64_t seed,
                            uint64_t offset, const uint32_t* neg_idx, float neg_k, float* loss_out, int32_t mode,
@@ -710,26 +748,20 @@ static int launch_block_tc(const void* params, float* grads, int64_t n_rows, int
     int e = make_row_tmap(&tmap, params, (uint64_t)n_rows, box_rows > 0 ? (uint32_t)box_rows : 1u);
     if (e) return e;
   }
+  TcArgs a{(const __nv_bfloat16*)params, grads, inv_in, inv_out, (int)n_tok, sent_len, window, seed, offset,
+           neg_idx, neg_k, loss_out, mode, debug, dm};
+  if (mode & 8) return launch_block_tc_serial(a, tmap, stream);
   static bool attr_set[64] = {false};   // the attribute is per device: a process may drive several
   int dev_id = 0;
   if (cudaGetDevice(&dev_id) != cudaSuccess || dev_id < 0 || dev_id >= 64) return (int)cudaErrorInvalidDevice;
   if (!attr_set[dev_id]) {
-    cudaError_t e = cudaFuncSetAttribute(sgns_block_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(sgns_block_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(sgns_block_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
     if (e != cudaSuccess) return (int)e;
     attr_set[dev_id] = true;
   }
   int64_t tiles = (n_tok + kM - 1) / kM;
   int blocks = (int)(tiles < ssb::kNumSMs ? tiles : ssb::kNumSMs);
-  if (mode & 4)
-    sgns_block_tc_kernel<true><<<blocks, kThreads, kSmemBytes, (cudaStream_t)stream>>>(
-        (const __nv_bfloat16*)params, grads, inv_in, inv_out, (int)n_tok, sent_len, window, seed, offset, neg_idx, neg_k,
-        loss_out, tmap, mode, debug, dm);
-  else
-    sgns_block_tc_kernel<false><<<blocks, kThreads, kSmemBytes, (cudaStream_t)stream>>>(
-        (const __nv_bfloat16*)params, grads, inv_in, inv_out, (int)n_tok, sent_len, window, seed, offset, neg_idx, neg_k,
-        loss_out, tmap, mode, debug, dm);
+  sgns_block_tc_kernel<<<blocks, kThreads, kSmemBytes, (cudaStream_t)stream>>>(a, tmap);
   SSB_LAUNCH_CHECK();
   return 0;
 }

@@ -222,6 +222,10 @@ int ssb_table_load(const SsbTableView *view, const uint32_t *keys, const float *
 /* ---- K12: peer bandwidth probe -------------------------------------------------------------
  * Copies n_bytes from src to dst with a grid of vector loads/stores (either may be a peer). */
 int ssb_p2p_copy(const void *src, void *dst, int64_t n_bytes, int32_t blocks, void *stream);
+/* Reduction-throughput probe (benchmarks/red_probe.py): every warp of `blocks` x 512 threads adds into
+ * `iters` random rows of buf [n_rows x 128 fp32]. pattern 0 = one red.v4.f32 per 512-byte row, 1 = four
+ * scalar 128-byte reds per row, 2 = red.v4.f32 over four rows x 128 bytes, 3 = plain row stores. */
+int ssb_red_probe(float *buf, uint32_t n_rows, int32_t iters, int32_t pattern, int32_t blocks, void *stream);
 
 /* ---- misc ---------------------------------------------------------------------------------- */
 int ssb_fill_u32(uint32_t *p, uint32_t v, int64_t n, void *stream);

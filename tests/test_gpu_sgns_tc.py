@@ -60,6 +60,12 @@ def test_sgns_block_tc_tma_gather4(device, n_tok, U, sent_len, window):
     _run(device, 1, n_tok, U, sent_len, window, box_rows=int(os.environ.get("SSB200_GATHER_BOX_ROWS", "1")))
 
 
+@pytest.mark.parametrize("n_tok,U,sent_len,window", [(128, 300, 1000, 5), (1000, 500, 37, 5), (5000, 64, 100, 8), (128 * 148 * 2 + 5, 3000, 100, 5)])
+def test_sgns_block_tc_cp_async_gather(device, n_tok, U, sent_len, window):
+    """Mode bit 32: rows are gathered by four warps of 16-byte cp.async (manual 128-byte swizzle) instead of TMA."""
+    _run(device, 33, n_tok, U, sent_len, window)
+
+
 def test_fused_pull_direct_mode_matches_cache_mode(device):
     """tcgen05_direct: the TMA gathers operand rows straight from the table's bf16 row mirror; the
     gradients must equal those of the cache path (same bf16 inputs, same reductions)."""
@@ -93,23 +99,31 @@ def test_fused_pull_direct_mode_matches_cache_mode(device):
     assert err < 1e-2 * scale, (err, scale)
 
 
-def _diag_child():
-    """Runs in a child process: the experimental diagonal epilogue (mode bit 4) on the standard cases."""
+def _serial_child():
+    """Runs in a child process: the round-1 serial kernel (mode bit 8; bit 4 = its diagonal epilogue),
+    kept for A/B timing, on the standard cases."""
     dev = torch.device("cuda", 0)
-    for n_tok, U, sent_len, window in [(128, 300, 1000, 5), (1000, 500, 37, 5), (5000, 64, 100, 8), (300, 2000, 50, 1)]:
-        _run(dev, 5, n_tok, U, sent_len, window)
-    print("DIAG_OK")
+    for mode in (9, 13):
+        for n_tok, U, sent_len, window in [(128, 300, 1000, 5), (1000, 500, 37, 5), (5000, 64, 100, 8), (300, 2000, 50, 1)]:
+            _run(dev, mode, n_tok, U, sent_len, window)
+    print("SERIAL_OK")
 
 
-def test_sgns_block_tc_diagonal_epilogue_experimental(device):
-    """Mode bit 4 (`bench.py --tc-mode 5`): the diagonal form of epilogue 1 gives the same gradients and
-    loss as the oracle. Run in a child process so that a fault in the experimental instantiation cannot
-    poison this process's CUDA context."""
+def test_sgns_block_tc_serial_kernel_kept_for_ab(device):
+    """Mode bit 8 selects the serial (round-1) kernel: same gradients and loss as the oracle. Run in a child
+    process so that a fault there cannot poison this process's CUDA context."""
     import subprocess
     import sys
 
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    code = "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r); import test_gpu_sgns_tc as t; t._diag_child()" % (
+    code = "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r); import test_gpu_sgns_tc as t; t._serial_child()" % (
         root, os.path.join(root, "tests"))
     p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, cwd=root)
-    assert p.returncode == 0 and "DIAG_OK" in p.stdout, p.stdout[-1500:] + p.stderr[-1500:]
+    assert p.returncode == 0 and "SERIAL_OK" in p.stdout, p.stdout[-1500:] + p.stderr[-1500:]
+
+
+@pytest.mark.parametrize("n_tok", [128 * 148 * 3 + 77, 128 * 5])
+def test_sgns_block_tc_many_tiles_per_cta(device, n_tok):
+    """Several tiles per persistent CTA: the cross-tile pipeline (S of tile t+1 under the epilogues of tile
+    t, single-buffered TMEM accumulators, two shared-memory stages) must not mix tiles up."""
+    _run(device, 1, n_tok, 4000, 211, 5)
