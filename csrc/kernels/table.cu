@@ -345,7 +345,7 @@ __device__ __forceinline__ void bulk_mbar_wait(unsigned long long* bar, uint32_t
   __trap();
 }
 __device__ __forceinline__ void bulk_copy_g2s(void* dst_smem, const void* src, uint32_t bytes, unsigned long long* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+  asm volatile("cp.async.bulk.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(smem_addr(dst_smem)), "l"(src), "r"(bytes), "r"(smem_addr(bar)) : "memory");
 }
 __device__ __forceinline__ uint4 ld_relaxed_sys_v4(const uint4* p) {

@@ -121,7 +121,7 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
 __device__ __forceinline__ void tma_gather4(uint32_t dst_smem, const CUtensorMap* map, unsigned long long* bar,
                                             int col, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3) {
   asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes"
+      "cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes"
       " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
       ::"r"(dst_smem), "l"((uint64_t)map), "r"(smem_u32(bar)), "r"(col), "r"(r0), "r"(r1), "r"(r2), "r"(r3)
       : "memory");
