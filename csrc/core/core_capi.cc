@@ -164,6 +164,7 @@ void* ssb_corpus_open(const char* path, int batch_tokens, int sent_len, uint32_t
   FILE* f = std::fopen(path, "r");
   if (!f) return nullptr;
   std::fclose(f);
+  if (batch_tokens <= 0 || sent_len <= 0 || batch_tokens % sent_len != 0) return nullptr;   // refuse, do not abort
   return new CorpusLoader(path, batch_tokens, sent_len, pad_id, epochs);
 }
 void* ssb_corpus_open_split(const char* path, int batch_tokens, int sent_len, uint32_t pad_id, int epochs, int split_n,
@@ -172,7 +173,28 @@ void* ssb_corpus_open_split(const char* path, int batch_tokens, int sent_len, ui
   if (!f) return nullptr;
   std::fclose(f);
   if (split_n < 1 || split_i < 0 || split_i >= split_n) return nullptr;
+  if (batch_tokens <= 0 || sent_len <= 0 || batch_tokens % sent_len != 0) return nullptr;   // refuse, do not abort
   return new CorpusLoader(path, batch_tokens, sent_len, pad_id, epochs, 4, split_n, split_i);
+}
+// Full form: parser threads (<= 0: chosen from the host) and an id bound (ids >= max_id become padding; 0 = off).
+void* ssb_corpus_open_ex(const char* path, int batch_tokens, int sent_len, uint32_t pad_id, int epochs, int split_n,
+                         int split_i, int threads, uint32_t max_id) {
+  FILE* f = std::fopen(path, "r");
+  if (!f) return nullptr;
+  std::fclose(f);
+  if (split_n < 1 || split_i < 0 || split_i >= split_n) return nullptr;
+  if (batch_tokens <= 0 || sent_len <= 0 || batch_tokens % sent_len != 0) return nullptr;   // refuse, do not abort
+  return new CorpusLoader(path, batch_tokens, sent_len, pad_id, epochs, 4, split_n, split_i, threads, max_id);
+}
+// out[0] = sentence lines of this reader's share per pass, out[1] = minibatches it will deliver,
+// out[2] = token ids >= max_id replaced by padding so far
+void ssb_corpus_stats(void* h, long long* out) {
+  CorpusLoader* c = static_cast<CorpusLoader*>(h);
+  out[0] = c->sentences(); out[1] = c->batches(); out[2] = c->bad_tokens();
+}
+// counts[vocab] += word frequencies of the corpus; returns the number of ids >= vocab, or -1 if the file cannot be opened
+long long ssb_corpus_count_words(const char* path, uint32_t vocab, unsigned long long* counts, int threads) {
+  return corpus_count_words(path, vocab, counts, threads);
 }
 long ssb_corpus_next(void* h, uint32_t* out) { return static_cast<CorpusLoader*>(h)->next(out); }
 void ssb_corpus_close(void* h) { delete static_cast<CorpusLoader*>(h); }

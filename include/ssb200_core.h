@@ -50,6 +50,13 @@ void *ssb_corpus_open(const char *path, int batch_tokens, int sent_len, uint32_t
 /* Same, keeping only the non-empty lines whose index % split_n == split_i (per-worker data split). */
 void *ssb_corpus_open_split(const char *path, int batch_tokens, int sent_len, uint32_t pad_id, int epochs,
                             int split_n, int split_i);
+/* full form: `threads` parser threads (<= 0: chosen from the host), ids >= max_id become padding (0 = no bound) */
+void *ssb_corpus_open_ex(const char *path, int batch_tokens, int sent_len, uint32_t pad_id, int epochs, int split_n,
+                         int split_i, int threads, uint32_t max_id);
+/* out[0] = sentence lines per pass (this reader's share), out[1] = minibatches, out[2] = ids replaced by padding */
+void ssb_corpus_stats(void *h, long long *out);
+/* counts[vocab] += word frequencies (for the unigram^0.75 noise table); returns the number of ids >= vocab, -1 = cannot open */
+long long ssb_corpus_count_words(const char *path, uint32_t vocab, unsigned long long *counts, int threads);
 long ssb_corpus_next(void *h, uint32_t *out);
 void ssb_corpus_close(void *h);
 

@@ -132,7 +132,11 @@ class Word2VecWorker:
         self.n_negs = self.max_tiles * cfg.neg_pool
         self.n_keys = 2 * B + self.n_negs
         if sampler is None:
-            sampler = AliasSampler(unigram_weights_from_zipf(cfg.vocab, cfg.zipf_s), device, seed=cfg.seed + 77)
+            # synthetic-benchmark default: the noise distribution of the synthetic Zipf corpus. Training from a real
+            # corpus replaces it with the corpus' own unigram^0.75 (Word2VecTrainer.train_file). The rank is mixed
+            # into the seed so that the workers of a job do not all draw the same negatives.
+            sampler = AliasSampler(unigram_weights_from_zipf(cfg.vocab, cfg.zipf_s), device,
+                                   seed=cfg.seed + 77 + 7919 * int(getattr(table, "rank", 0)))
         self.sampler = sampler
         use_cache = cfg.slot_cache if cfg.slot_cache is not None else getattr(table, "num_shards", 1) > 1
         if use_cache and getattr(table, "slot_cache", 0) is None:
@@ -281,6 +285,8 @@ class Word2VecTrainer:
         self.h2d_bytes = cfg.tokens_per_step * 4
         self.d2h_bytes = 2 * 4
         self._i = 0
+        self.on_step = None        # optional callback(step) after every minibatch of train_file (periodic backups)
+        self.bad_tokens = 0
         from ..utils.metrics import registry
 
         reg = registry()
@@ -318,17 +324,52 @@ class Word2VecTrainer:
         self._m_rate.mark(self.cfg.tokens_per_step)
         return prev
 
-    def train_file(self, path, epochs=1, log_every=0, split=None, max_steps=None):
+    def health(self):
+        """Counters of the two ways an update can be lost, read from the device (synchronises): rows the table had
+        no room for (``table_full``: their pull returned zeros and their push was skipped) and gradient rows dropped
+        because a sender's share of an owner's inbox was full (``inbox_overflow``). Both must stay 0."""
+        self.worker.flush()
+        out = {"table_full": int(self.worker.table.stats[1].item()), "inbox_overflow": 0}
+        inbox = getattr(self.worker.table, "inbox", None)
+        if inbox is not None:
+            out["inbox_overflow"] = int(inbox.overflow.item())
+        return out
+
+    def check_health(self):
+        h = self.health()
+        if h["table_full"] or h["inbox_overflow"]:
+            raise RuntimeError("updates were lost: %r (grow the table capacity / the inbox)" % (h,))
+        return h
+
+    def use_corpus_noise(self, path, power=0.75):
+        """Negative-sampling table from the corpus' own word counts (unigram^power), as word2vec defines it.
+        Returns (distinct words seen, ids >= vocab found in the corpus)."""
+        from ..utils.corpus import count_words
+
+        counts, bad = count_words(path, self.cfg.vocab)
+        seen = int((counts > 0).sum())
+        if seen > 0:
+            w = self.worker
+            w.sampler = AliasSampler(np.power(counts.astype(np.float64), power), self.device,
+                                     seed=self.cfg.seed + 77 + 7919 * int(getattr(w.table, "rank", 0)))
+        return seen, bad
+
+    def train_file(self, path, epochs=1, log_every=0, split=None, max_steps=None, corpus_noise=True):
         """Train from a text corpus (one sentence of integer word ids per line — the reference's data
         format, tools/gen_word2vec_data.py). Sentences are cut / padded to ``cfg.sent_len``; a native
-        background reader (utils/corpus.py) fills pinned batches while the GPU works.
+        parallel reader (utils/corpus.py) fills pinned batches while the GPU works.
         ``split=(n, i)`` reads worker i's share of the lines; ``max_steps`` stops after that many
         minibatches (with the inbox push every rank has to run the same number of steps).
-        Returns (tokens_trained, last_mean_loss)."""
+        ``corpus_noise``: draw negatives from the corpus' own unigram^0.75 (counted here, before training).
+        Token ids >= vocab are dropped (turned into padding) and counted in ``self.bad_tokens``; lost updates
+        (table full / inbox overflow) raise. Returns (tokens_trained, last_mean_loss)."""
         from ..utils.corpus import CorpusLoader
 
+        if corpus_noise:
+            self.use_corpus_noise(path)
         self.worker.has_padding = True
-        loader = CorpusLoader(path, self.cfg.tokens_per_step, self.cfg.sent_len, epochs=epochs, split=split)
+        loader = CorpusLoader(path, self.cfg.tokens_per_step, self.cfg.sent_len, epochs=epochs, split=split,
+                              max_id=self.cfg.vocab)
         total, step = 0, 0
         for buf, n_real in loader:
             if max_steps is not None and step >= max_steps:
@@ -336,11 +377,17 @@ class Word2VecTrainer:
             loss = self.train_step(buf)
             total += n_real
             step += 1
+            if self.on_step is not None:
+                self.on_step(step)
             if log_every and step % log_every == 0 and loss is not None:
+                self.check_health()
                 print("step %d  tokens %d  loss/pair %.4f" % (step, total, loss))
+        self.bad_tokens = loader.bad_tokens
         loader.close()
         self.steps_done = step
-        return total, self.finish()
+        last = self.finish()
+        self.check_health()
+        return total, last
 
     def finish(self):
         if self._i == 0:

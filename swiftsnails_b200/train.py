@@ -58,13 +58,14 @@ def word2vec_config(conf, world=1):
 
 
 def count_sentences(path):
-    """Lines the loader will turn into a sentence: non-empty and starting with a number (the native
-    reader, csrc/core/corpus_loader.h, skips anything else)."""
+    """Lines the loader will turn into a sentence: the first non-blank character is a digit (the same rule as
+    the native reader, csrc/core/corpus_loader.h: corpus_is_sentence — it skips, and does not number, anything
+    else, so every rank derives the same number of minibatches from this count)."""
     n = 0
     with open(path, "rb") as f:
         for line in f:
-            t = line.lstrip()
-            if t[:1].isdigit() or (t[:1] in b"+-" and t[1:2].isdigit()):
+            t = line.lstrip(b" \t\r")
+            if t[:1].isdigit():
                 n += 1
     return n
 
