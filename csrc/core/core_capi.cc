@@ -82,6 +82,76 @@ int64_t ssb_dump_write_text(const char* path, const uint32_t* keys, const float*
   std::fclose(f);
   return n;
 }
+// Param-style line: "<key>\tVec:\t v0 v1 … \tAcc:\t a0 a1 … \n" — the row followed by its optimizer state (AdaGrad
+// accumulator), which is what the reference's dump prints when the table's Param carries one (the whole Param goes
+// through operator<<, parameter/sparsetable.h:49-56). state == nullptr writes plain rows. digits: significant digits per
+// number (6 = the reference's default ostream precision; 9 round-trips a float exactly).
+int64_t ssb_dump_write_text2(const char* path, const uint32_t* keys, const float* rows, const float* state, int64_t n, int dim,
+                             int append, int digits) {
+  FILE* f = std::fopen(path, append ? "a" : "w");
+  if (!f) return -1;
+  std::vector<char> buf(1 << 20);
+  std::setvbuf(f, buf.data(), _IOFBF, buf.size());
+  if (digits < 1) digits = 6;
+  if (digits > 17) digits = 17;
+  for (int64_t i = 0; i < n; ++i) {
+    const float* r = rows + i * dim;
+    if (dim == 1 && !state) {
+      std::fprintf(f, "%u\t%.*g\n", keys[i], digits, r[0]);
+      continue;
+    }
+    std::fprintf(f, "%u\tVec:\t", keys[i]);
+    for (int j = 0; j < dim; ++j) std::fprintf(f, "%.*g ", digits, r[j]);
+    if (state) {
+      std::fputs("\tAcc:\t", f);
+      const float* a = state + i * dim;
+      for (int j = 0; j < dim; ++j) std::fprintf(f, "%.*g ", digits, a[j]);
+    }
+    std::fputc('\n', f);
+  }
+  std::fclose(f);
+  return n;
+}
+// Reads either line form. state may be nullptr (an "Acc:" part is then skipped); rows / state shorter than dim are
+// zero-padded. *has_state (optional) is set to 1 if any line carried an "Acc:" part. Returns the rows read (<= max_n).
+int64_t ssb_dump_read_text2(const char* path, uint32_t* keys, float* rows, float* state, int64_t max_n, int dim, int* has_state) {
+  FILE* f = std::fopen(path, "r");
+  if (!f) return -1;
+  LineFileReader reader;
+  int64_t n = 0;
+  if (has_state) *has_state = 0;
+  auto parse_vec = [dim](char* p, float* out) -> char* {
+    for (int j = 0; j < dim; ++j) {
+      char* end = nullptr;
+      const float v = std::strtof(p, &end);
+      if (end == p) { if (out) for (; j < dim; ++j) out[j] = 0.f; break; }
+      if (out) out[j] = v;
+      p = end;
+    }
+    return p;
+  };
+  while (n < max_n) {
+    char* line = reader.getline(f);
+    if (!line) break;
+    char* tab = std::strchr(line, '\t');
+    if (!tab) continue;
+    keys[n] = (uint32_t)std::strtoul(line, nullptr, 10);
+    char* p = tab + 1;
+    if (std::strncmp(p, "Vec:", 4) == 0) p += 4;
+    p = parse_vec(p, rows + n * dim);
+    float* st = state ? state + n * dim : nullptr;
+    char* acc = std::strstr(p, "Acc:");
+    if (acc) {
+      if (has_state) *has_state = 1;
+      parse_vec(acc + 4, st);
+    } else if (st) {
+      for (int j = 0; j < dim; ++j) st[j] = 0.f;
+    }
+    ++n;
+  }
+  std::fclose(f);
+  return n;
+}
 // returns the number of rows read (<= max_n); rows shorter than dim are zero-padded
 int64_t ssb_dump_read_text(const char* path, uint32_t* keys, float* rows, int64_t max_n, int dim) {
   FILE* f = std::fopen(path, "r");

@@ -771,6 +771,42 @@ dump_compact_kernel(const uint32_t* __restrict__ keys, const float* __restrict__
   }
 }
 
+// Chunked form for checkpoints: compacts the live slots of the bucket range [bucket_lo, bucket_hi) of one shard,
+// copying the row AND (when the shard has one) the optimizer-state row of a slot to the same output index, so a
+// shard of any size streams through bounded host / device buffers with rows and state aligned.
+__global__ void __launch_bounds__(256)
+dump_compact_range_kernel(const uint32_t* __restrict__ keys, const float* __restrict__ rows, const float* __restrict__ state,
+                          uint32_t bucket_lo, uint32_t bucket_hi, int D, uint32_t* __restrict__ out_keys,
+                          float* __restrict__ out_rows, float* __restrict__ out_state, uint32_t* __restrict__ n_live,
+                          uint32_t max_out) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  for (uint32_t b = bucket_lo + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5); b < bucket_hi; b += warps) {
+    const uint32_t k = keys[(size_t)b * SSB_BUCKET + lane];
+    const unsigned live = __ballot_sync(0xffffffffu, k < SSB_LOCKED_KEY);
+    if (!live) continue;
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(n_live, (uint32_t)__popc(live));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (k < SSB_LOCKED_KEY) {
+      const uint32_t dst = base + __popc(live & ((1u << lane) - 1));
+      if (dst < max_out) out_keys[dst] = k;
+    }
+    unsigned m = live;
+    while (m) {
+      const int src = __ffs(m) - 1;
+      m &= m - 1;
+      const uint32_t dst = base + __popc(live & ((1u << src) - 1));
+      if (dst >= max_out) break;
+      const size_t slot = (size_t)b * SSB_BUCKET + src;
+      for (int j = lane; j < D; j += 32) {
+        out_rows[(size_t)dst * D + j] = rows[slot * D + j];
+        if (out_state) out_state[(size_t)dst * D + j] = state[slot * D + j];
+      }
+    }
+  }
+}
+
 inline int row_grid(int64_t n) {
   // warp per row, 8 warps per block; cap at a few waves of 148 SMs x 8 resident blocks
   return grid_for(n, 8, kNumSMs * 8);
@@ -935,6 +971,23 @@ int ssb_table_load(const SsbTableView* view, const uint32_t* keys, const float* 
   if (int e = check_view(view)) return e;
   if (n <= 0) return 0;
   ssb::table_load_kernel<<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, keys, rows, state, n, stats);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_dump_compact_range(const uint32_t* keys, const float* rows, const float* state, uint32_t capacity, int32_t dim,
+                           uint32_t slot_lo, uint32_t slot_hi, uint32_t* out_keys, float* out_rows, float* out_state,
+                           uint32_t* n_live, uint32_t max_out, void* stream) {
+  if (capacity == 0 || capacity % SSB_BUCKET != 0 || slot_lo % SSB_BUCKET != 0 || slot_hi % SSB_BUCKET != 0 ||
+      slot_lo > slot_hi || slot_hi > capacity || dim < 1 || !keys || !rows || !out_keys || !out_rows || !n_live ||
+      (out_state && !state))
+    return (int)cudaErrorInvalidValue;
+  cudaError_t e = cudaMemsetAsync(n_live, 0, sizeof(uint32_t), (cudaStream_t)stream);
+  if (e != cudaSuccess) return (int)e;
+  if (slot_lo == slot_hi) return 0;
+  const uint32_t b_lo = slot_lo / SSB_BUCKET, b_hi = slot_hi / SSB_BUCKET;
+  ssb::dump_compact_range_kernel<<<ssb::row_grid(b_hi - b_lo), 256, 0, (cudaStream_t)stream>>>(
+      keys, rows, state, b_lo, b_hi, dim, out_keys, out_rows, out_state, n_live, max_out);
   SSB_LAUNCH_CHECK();
   return 0;
 }

@@ -210,6 +210,13 @@ int ssb_vmm_release(uint64_t handle);
 int ssb_vmm_free_va(uint64_t va, uint64_t bytes);
 int ssb_memset_async(void *p, int value, uint64_t bytes, void *stream);
 
+/* Chunked dump for checkpoints: compacts the live slots in [slot_lo, slot_hi) (multiples of 32) of one shard into
+ * out_keys / out_rows and, when out_state is given, the optimizer-state rows into out_state at the SAME indices.
+ * n_live (device) receives the count; at most max_out entries are written.
+ * ref: parameter/sparsetable.h:49-56 — the reference dumps the whole Param (row + whatever state it carries). */
+int ssb_dump_compact_range(const uint32_t *keys, const float *rows, const float *state, uint32_t capacity, int32_t dim,
+                           uint32_t slot_lo, uint32_t slot_hi, uint32_t *out_keys, float *out_rows, float *out_state,
+                           uint32_t *n_live, uint32_t max_out, void *stream);
 /* ---- K11: parameter dump -----------------------------------------------------------------
  * Compacts the live slots of one shard: out_keys[*n_live], out_rows[*n_live][dim].        */
 int ssb_dump_compact(const uint32_t *keys, const float *rows, uint32_t capacity, int32_t dim,

@@ -33,6 +33,13 @@ int ssb_buffer_selftest(void);
 int64_t ssb_dump_write_text(const char *path, const uint32_t *keys, const float *rows, int64_t n,
                             int dim, int append);
 int64_t ssb_dump_read_text(const char *path, uint32_t *keys, float *rows, int64_t max_n, int dim);
+/* Param-style dump lines "<key>\tVec:\t v…\tAcc:\t a…" (row + optimizer state, the whole Param as the reference's
+ * operator<< would print it, parameter/sparsetable.h:49-56); state may be NULL. digits = significant digits
+ * (6 = the reference's ostream default, 9 = exact float round trip). */
+int64_t ssb_dump_write_text2(const char *path, const uint32_t *keys, const float *rows, const float *state, int64_t n,
+                             int dim, int append, int digits);
+int64_t ssb_dump_read_text2(const char *path, uint32_t *keys, float *rows, float *state, int64_t max_n, int dim,
+                            int *has_state);
 
 /* CPU sparse table with the stock SGD / AdaGrad access methods — ref: parameter/sparsetable.h */
 void *ssb_cpu_table_new(int shard_num, int dim, int adagrad, float lr, float eps, uint64_t seed,

@@ -189,6 +189,32 @@ class ShardedTable:
         torch.cuda.synchronize(shard.device)
         return out_keys[:n].cpu().numpy().view(np.uint32), out_rows[:n].cpu().numpy()
 
+    def iter_shard_chunks(self, shard: DeviceShard, with_state=False, max_bytes=256 << 20):
+        """Stream the live entries of an owned shard in bounded pieces: yields (keys uint32 np, rows float32 np,
+        state float32 np | None). One fused compaction kernel per piece copies a slot's row and optimizer-state
+        row to the same index; device and host staging are sized by ``max_bytes``, not by the shard (config 4
+        is 6.4 GB of rows + 6.4 GB of state per shard)."""
+        want_state = bool(with_state) and shard.state is not None
+        per_slot = 4 + shard.dim * 4 * (2 if want_state else 1)
+        chunk = max(_lib.BUCKET, (int(max_bytes) // per_slot) // _lib.BUCKET * _lib.BUCKET)
+        chunk = min(chunk, shard.capacity)
+        dev = shard.device
+        n_live = torch.zeros(1, dtype=torch.int32, device=dev)
+        out_keys = torch.empty(chunk, dtype=torch.int32, device=dev)
+        out_rows = torch.empty((chunk, shard.dim), dtype=torch.float32, device=dev)
+        out_state = torch.empty((chunk, shard.dim), dtype=torch.float32, device=dev) if want_state else None
+        for lo in range(0, shard.capacity, chunk):
+            hi = min(lo + chunk, shard.capacity)
+            _lib.call("ssb_dump_compact_range", shard.keys.data_ptr(), shard.rows.data_ptr(),
+                      shard.state.data_ptr() if want_state else None, shard.capacity, shard.dim, lo, hi,
+                      out_keys.data_ptr(), out_rows.data_ptr(), _lib.ptr(out_state), n_live.data_ptr(), chunk,
+                      _lib.stream_ptr())
+            n = int(n_live.item())
+            if n == 0:
+                continue
+            yield (out_keys[:n].cpu().numpy().view(np.uint32), out_rows[:n].cpu().numpy(),
+                   out_state[:n].cpu().numpy() if want_state else None)
+
     def load(self, keys, rows, state=None):
         """Insert (key,row[,state]) entries (checkpoint resume; not in the reference)."""
         check_cuda(keys, rows)

@@ -7,7 +7,8 @@
 Same config grammar and key names as the reference's apps read (``dim``, ``vocab``, ``window``,
 ``negative``, ``learning_rate``, ``num_iters``) plus the optional keys of this
 framework (``update: sgd|adagrad``, ``table_seed``, ``init_scale``, ``tokens_per_step``, ``sent_len``,
-``param_dump_path``).  Same data format (one sentence of integer word ids per line) and the same
+``param_dump_path``), and the server's ``param_backup_period`` / ``param_backup_root``: every that many
+minibatches each rank writes ``<root>/param-<rank>-<n>.txt`` (system/server/init.h:128-149).  Same data format (one sentence of integer word ids per line) and the same
 ``key \\t value`` text dump at the end — one file per rank (``<out>.<rank>`` when there are several),
 which is what the reference's servers produce (one dump per server, server/terminate.h:36).
 
@@ -34,6 +35,9 @@ def parse_args(argv=None):
     ap.add_argument("--epochs", type=int, default=None, help="passes over the data (default: config key num_iters)")
     ap.add_argument("--log-every", type=int, default=0)
     ap.add_argument("--binary", action="store_true", help="write the raw binary shard dump instead of text")
+    ap.add_argument("--dump-state", action="store_true",
+                    help="text dump carries the optimizer state too (Param-style lines, 9 digits): exact resume")
+    ap.add_argument("--resume", default=None, help="load this dump (text or binary; <path>.<rank> with several GPUs) before training")
     return ap.parse_args(argv)
 
 
@@ -114,6 +118,25 @@ def main(argv=None):
     if steps == 0:
         raise SystemExit("corpus %s has fewer sentences (%d) than workers (%d)" % (args.data, n_sent, world))
     trainer = Word2VecTrainer(cfg, table, dev, pipeline=(cfg.tile_impl == "tcgen05"))
+    if args.resume:
+        rpath = args.resume if world == 1 else "%s.%d" % (args.resume, rank)
+        with open(rpath, "rb") as f:
+            is_binary = f.read(4) == b"SSB2"
+        loaded = (dump.load_table_binary if is_binary else dump.load_table)(table, rpath)
+        if rank == 0:
+            print("resumed %d rows from %s" % (loaded, rpath))
+    # periodic parameter backup, as the reference's server does every param_backup_period push requests
+    # (system/server/init.h:128-149); here a push request is a minibatch of this rank's worker
+    from .framework import SwiftServer
+
+    server = SwiftServer(table, conf)
+    if server.backup_period > 0:
+        os.makedirs(server.backup_root, exist_ok=True)
+
+        def _backup(step):
+            trainer.worker.flush()
+            server.on_push()
+        trainer.on_step = _backup
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -136,13 +159,20 @@ def main(argv=None):
     rows = 0
     if out:
         path = out if world == 1 else "%s.%d" % (out, rank)
-        rows = dump.save_table_binary(table, path) if args.binary else dump.save_table(table, path)
+        if args.binary:
+            rows = dump.save_table_binary(table, path)
+        elif args.dump_state:
+            rows = dump.save_table(table, path, with_state=True, digits=9)
+        else:
+            rows = dump.save_table(table, path)
     if world > 1:
         dist.barrier()
     if rank == 0:
         print("RESULT " + json.dumps({"app": "word2vec", "gpus": world, "tokens": tokens_all, "seconds": round(dt, 3),
                                       "words_per_s": round(tokens_all / max(dt, 1e-9), 1), "loss_per_pair": loss,
-                                      "steps_per_rank": steps, "dump": out or None, "rows_dumped_rank0": rows}))
+                                      "steps_per_rank": steps, "dump": out or None, "rows_dumped_rank0": rows,
+                                      "ids_out_of_vocab_rank0": trainer.bad_tokens, "health_rank0": trainer.health(),
+                                      "backups_rank0": server.push_counter // server.backup_period if server.backup_period > 0 else 0}))
     if world > 1:
         dist.destroy_process_group()
     return 0

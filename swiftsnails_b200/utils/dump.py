@@ -48,43 +48,94 @@ def read_text(path, dim, max_rows=None):
     return keys[:n], rows[:n]
 
 
-def save_table(table, path):
-    """Dump every shard this process owns to ``path`` (text, reference format)."""
+def write_text_param(path, keys, rows, state=None, append=False, digits=6):
+    """Param-style lines: the row followed by ``\\tAcc:\\t`` and the optimizer state when ``state`` is given."""
+    lib = _core()
+    lib.ssb_dump_write_text2.restype = C.c_int64
+    lib.ssb_dump_write_text2.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int]
+    keys = np.ascontiguousarray(keys, dtype=np.uint32)
+    rows = np.ascontiguousarray(rows, dtype=np.float32).reshape(len(keys), -1)
+    st = None if state is None else np.ascontiguousarray(state, dtype=np.float32).reshape(len(keys), -1)
+    n = lib.ssb_dump_write_text2(path.encode(), keys.ctypes.data, rows.ctypes.data, None if st is None else st.ctypes.data,
+                                 len(keys), rows.shape[1], 1 if append else 0, int(digits))
+    if n < 0:
+        raise OSError("cannot write %s" % path)
+    return n
+
+
+def read_text_param(path, dim, max_rows=None):
+    """Reads plain or Param-style lines. Returns (keys, rows, state or None)."""
+    lib = _core()
+    lib.ssb_dump_read_text2.restype = C.c_int64
+    lib.ssb_dump_read_text2.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
+    if max_rows is None:
+        with open(path, "rb") as f:
+            max_rows = sum(1 for _ in f)
+    keys = np.empty(max_rows, dtype=np.uint32)
+    rows = np.zeros((max_rows, dim), dtype=np.float32)
+    state = np.zeros((max_rows, dim), dtype=np.float32)
+    has = C.c_int(0)
+    n = lib.ssb_dump_read_text2(path.encode(), keys.ctypes.data, rows.ctypes.data, state.ctypes.data, max_rows, dim, C.byref(has))
+    if n < 0:
+        raise OSError("cannot read %s" % path)
+    return keys[:n], rows[:n], (state[:n] if has.value else None)
+
+
+def save_table(table, path, with_state=False, digits=6, max_bytes=256 << 20):
+    """Dump every shard this process owns to ``path`` (text, reference format), streamed in bounded pieces.
+    ``with_state``: Param-style lines that also carry the optimizer state (AdaGrad accumulator), so that a run
+    resumed from the dump continues with the same step sizes; ``digits=9`` makes the text exact for float32."""
     total = 0
     first = True
+    with_state = bool(with_state) and table.has_state
     for shard in table.owned:
-        k, r = table.dump_shard(shard)
-        total += write_text(path, k, r, append=not first)
-        first = False
+        for k, r, st in table.iter_shard_chunks(shard, with_state=with_state, max_bytes=max_bytes):
+            if with_state or digits != 6:
+                total += write_text_param(path, k, r, st, append=not first, digits=digits)
+            else:
+                total += write_text(path, k, r, append=not first)
+            first = False
+    if first:
+        open(path, "w").close()
     return total
 
 
 def load_table(table, path, chunk=1 << 20):
-    """Insert a text dump into an HBM table (checkpoint resume)."""
+    """Insert a text dump (plain or Param-style) into an HBM table (checkpoint resume)."""
     import torch
 
     from ..ops._util import u32_tensor
 
-    keys, rows = read_text(path, table.dim)
+    keys, rows, state = read_text_param(path, table.dim)
     for s in range(0, len(keys), chunk):
         kd = u32_tensor(keys[s:s + chunk], table.device)
         rd = torch.from_numpy(rows[s:s + chunk]).to(table.device)
-        table.load(kd, rd)
+        sd = torch.from_numpy(state[s:s + chunk]).to(table.device) if (state is not None and table.has_state) else None
+        table.load(kd, rd, sd)
     return len(keys)
 
 
-def save_table_binary(table, path):
-    """Raw shard dump: <uint32 n><uint32 dim> keys[n] rows[n*dim] per owned shard (little endian)."""
+_BIN_MAGIC = 0x32425353          # "SSB2": records <magic><n><dim><flags> keys[n] rows[n*dim] (state[n*dim] if flags & 1)
+
+
+def save_table_binary(table, path, with_state=True, max_bytes=256 << 20):
+    """Raw dump, streamed in bounded pieces: a sequence of records
+    ``<uint32 magic "SSB2"><uint32 n><uint32 dim><uint32 flags> keys[n] rows[n*dim] [state[n*dim] if flags & 1]``
+    (little endian). The optimizer state is included by default when the table has one."""
+    with_state = bool(with_state) and table.has_state
     with open(path, "wb") as f:
         for shard in table.owned:
-            k, r = table.dump_shard(shard)
-            np.array([len(k), table.dim], dtype=np.uint32).tofile(f)
-            k.tofile(f)
-            r.astype(np.float32).tofile(f)
+            for k, r, st in table.iter_shard_chunks(shard, with_state=with_state, max_bytes=max_bytes):
+                np.array([_BIN_MAGIC, len(k), table.dim, 1 if st is not None else 0], dtype=np.uint32).tofile(f)
+                k.tofile(f)
+                r.astype(np.float32).tofile(f)
+                if st is not None:
+                    st.astype(np.float32).tofile(f)
     return os.path.getsize(path)
 
 
 def load_table_binary(table, path):
+    """Reads the record format above, and the round-1 format (``<n><dim> keys rows`` per shard, no state)."""
     import torch
 
     from ..ops._util import u32_tensor
@@ -95,9 +146,16 @@ def load_table_binary(table, path):
             hdr = np.fromfile(f, dtype=np.uint32, count=2)
             if hdr.size < 2:
                 break
-            n, dim = int(hdr[0]), int(hdr[1])
+            flags = 0
+            if int(hdr[0]) == _BIN_MAGIC:
+                rest = np.fromfile(f, dtype=np.uint32, count=2)
+                n, dim, flags = int(hdr[1]), int(rest[0]), int(rest[1])
+            else:
+                n, dim = int(hdr[0]), int(hdr[1])
             k = np.fromfile(f, dtype=np.uint32, count=n)
             r = np.fromfile(f, dtype=np.float32, count=n * dim).reshape(n, dim)
-            table.load(u32_tensor(k, table.device), torch.from_numpy(r).to(table.device))
+            st = np.fromfile(f, dtype=np.float32, count=n * dim).reshape(n, dim) if flags & 1 else None
+            sd = torch.from_numpy(st).to(table.device) if (st is not None and table.has_state) else None
+            table.load(u32_tensor(k, table.device), torch.from_numpy(r).to(table.device), sd)
             total += n
     return total
