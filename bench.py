@@ -51,7 +51,7 @@ def parse_args():
     ap.add_argument("--inbox", type=int, default=1, help="multi-GPU AdaGrad push through owner inboxes (one-way) instead of remote atomics")
     ap.add_argument("--prepopulate", type=int, default=1, help="create all 2*vocab rows before timing (steady-state table)")
     ap.add_argument("--pipeline", type=int, default=1, help="overlap dedup+pull of step i+1 with SGNS+push of step i (2 streams)")
-    ap.add_argument("--tc-mode", type=int, default=1, help="tcgen05 kernel mode bits (1 = TMA gather4; 2 = perf experiment: skip gradient reds; 4 = experimental diagonal sigmoid epilogue)")
+    ap.add_argument("--tc-mode", type=int, default=33, help="tcgen05 kernel mode bits (32 = cp.async gather warps (default), 1 = TMA gather4; 2 / 16 / 64 = perf experiments; 8 = round-1 serial kernel)")
     ap.add_argument("--slot-cache", type=int, default=-1, help="worker-side key->slot cache (starts empty after the table is populated; fills from the warm-up steps on); -1 = auto: on from 2 GPUs")
     ap.add_argument("--ref-tokens", type=int, default=60_000, help="tokens per worker for the reference arm")
     return ap.parse_args()

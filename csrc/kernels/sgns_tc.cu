@@ -82,13 +82,14 @@ struct Misc {
   uint32_t on_tab[2][kN];
   uint16_t row_lead[2][kM];        // per stage, per centre row: lead | dup << 8                         (producer warp)
   uint16_t row_win[2][kM];         // per stage, per centre row: c_lo | c_hi << 8 (c_lo > c_hi: no contexts) (helper warps)
+  uint32_t row_msum[2][kM];        // per stage, per LEADER row: sum of m_i (contexts per centre) over the rows folded into it
   uint16_t col_meta[2][kN];        // per stage, per ON column: lead | dup << 8                          (producer, after the dedup)
   uint8_t col_bad[2][kN];          // per stage, per ON column: the row is INVALID (padding)             (producer, at once)
   uint32_t out_rows[3][kM + kN];   // per tile (it % 3): gradient destination rows, leaders only (INVALID = skip)
   unsigned long long full_bar[2];  // operand rows landed (producer TMA / gather warps -> MMA)
   unsigned long long empty_bar[2]; // gradient MMAs retired: stage free (MMA -> producer)
   unsigned long long lead_bar[2];  // row_lead / col_meta ready (producer -> epilogue 1)
-  unsigned long long win_bar[2];   // row_win ready (helper warps -> epilogue 1)
+  unsigned long long win_bar[2];   // row_win ready (helper warps -> producer, epilogue 1)
   unsigned long long early_bar[2]; // col_bad / ctx_has_invalid ready (producer -> epilogue 1)
   unsigned long long rows_bar[3];  // out_rows[it % 3] ready (producer -> epilogue 2)
   unsigned long long idx_bar[2];   // gather indices published, stage free (producer -> cp.async gather warps)
@@ -366,6 +367,21 @@ sgns_block_tc_kernel(const __grid_constant__ TcArgs a, const __grid_constant__ C
         tile_leaders<4, 256>(ri, epoch, ds->tab_in, ds->ids_in, ds->flag_in, lead_i, dup_i, lane, identity);
         tile_leaders<5, 512>(ro, epoch, ds->tab_on, ds->ids_on, ds->flag_on, lead_o, dup_o, lane, identity);
       }
+      // Negative columns: the rows folded into one leader hold the SAME centre word, so their logits against the
+      // tile's negatives are identical and only their weights m_i * K / 16 differ. The leader writes those 16
+      // cells once with the group's summed weight (msum); the other members write none. Without this every member
+      // of a hot word's group adds into the same 16 cells at the same time (measured: ~5 K cycles per tile of
+      // shared-memory CAS retries). m_i comes from the helper warps' windows (row_win).
+#pragma unroll
+      for (int k = 0; k < 4; ++k) misc->row_msum[b][lane + 32 * k] = 0;
+      mbar_wait(&misc->win_bar[b], (it >> 1) & 1);
+      __syncwarp();
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t rw = misc->row_win[b][lane + 32 * k];
+        const int m = (int)(rw >> 8) - (int)(rw & 0xFFu);
+        if (m > 0) atomicAdd(&misc->row_msum[b][lead_i[k]], (uint32_t)m);
+      }
       uint32_t* orow = misc->out_rows[it % 3];
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
@@ -479,33 +495,12 @@ sgns_block_tc_kernel(const __grid_constant__ TcArgs a, const __grid_constant__ C
       // (c) helper thread gt owns centre rows gt and gt + 64 of the tile: its shrunk window (Philox, one draw per token
       // position) and sentence bounds as the range of valid context columns [c_lo, c_hi] (column c <-> token
       // t0 - 8 + c; the centre itself sits at column gt + 8). Needs nothing but the token's validity, read from
-      // global memory; issued here so the load is in flight during the gather.
+      // global memory. Done first: the producer and epilogue 1 both wait for it.
       uint32_t my_row[kM / kHelpers];
 #pragma unroll
       for (int k = 0; k < kM / kHelpers; ++k) {
         const int gi = t0 + gt + k * kHelpers;
         my_row[k] = gi < n_tok ? __ldg(a.inv_in + gi) : SSB_INVALID_SLOT;
-      }
-      if (mode & 32) {
-        mbar_wait(&misc->idx_bar[b], (it >> 1) & 1);
-        if (warp == kGatherWarp0) SSB_STAMP(6);
-        const uint32_t in_dst = sbase + kOffIn + b * kInBytes + sw_lo * kInBlk;
-        const uint32_t on_dst = sbase + kOffOn + b * kOnBytes + sw_lo * kOnBlk;
-#pragma unroll 4
-        for (uint32_t r = r_off; r < (uint32_t)kM; r += kHelpers / 16) {
-          uint32_t row = misc->in_tab[b][r];
-          row = row == SSB_INVALID_SLOT ? 0u : row;
-          const uint32_t dst = in_dst + r * 128 + ((sw_ch ^ (r & 7)) << 4);
-          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src_base + (size_t)row * (kD * 2)) : "memory");
-        }
-#pragma unroll 4
-        for (uint32_t r = r_off; r < (uint32_t)kN; r += kHelpers / 16) {
-          uint32_t row = misc->on_tab[b][r];
-          row = row == SSB_INVALID_SLOT ? 0u : row;
-          const uint32_t dst = on_dst + r * 128 + ((sw_ch ^ (r & 7)) << 4);
-          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src_base + (size_t)row * (kD * 2)) : "memory");
-        }
-        asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&misc->full_bar[b])) : "memory");
       }
       {
         // row_win[b] of tile it-2 was last read by epilogue 1 before g_full(it-2); this warp has seen
@@ -528,6 +523,27 @@ sgns_block_tc_kernel(const __grid_constant__ TcArgs a, const __grid_constant__ C
         __syncwarp();
         if (lane == 0) mbar_arrive(&misc->win_bar[b]);
         if (warp == kGatherWarp0) SSB_STAMP(7);
+      }
+      if (mode & 32) {
+        mbar_wait(&misc->idx_bar[b], (it >> 1) & 1);
+        if (warp == kGatherWarp0) SSB_STAMP(6);
+        const uint32_t in_dst = sbase + kOffIn + b * kInBytes + sw_lo * kInBlk;
+        const uint32_t on_dst = sbase + kOffOn + b * kOnBytes + sw_lo * kOnBlk;
+#pragma unroll 4
+        for (uint32_t r = r_off; r < (uint32_t)kM; r += kHelpers / 16) {
+          uint32_t row = misc->in_tab[b][r];
+          row = row == SSB_INVALID_SLOT ? 0u : row;
+          const uint32_t dst = in_dst + r * 128 + ((sw_ch ^ (r & 7)) << 4);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src_base + (size_t)row * (kD * 2)) : "memory");
+        }
+#pragma unroll 4
+        for (uint32_t r = r_off; r < (uint32_t)kN; r += kHelpers / 16) {
+          uint32_t row = misc->on_tab[b][r];
+          row = row == SSB_INVALID_SLOT ? 0u : row;
+          const uint32_t dst = on_dst + r * 128 + ((sw_ch ^ (r & 7)) << 4);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src_base + (size_t)row * (kD * 2)) : "memory");
+        }
+        asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&misc->full_bar[b])) : "memory");
       }
       if (it >= 1) mbar_wait(&misc->g_free, (it - 1) & 1);
       if (warp == kGatherWarp0) SSB_STAMP(8);
@@ -607,8 +623,10 @@ sgns_block_tc_kernel(const __grid_constant__ TcArgs a, const __grid_constant__ C
         m_i = 0.f;
         for (int c = c_lo; c <= c_hi; ++c) m_i += (c != self_c && !cbad[c]) ? 1.f : 0.f;
       }
-      const float w = m_i * a.neg_k * (1.0f / kNeg);
-      uint32_t ent[16], okm = 0;                // per entry: bf16 bits of dL/dS (phase B adds the G cell offset << 16)
+      const bool fold_negs = misc->ctx_has_invalid[b] == 0;   // no padding among the contexts: m_i is the plain range size
+      float neg_l = 0.f;                        // sum over this side's valid negatives of softplus(x) (weighted in phase B)
+      uint32_t ent[16], okm = 0;                // per entry: bf16 bits of dL/dS (phase B adds the G cell offset << 16);
+                                                // negatives: fp32 bits of the unweighted sigmoid until phase B
 #pragma unroll
       for (int e = 0; e < 16; ++e) {
         const int aa = e + 1, j = e - 8;
@@ -616,14 +634,18 @@ sgns_block_tc_kernel(const __grid_constant__ TcArgs a, const __grid_constant__ C
         if (e >= 8 || aa <= window) {
           const float x = (e < 8) ? (side ? v[aa] : v[kHalo - aa]) : xn[j < 0 ? 0 : j];
           const bool bad = (e < 8) ? cbad[side ? self_c + aa : self_c - aa] : cbad[kCtx + 8 * side + j];   // static offsets
-          const bool ok = !bad && ((e < 8) ? (aa <= reach) : (m_i > 0.f));
+          const bool ok = !bad && ((e < 8) ? (aa <= reach) : true);
           float sg, lt;
           sig_logt(x, sg, lt);
-          const float g = (e < 8) ? sg - 1.0f : w * sg;
-          loss_acc += ok ? ((e < 8) ? lt : w * (x + lt)) : 0.f;       // softplus(x) = x + log t
-          if (e < 8) pair_acc += ok ? 1.f : 0.f;
-          const __nv_bfloat16 hv = __float2bfloat16_rn(g);
-          ent[e] = (uint32_t)(*reinterpret_cast<const unsigned short*>(&hv));
+          if (e < 8) {
+            loss_acc += ok ? lt : 0.f;
+            pair_acc += ok ? 1.f : 0.f;
+            const __nv_bfloat16 hv = __float2bfloat16_rn(sg - 1.0f);
+            ent[e] = (uint32_t)(*reinterpret_cast<const unsigned short*>(&hv));
+          } else {
+            neg_l += ok ? (x + lt) : 0.f;                               // softplus(x) = x + log t
+            ent[e] = __float_as_uint(sg);
+          }
           okm |= ok ? (1u << e) : 0u;
         }
       }
@@ -636,6 +658,18 @@ sgns_block_tc_kernel(const __grid_constant__ TcArgs a, const __grid_constant__ C
       const bool row_dup = (rlead & 0x100u) != 0;
       const uint16_t* cm = misc->col_meta[b];
       const uint32_t g_row = li * 128, rx = li & 7;
+      // weight of this thread's negative entries: the group's summed m (leader only) when folding, else its own m_i
+      const float m_neg = fold_negs ? ((li == (uint32_t)i) ? (float)misc->row_msum[b][i] : 0.f) : m_i;
+      const float w = m_neg * a.neg_k * (1.0f / kNeg);
+      loss_acc += w * neg_l;
+      if (!(m_neg > 0.f)) okm &= 0x00FFu;       // no negative entries from this thread
+#pragma unroll
+      for (int e = 8; e < 16; ++e) {
+        const __nv_bfloat16 hv = __float2bfloat16_rn(w * __uint_as_float(ent[e]));
+        ent[e] = (uint32_t)(*reinterpret_cast<const unsigned short*>(&hv));
+      }
+      // with folded negatives a duplicated ROW no longer makes its negative cells shared (one writer: the leader)
+      const uint32_t row_shared = row_dup ? (fold_negs ? 0x00FFu : 0xFFFFu) : 0u;
       uint32_t atm = 0;
 #pragma unroll
       for (int e = 0; e < 16; ++e) {
@@ -644,7 +678,7 @@ sgns_block_tc_kernel(const __grid_constant__ TcArgs a, const __grid_constant__ C
         const uint32_t lc = meta & 0xFFu;
         const uint32_t off = g_row + (lc >> 6) * kInBlk + ((((lc >> 3) & 7) ^ rx) << 4) + ((lc & 7) << 1);   // < 49152
         ent[e] |= off << 16;
-        atm |= (row_dup || (meta & 0x100u)) ? (1u << e) : 0u;
+        atm |= (((row_shared >> e) & 1u) || (meta & 0x100u)) ? (1u << e) : 0u;
       }
       atm &= okm;
       if (warp == kE1Warp0) SSB_STAMP(15);
