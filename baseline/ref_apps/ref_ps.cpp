@@ -143,6 +143,22 @@ class RefWord2Vec : public BaseAlgorithm<rkey_t, AdaRow, Row, std::vector<rkey_t
     batch_lines_ = global_config().get_config("minibatch_lines").to_int32();
     num_iters_ = global_config().get_config("num_iters").to_int32();
     threads_ = global_config().get_config("async_channel_thread_num").to_int32();
+    prepopulate_ = global_config().get_config("prepopulate").to_int32();
+  }
+  // Create every input and output row before the timed region (the GPU arm does the same with its table: a
+  // steady-state model whose rows all exist). The reference creates rows lazily on the first pull
+  // (PullAccessAgent::get_pull_value, parameter/sparsetable.h:142-149), so pulling every key once does it.
+  void populate_all() {
+    const rkey_t total = 2u * vocab_;
+    const rkey_t chunk = 50000;
+    cache_t cache;
+    for (rkey_t k0 = 0; k0 < total; k0 += chunk) {
+      std::unordered_set<rkey_t> keys;
+      for (rkey_t k = k0; k < std::min(total, k0 + chunk); ++k) keys.insert(k);
+      global_pull_access<rkey_t, AdaRow, Row>().pull_with_barrier(keys, cache);
+      cache.params().clear();
+      cache.grads().clear();
+    }
   }
   rcd_t parse_record(const std::string& line) override {
     rcd_t out;
@@ -171,6 +187,7 @@ class RefWord2Vec : public BaseAlgorithm<rkey_t, AdaRow, Row, std::vector<rkey_t
   void train() override {
     build_unigram_table();
     create_async_channel();
+    if (prepopulate_) populate_all();
     std::vector<std::unique_ptr<ThreadState>> states;
     for (int t = 0; t < threads_; ++t) { states.emplace_back(new ThreadState); states.back()->rng.seed(12345 + 977 * t); }
     double t0 = now_s();
@@ -212,7 +229,7 @@ class RefWord2Vec : public BaseAlgorithm<rkey_t, AdaRow, Row, std::vector<rkey_t
   }
   void train_batch(ThreadState& st);
   unsigned vocab_;
-  int window_, negative_, neg_pool_, batch_lines_, num_iters_, threads_;
+  int window_, negative_, neg_pool_, batch_lines_, num_iters_, threads_, prepopulate_ = 0;
   std::vector<rkey_t> neg_words_;
   std::vector<double> neg_cdf_;
 };

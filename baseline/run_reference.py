@@ -71,7 +71,7 @@ def _write_conf(wd, n_nodes, extra):
     common = {
         "async_exec_num": 4, "listen_thread_num": 1, "init_timeout": 120, "master_time_out": 120,
         "master_longest_alive_duration": 3600, "frag_num": 1024, "shard_num": 8, "param_backup_period": 0,
-        "param_backup_root": wd, "num_iters": 1, "learning_rate": 0.05, "async_channel_thread_num": 2, "optimizer": "adagrad", "neg_pool": 16,
+        "param_backup_root": wd, "num_iters": 1, "learning_rate": 0.05, "async_channel_thread_num": 2, "optimizer": "adagrad", "neg_pool": 16, "prepopulate": 0,
         "local_train": 0, "master_addr": "tcp://127.0.0.1:%d" % port,
     }
     common.update(extra)
@@ -171,7 +171,7 @@ def run(args):
     sys.path.insert(0, os.path.dirname(HERE))
     from swiftsnails_b200.models.word2vec import synthetic_corpus  # data generator only (shared corpus shape)
 
-    sent_len = 1000
+    sent_len = int(getattr(args, "sent_len", 1024))
     tokens = max(sent_len * 8, (args.ref_tokens // sent_len) * sent_len)
     wd = tempfile.mkdtemp(prefix="ssb200_refdata_")
     data_files = []
@@ -186,6 +186,7 @@ def run(args):
     lr = float(getattr(args, "lr", 0.05))
     optimizer = getattr(args, "optimizer", "adagrad")
     neg_pool = int(getattr(args, "neg_pool", 16))
+    prepop = int(getattr(args, "prepopulate", 1))
     sweep = [int(x) for x in str(getattr(args, "ref_minibatch_lines", "4,16")).split(",") if x]
     # a few hundred thousand tokens of a 1M-word vocabulary move the loss only a little (AdaGrad's first update of a
     # row is a full lr-sized step, which can lift the mean by a fraction of a percent): a run counts when its loss is
@@ -195,7 +196,8 @@ def run(args):
     best, tried, last_err = None, [], None
     for mb in sweep:
         conf = {"dim": args.dim, "vocab": args.vocab, "window": args.window, "negative": args.negatives, "neg_pool": neg_pool,
-                "minibatch_lines": mb, "learning_rate": lr, "optimizer": optimizer, "async_channel_thread_num": threads}
+                "minibatch_lines": mb, "learning_rate": lr, "optimizer": optimizer, "async_channel_thread_num": threads,
+                "prepopulate": prepop}
         res, err = _one_run(n, conf, data_files)
         if err and threads > 1:
             # the reference's StateBarrier can lose a wake-up when many threads block at once: one retry, single-threaded
@@ -228,7 +230,7 @@ def run(args):
                    "negatives": args.negatives, "neg_pool_per_128_pair_tile": neg_pool, "tokens_per_worker": tokens, "seq_len": sent_len,
                    "optimizer": optimizer, "lr": lr, "minibatch_lines": best["minibatch_lines"], "minibatch_sweep": tried,
                    "worker_threads": best["threads"], "data_path": "text corpus file read by scan_file_by_line inside the timed region",
-                   "table": "empty at start, rows created lazily inside the timed region",
+                   "table": "all 2*vocab rows created before timing" if prepop else "empty at start, rows created lazily inside the timed region",
                    "parallelism": "1 master + %d servers + %d workers over ZeroMQ on the host CPUs" % (n, n),
                    "hash_map": "std::unordered_map stand-in for google::dense_hash_map",
                    "timing": "words / max over workers of the time inside train(); fixed sleeps excluded",
@@ -256,4 +258,6 @@ if __name__ == "__main__":
     ap.add_argument("--lr", type=float, default=0.05)
     ap.add_argument("--optimizer", default="adagrad")
     ap.add_argument("--neg-pool", type=int, default=16)
+    ap.add_argument("--prepopulate", type=int, default=1)
+    ap.add_argument("--sent-len", type=int, default=1024)
     print(json.dumps(run(ap.parse_args())))

@@ -45,15 +45,20 @@ def parse_args():
     ap.add_argument("--tile-impl", default="auto", choices=["auto", "cuda_core", "tcgen05", "tcgen05_direct"])
     ap.add_argument("--lr", type=float, default=0.05)
     ap.add_argument("--zipf-s", type=float, default=1.0)
-    ap.add_argument("--shadow", type=int, default=-1, help="bf16 mirror of the table rows, read by the pull (half the row bytes over NVLink); -1 = auto: on from 4 GPUs (measured: 0.563 -> 0.532 ms/step at 8 GPUs, neutral at 2, -3%% at 1)")
+    ap.add_argument("--shadow", type=int, default=1, help="bf16 mirror of the table rows, read by the pull (half the row bytes over NVLink); on at every GPU count so that the scaling curve is ONE configuration (it costs ~3%% on one GPU)")
     ap.add_argument("--inbox-bf16", type=int, default=1, help="ship inbox gradient rows as bf16")
     ap.add_argument("--inbox-barrier", default="flags", choices=["flags", "nccl"])
     ap.add_argument("--inbox", type=int, default=1, help="multi-GPU AdaGrad push through owner inboxes (one-way) instead of remote atomics")
     ap.add_argument("--prepopulate", type=int, default=1, help="create all 2*vocab rows before timing (steady-state table)")
     ap.add_argument("--pipeline", type=int, default=1, help="overlap dedup+pull of step i+1 with SGNS+push of step i (2 streams)")
     ap.add_argument("--tc-mode", type=int, default=33, help="tcgen05 kernel mode bits (32 = cp.async gather warps (default), 1 = TMA gather4; 2 / 16 / 64 = perf experiments; 8 = round-1 serial kernel)")
-    ap.add_argument("--slot-cache", type=int, default=-1, help="worker-side key->slot cache (starts empty after the table is populated; fills from the warm-up steps on); -1 = auto: on from 2 GPUs")
-    ap.add_argument("--ref-tokens", type=int, default=60_000, help="tokens per worker for the reference arm")
+    ap.add_argument("--slot-cache", type=int, default=1, help="worker-side key->slot cache (starts empty after the table is populated; fills from the warm-up steps on); on at every GPU count (same configuration for the whole scaling curve)")
+    ap.add_argument("--windows", type=int, default=5, help="timed windows of exactly --steps steps each; the reported value is the median window")
+    ap.add_argument("--sent-len", type=int, default=1024, help="tokens per sentence (pairs never cross sentences); divides tokens-per-step so the text arm reads whole minibatches")
+    ap.add_argument("--text-arm", type=int, default=1, help="also time Word2VecTrainer.train_file on a text corpus file (the reference arm's input format)")
+    ap.add_argument("--fp32-tile", type=int, default=1, help="also time a few steps with the fp32 CUDA-core tile kernel (config.fp32_tile_ms_per_step)")
+    ap.add_argument("--ref-minibatch-lines", default="8,32", help="reference arm: minibatch sizes (sentences) to sweep; the fastest run that trains is reported")
+    ap.add_argument("--ref-tokens", type=int, default=204_800, help="tokens per worker for the reference arm")
     return ap.parse_args()
 
 
@@ -91,14 +96,14 @@ def run_ours(args):
                                   and os.environ.get("SSB200_NO_TC") != "1") else "cuda_core"
     cfg = Word2VecConfig(vocab=args.vocab, dim=args.dim, window=args.window, negatives=args.negatives,
                          neg_pool=args.neg_pool, tokens_per_step=args.tokens_per_step, lr=args.lr,
-                         optimizer=args.optimizer, seed=1 + rank, tile_impl=tile_impl, zipf_s=args.zipf_s,
-                         slot_cache=(args.impl == "ours" and (world > 1 if args.slot_cache < 0 else bool(args.slot_cache))))
+                         optimizer=args.optimizer, seed=1 + rank, tile_impl=tile_impl, zipf_s=args.zipf_s, sent_len=args.sent_len,
+                         slot_cache=(args.impl == "ours" and bool(args.slot_cache)))
     # 2*vocab keys (input + output vectors) spread over `world` shards at load factor 0.5
     rows_per_shard = (2 * cfg.vocab + world - 1) // world
     use_inbox = args.impl == "ours" and args.inbox and world > 1 and cfg.optimizer == "adagrad"
     # bf16 mirror of the rows for the (bf16-only) pull; kept in step by owner-side writers, so it is
     # enabled when every push is applied by the owner (single GPU, or the inbox push)
-    shadow_on = (world >= 4) if args.shadow < 0 else bool(args.shadow)
+    shadow_on = bool(args.shadow)
     with_shadow = (shadow_on or tile_impl == "tcgen05_direct") and args.impl == "ours" and tile_impl.startswith("tcgen05") and (world == 1 or use_inbox)
     table = make_table(rows_per_shard, cfg.dim, dev, with_state=(cfg.optimizer == "adagrad"),
                        init_scale=1.0 / cfg.dim, frag_num=max(1024, world), with_shadow=with_shadow)
@@ -139,31 +144,47 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    NW = max(1, args.windows)
+
+    def median(xs):
+        xs = sorted(xs)
+        return xs[len(xs) // 2]
+
     # ---------------- device-timed arm: batches already on the device -------------------------
+    # W warm-up steps, then NW windows of exactly K steps each, every window bracketed by a barrier + synchronize
+    # and timed with CUDA events (max over ranks); the reported value is the median window. The K + W distinct
+    # batches are cycled through (the table keeps training, so no window repeats another's state).
     worker = Word2VecWorker(cfg, table, dev, pipeline=bool(args.pipeline) and args.impl == "ours")
     worker.tma_mode = args.tc_mode
     dev_tokens = host.to(dev)
+    nb = dev_tokens.shape[0]
     for s in range(W):
         worker.step(dev_tokens[s])
     worker.flush()
     barrier()
     sampler = ClockSampler(gpu_index=local).start()
     time.sleep(0.3)
-    worker.reset_loss()
-    launches0 = _lib.launch_count
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.time()
-    e0.record()
-    for s in range(W, W + K):
-        worker.step(dev_tokens[s])
-    worker.flush()
-    e1.record()
-    barrier()
+    win_ms, launches, loss_dev, n_pairs = [], 0, None, 0.0
+    cur = W
+    for wdx in range(NW):
+        worker.reset_loss()
+        launches0 = _lib.launch_count
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for s in range(K):
+            worker.step(dev_tokens[cur % nb])
+            cur += 1
+        worker.flush()
+        e1.record()
+        barrier()
+        launches = _lib.launch_count - launches0
+        win_ms.append(max_over_ranks(e0.elapsed_time(e1)))
+        loss_dev = worker.mean_loss()
+        n_pairs = float(worker.loss[1].item())
     t1 = time.time()
-    launches = _lib.launch_count - launches0
-    ms = max_over_ranks(e0.elapsed_time(e1))
-    loss_dev = worker.mean_loss()
-    n_pairs = float(worker.loss[1].item())
+    ms = median(win_ms)
     n_unique_last = int(worker.n_unique.item())
     sampler.stop()
     clocks = sampler.summary(t0, t1)
@@ -173,19 +194,89 @@ def run_ours(args):
     trainer = Word2VecTrainer(cfg, table, dev, pipeline=bool(args.pipeline) and args.impl == "ours")
     trainer.worker.tma_mode = args.tc_mode
     trainer.worker.step_idx = worker.step_idx
+    nbe = host_e2e.shape[0]
     for s in range(W):
         trainer.train_step(host_e2e[s])
     trainer.finish()
-    barrier()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record()
-    for s in range(W, W + K):
-        trainer.train_step(host_e2e[s])
-    last_loss = trainer.finish()
-    trainer.worker.flush()
-    f1.record()
-    barrier()
-    ms_e2e = max_over_ranks(f0.elapsed_time(f1))
+    e2e_ms, last_loss = [], None
+    cur = W
+    for wdx in range(NW):
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for s in range(K):
+            trainer.train_step(host_e2e[cur % nbe])
+            cur += 1
+        last_loss = trainer.finish()
+        trainer.worker.flush()
+        f1.record()
+        barrier()
+        e2e_ms.append(max_over_ranks(f0.elapsed_time(f1)))
+    ms_e2e = median(e2e_ms)
+
+    # ---------------- text arm: the same public API fed from a corpus FILE (the reference arm's input) ----------
+    # Word2VecTrainer.train_file: native parallel reader -> pinned batches -> H2D -> step -> D2H loss. The whole
+    # call is timed (its first steps included), over K + W minibatches per rank.
+    text = None
+    if args.text_arm and args.impl == "ours" and B % args.sent_len == 0:
+        import tempfile
+
+        tdir = tempfile.mkdtemp(prefix="ssb200_text_")
+        tpath = os.path.join(tdir, "corpus%d.txt" % rank)
+        arr = host_e2e.numpy().view(np.uint32).reshape(-1, args.sent_len)
+        with open(tpath, "w") as f:
+            for row in arr:
+                f.write(" ".join(map(str, row.tolist())))
+                f.write("\n")
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tw0 = time.time()
+        g0.record()
+        # negatives stay on the synthetic corpus' noise distribution, as in the other arms
+        n_tok_text, text_loss = trainer.train_file(tpath, corpus_noise=False)
+        trainer.worker.flush()
+        g1.record()
+        barrier()
+        ms_text = max_over_ranks(g0.elapsed_time(g1))
+        text = {"value": float(n_tok_text) * world / (ms_text / 1e3), "unit": "words/s", "steps": trainer.steps_done,
+                "ms_per_step": ms_text / max(trainer.steps_done, 1), "wall_ms": (time.time() - tw0) * 1e3,
+                "file_bytes_per_rank": os.path.getsize(tpath), "loss_last": text_loss,
+                "includes": "text parse by the native loader threads + H2D + step + D2H loss, every step"}
+        os.unlink(tpath)
+        os.rmdir(tdir)
+
+    # ---------------- fp32 tile kernel (CUDA cores, fp32 operands): the step at the reference's operand precision ----
+    fp32_ms = None
+    if args.fp32_tile and args.impl == "ours" and tile_impl.startswith("tcgen05"):
+        import dataclasses
+
+        cfg32 = dataclasses.replace(cfg, tile_impl="cuda_core")
+        w32 = Word2VecWorker(cfg32, table, dev, pipeline=bool(args.pipeline))
+        w32.step_idx = trainer.worker.step_idx
+        n32 = min(8, host.shape[0])
+        d32 = host[:n32].to(dev)
+        for s in range(3):
+            w32.step(d32[s % n32])
+        w32.flush()
+        barrier()
+        h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        h0.record()
+        for s in range(3, 8):
+            w32.step(d32[s % n32])
+        w32.flush()
+        h1.record()
+        barrier()
+        fp32_ms = max_over_ranks(h0.elapsed_time(h1)) / 5.0
+        del w32, d32
+
+    # ---------------- lost updates: table full / inbox overflow must both be zero -----------------------------
+    health = {"table_full": int(table.stats[1].item()) if hasattr(table, "stats") else 0, "inbox_overflow": 0}
+    if getattr(table, "inbox", None) is not None:
+        health["inbox_overflow"] = int(table.inbox.overflow.item())
+    if world > 1:
+        ht = torch.tensor([health["table_full"], health["inbox_overflow"]], dtype=torch.int64, device=dev)
+        dist.all_reduce(ht)
+        health = {"table_full": int(ht[0].item()), "inbox_overflow": int(ht[1].item())}
 
     words = float(K) * B * world
     value = words / (ms / 1e3)
@@ -201,11 +292,17 @@ def run_ours(args):
                        "neg_pool_per_128_pair_tile": cfg.neg_pool, "global_batch": B * world,
                        "tokens_per_step_per_gpu": B, "seq_len": cfg.sent_len, "optimizer": cfg.optimizer,
                        "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if args.impl == "nccl" else "P2P"),
-                       "bf16_row_mirror": with_shadow, "worker_slot_cache": bool(cfg.slot_cache), "inbox_push": bool(use_inbox), "inbox_rows_bf16": bool(use_inbox and args.inbox_bf16),
+                       "bf16_row_mirror": with_shadow, "worker_slot_cache": bool(cfg.slot_cache),
+                       "inbox_push": bool(use_inbox), "inbox_rows_bf16": bool(use_inbox and args.inbox_bf16),
+                       "same_switches_at_every_gpu_count": "slot cache, bf16 row mirror and bf16 inbox rows are on for every N; the inbox itself only exists with peers (N > 1)",
+                       "timed_windows": NW, "window_ms_per_step": [round(x / K, 5) for x in win_ms],
+                       "e2e_window_ms_per_step": [round(x / K, 5) for x in e2e_ms],
+                       "fp32_tile_ms_per_step": fp32_ms, "e2e_text": text,
                        "table": "all 2*vocab rows created before timing" if args.prepopulate else "empty at start, rows created lazily inside the timed region",
                        "pipeline": "3 streams: dedup+pull of step i+1 | SGNS of step i | push of step i-1 (staleness <= 1 step)" if worker.pipeline else "off",
                        "tile_impl": tile_impl, "pairs_per_step_per_gpu": n_pairs / K, "unique_keys_last_step": n_unique_last,
-                       "precision": "bf16 tensor-core operands (tcgen05), fp32 accumulate, fp32 master table / AdaGrad state / gradients",
+                       "precision": ("bf16 tensor-core operands (tcgen05), fp32 accumulate, fp32 master table / AdaGrad state, fp32 gradient accumulation on the worker"
+                                     + ("; gradient rows cross NVLink as bf16 and are applied in fp32 by the owner" if (use_inbox and args.inbox_bf16) else "")),
                        "l2": "no flush: table (%.2f GiB/shard) and caches exceed the 126 MB L2"
                              % (table.owned[0].nbytes() / 2 ** 30)},
             "clocks": clocks,
@@ -213,11 +310,14 @@ def run_ours(args):
                     "h2d_bytes_per_step": trainer.h2d_bytes, "d2h_bytes_per_step": trainer.d2h_bytes},
             "gpu_launches": launches,
             "loss": {"device_arm_mean": loss_dev, "e2e_last": last_loss},
+            "health": health,
         }
         print(json.dumps(out))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if health["table_full"] or health["inbox_overflow"]:
+        raise SystemExit("bench.py: updates were lost during the run: %r" % (health,))
 
 
 def run_reference(args):
