@@ -229,7 +229,15 @@ def run_ours(args):
                 f.write(" ".join(map(str, row.tolist())))
                 f.write("\n")
         barrier()
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0, g1, gw = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        marks = {}
+
+        def _mark(step):                      # after the W-th minibatch: start of the steady-state span
+            if step == W:
+                trainer.worker.flush()
+                gw.record()
+                marks["tokens_before"] = step * B
+        trainer.on_step = _mark
         tw0 = time.time()
         g0.record()
         # negatives stay on the synthetic corpus' noise distribution, as in the other arms
@@ -237,10 +245,15 @@ def run_ours(args):
         trainer.worker.flush()
         g1.record()
         barrier()
+        trainer.on_step = None
         ms_text = max_over_ranks(g0.elapsed_time(g1))
-        text = {"value": float(n_tok_text) * world / (ms_text / 1e3), "unit": "words/s", "steps": trainer.steps_done,
-                "ms_per_step": ms_text / max(trainer.steps_done, 1), "wall_ms": (time.time() - tw0) * 1e3,
-                "file_bytes_per_rank": os.path.getsize(tpath), "loss_last": text_loss,
+        ms_steady = max_over_ranks(gw.elapsed_time(g1)) if marks else ms_text
+        n_steady = trainer.steps_done - (W if marks else 0)
+        text = {"value": float(n_steady) * B * world / (ms_steady / 1e3), "unit": "words/s", "steps": n_steady,
+                "ms_per_step": ms_steady / max(n_steady, 1),
+                "whole_call": {"steps": trainer.steps_done, "ms": ms_text, "wall_ms": (time.time() - tw0) * 1e3,
+                               "note": "includes opening, mapping and indexing the file and the first (warm-up) steps"},
+                "file_bytes_per_rank": os.path.getsize(tpath), "loss_last": text_loss, "host_cpus": os.cpu_count(),
                 "includes": "text parse by the native loader threads + H2D + step + D2H loss, every step"}
         os.unlink(tpath)
         os.rmdir(tdir)

@@ -33,7 +33,7 @@ class MappedFile {
     if (fd_ < 0) return;
     struct stat st;
     if (::fstat(fd_, &st) != 0 || st.st_size <= 0) return;
-    void* p = ::mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd_, 0);
+    void* p = ::mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE | MAP_POPULATE, fd_, 0);   // pre-fault: one bulk pass, not a fault per page
     if (p == MAP_FAILED) return;
     data_ = static_cast<const char*>(p);
     size_ = (size_t)st.st_size;
