@@ -47,7 +47,7 @@ def parse_args():
     ap.add_argument("--zipf-s", type=float, default=1.0)
     ap.add_argument("--shadow", type=int, default=1, help="bf16 mirror of the table rows, read by the pull (half the row bytes over NVLink); on at every GPU count so that the scaling curve is ONE configuration (it costs ~3%% on one GPU)")
     ap.add_argument("--inbox-bf16", type=int, default=1, help="ship inbox gradient rows as bf16")
-    ap.add_argument("--inbox-barrier", default="flags", choices=["flags", "nccl"])
+    ap.add_argument("--inbox-barrier", default="flags", choices=["flags", "nccl", "chunks"], help="hand-off of the multi-GPU inbox push: flags / nccl = ship everything, then apply; chunks = 256-row chunks applied as they land (ship and apply overlap)")
     ap.add_argument("--inbox", type=int, default=1, help="multi-GPU AdaGrad push through owner inboxes (one-way) instead of remote atomics")
     ap.add_argument("--prepopulate", type=int, default=1, help="create all 2*vocab rows before timing (steady-state table)")
     ap.add_argument("--pipeline", type=int, default=1, help="overlap dedup+pull of step i+1 with SGNS+push of step i (2 streams)")
@@ -286,6 +286,8 @@ def run_ours(args):
     health = {"table_full": int(table.stats[1].item()) if hasattr(table, "stats") else 0, "inbox_overflow": 0}
     if getattr(table, "inbox", None) is not None:
         health["inbox_overflow"] = int(table.inbox.overflow.item())
+        if hasattr(table.inbox, "err"):
+            health["inbox_overflow"] += int(table.inbox.err.item())      # an apply wait ran out: rows were skipped
     if world > 1:
         ht = torch.tensor([health["table_full"], health["inbox_overflow"]], dtype=torch.int64, device=dev)
         dist.all_reduce(ht)
@@ -307,6 +309,7 @@ def run_ours(args):
                        "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if args.impl == "nccl" else "P2P"),
                        "bf16_row_mirror": with_shadow, "worker_slot_cache": bool(cfg.slot_cache),
                        "inbox_push": bool(use_inbox), "inbox_rows_bf16": bool(use_inbox and args.inbox_bf16),
+                       "inbox_handoff": args.inbox_barrier if use_inbox else None,
                        "same_switches_at_every_gpu_count": "slot cache, bf16 row mirror and bf16 inbox rows are on for every N; the inbox itself only exists with peers (N > 1)",
                        "timed_windows": NW, "window_ms_per_step": [round(x / K, 5) for x in win_ms],
                        "e2e_window_ms_per_step": [round(x / K, 5) for x in e2e_ms],

@@ -18,6 +18,7 @@
 // warp that never waits, so this cannot deadlock). No deletion, no rehash: capacity is fixed,
 // which is also what makes caching (shard, slot) on the worker legal.
 #include <cuda_bf16.h>
+#include <algorithm>
 #include <cstdlib>
 #include "common.cuh"
 
@@ -709,6 +710,196 @@ push_send_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__
   }
 }
 
+// ---- chunked inbox push: ship and apply overlap -----------------------------------------------------
+// The inbox push above hands a whole shipment over at once (send -> publish counts -> wait for every sender ->
+// apply), so NVLink shipping and the owner's HBM update never overlap. Here a sender's sub-region is cut into
+// chunks of kChunkRows rows; blocks of the send kernel count the rows they have written into each chunk
+// (local atomics) and the block that completes a chunk raises its ready flag on the owner (st.release.sys);
+// the last block publishes the total. The owner's apply kernel — on another stream, next to its own send
+// kernel — takes (sender, chunk) items as they become ready. Flags carry the step number, so nothing is
+// cleared on the owner. ref: global_push_access.h:123-149 + server/init.h:116-132 ("send (key, grad)*, the
+// server applies"), carried by NVLink stores and pipelined chunk by chunk.
+constexpr uint32_t kChunkRows = 256;
+
+struct SendChunkState {          // sender-local device memory, zero before the first call
+  uint32_t* cursor;              // [SSB_MAX_SHARDS] rows claimed per owner this step
+  uint32_t* done;                // [SSB_MAX_SHARDS][max_chunks] rows written per (owner, chunk) this step
+  uint32_t* finished;            // [1] blocks of the send kernel that are done
+};
+
+template <bool kAdaGrad>
+__global__ void __launch_bounds__(256)
+push_send_chunks_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__ SsbChunkInboxView ib,
+                        const uint32_t* __restrict__ gslot, const float* __restrict__ grads, int64_t n,
+                        const uint32_t* __restrict__ n_dev, int self_shard, float lr, float eps, uint32_t tag,
+                        uint32_t* __restrict__ overflow, SendChunkState st) {
+  __shared__ uint32_t cnt[SSB_MAX_SHARDS], base[SSB_MAX_SHARDS];
+  __shared__ uint32_t row_slot[kSendRows];
+  __shared__ uint16_t row_owner[kSendRows], row_rank[kSendRows];
+  __shared__ uint32_t is_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t ne = effective_n(n, n_dev);
+  const int D = v.dim;
+  for (uint32_t r0 = blockIdx.x * kSendRows; r0 < ne; r0 += gridDim.x * kSendRows) {
+    if (threadIdx.x < SSB_MAX_SHARDS) cnt[threadIdx.x] = 0;
+    __syncthreads();
+    if (threadIdx.x < kSendRows) {
+      const uint32_t r = r0 + threadIdx.x;
+      uint32_t g = (r < ne) ? __ldg(gslot + r) : SSB_INVALID_SLOT;
+      uint16_t o = 0xFFFF, rk = 0;
+      uint32_t sl = 0;
+      if (g != SSB_INVALID_SLOT) {
+        o = (uint16_t)(g / v.capacity);
+        sl = g - (uint32_t)o * v.capacity;
+        if ((int)o != self_shard) rk = (uint16_t)atomicAdd(&cnt[o], 1u);
+      }
+      row_owner[threadIdx.x] = o; row_rank[threadIdx.x] = rk; row_slot[threadIdx.x] = sl;
+    }
+    __syncthreads();
+    if (threadIdx.x < v.num_shards && cnt[threadIdx.x]) base[threadIdx.x] = atomicAdd(st.cursor + threadIdx.x, cnt[threadIdx.x]);
+    __syncthreads();
+    for (int k = warp; k < kSendRows; k += 8) {
+      const uint32_t r = r0 + k;
+      const int o = row_owner[k];
+      if (o == 0xFFFF) continue;
+      const float* gr = grads + (size_t)r * D;
+      if (o == self_shard) {
+        // local row: apply directly
+        float* row = v.rows[o] + (size_t)row_slot[k] * D;
+        float* stt = kAdaGrad ? v.state[o] + (size_t)row_slot[k] * D : nullptr;
+        __nv_bfloat16* sh = v.shadow[o] ? reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)row_slot[k] * D : nullptr;
+        for (int j = lane * 4; j < D; j += 128) {
+          float4 gv = *reinterpret_cast<const float4*>(gr + j);
+          if (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
+          float4 d;
+          if (kAdaGrad) {
+            float4 g2 = make_float4(gv.x * gv.x, gv.y * gv.y, gv.z * gv.z, gv.w * gv.w);
+            float4 a = atom_add_f4_sys(stt + j, g2);
+            d.x = -lr * gv.x * rsqrtf(a.x + g2.x + eps); d.y = -lr * gv.y * rsqrtf(a.y + g2.y + eps);
+            d.z = -lr * gv.z * rsqrtf(a.z + g2.z + eps); d.w = -lr * gv.w * rsqrtf(a.w + g2.w + eps);
+          } else {
+            d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
+          }
+          row_update_f4(row + j, sh ? sh + j : nullptr, d);
+        }
+      } else {
+        const uint32_t idx = base[o] + row_rank[k];
+        if (idx >= ib.seg_rows) { if (lane == 0) atomicAdd(overflow, 1u); continue; }
+        if (lane == 0) ib.slots[o][idx] = row_slot[k];
+        __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(ib.rows[o]) + (size_t)idx * D;
+        for (int j = lane * 4; j < D; j += 128) *reinterpret_cast<uint2*>(dst + j) = pack_bf16x4(*reinterpret_cast<const float4*>(gr + j));
+      }
+    }
+    __threadfence_system();     // this thread's peer stores are performed before the block reports them
+    __syncthreads();
+    if (threadIdx.x < v.num_shards && cnt[threadIdx.x] && (int)threadIdx.x != self_shard) {
+      const uint32_t o = threadIdx.x;
+      const uint32_t lo = min(base[o], ib.seg_rows), hi = min(base[o] + cnt[o], ib.seg_rows);   // rows past the region were dropped
+      for (uint32_t c = lo / kChunkRows; c * kChunkRows < hi; ++c) {
+        const uint32_t a = max(lo, c * kChunkRows), b = min(hi, (c + 1) * kChunkRows);
+        if (b <= a) continue;
+        const uint32_t old = atomicAdd(st.done + (size_t)o * ib.max_chunks + c, b - a);
+        if (old + (b - a) == kChunkRows) {
+          __threadfence_system();   // order the other blocks' rows (seen through the counter) before the flag
+          st_release_sys(ib.ready[o] + c, tag);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  // last block out: publish the totals (which also cover each region's last, partial chunk), reset the step state
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    is_last = (atomicAdd(st.finished, 1u) == gridDim.x - 1) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence_system();
+    __shared__ uint32_t tot[SSB_MAX_SHARDS];
+    if (threadIdx.x < SSB_MAX_SHARDS) {
+      uint32_t t = 0;
+      if ((int)threadIdx.x < v.num_shards && (int)threadIdx.x != self_shard) {
+        t = min(*((volatile uint32_t*)(st.cursor + threadIdx.x)), ib.seg_rows);
+        *((volatile uint32_t*)ib.total[threadIdx.x]) = t;
+        st_release_sys(ib.total[threadIdx.x] + 1, tag);
+      }
+      tot[threadIdx.x] = t;
+      st.cursor[threadIdx.x] = 0;
+    }
+    __syncthreads();
+    for (int o = 0; o < v.num_shards; ++o) {
+      const uint32_t nc = (tot[o] + kChunkRows - 1) / kChunkRows;
+      for (uint32_t c = threadIdx.x; c < nc; c += blockDim.x) st.done[(size_t)o * ib.max_chunks + c] = 0;
+    }
+    if (threadIdx.x == 0) *st.finished = 0;
+  }
+}
+
+// Owner side: items (chunk c, sender s), chunk-major so that the first chunks of every sender come first. A block
+// waits (bounded) until its item is known — the chunk's ready flag carries this step's tag, or the sender's total
+// does (then the chunk holds min(C, total - c*C) rows, possibly none) — and applies it to the local shard.
+// A wait that runs out sets err[0] and gives up on the item (reported by the host) instead of trapping.
+template <bool kAdaGrad>
+__global__ void __launch_bounds__(256)
+push_apply_chunks_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ slots,
+                         const __nv_bfloat16* __restrict__ rows, const uint32_t* __restrict__ ready,
+                         const uint32_t* __restrict__ total, uint32_t seg_rows, uint32_t max_chunks, int world, int self,
+                         uint32_t tag, float lr, float eps, uint32_t spin_limit, uint32_t* __restrict__ err) {
+  __shared__ uint32_t n_rows_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int D = v.dim;
+  const uint32_t items = max_chunks * (uint32_t)world;
+  for (uint32_t item = blockIdx.x; item < items; item += gridDim.x) {
+    const uint32_t c = item / (uint32_t)world;
+    const int s = (int)(item - c * (uint32_t)world);
+    if (s == self) continue;
+    if (threadIdx.x == 0) {
+      uint32_t n = 0, it = 0;
+      for (;;) {
+        if (ld_acquire_sys(ready + (size_t)s * max_chunks + c) == tag) { n = kChunkRows; break; }
+        if (ld_acquire_sys(total + 2 * s + 1) == tag) {
+          const uint32_t t = *((const volatile uint32_t*)(total + 2 * s));
+          n = t > c * kChunkRows ? min(kChunkRows, t - c * kChunkRows) : 0u;
+          break;
+        }
+        __nanosleep(100);
+        if (++it > spin_limit) { atomicExch(err, 1u); break; }
+      }
+      n_rows_s = n;
+    }
+    __syncthreads();
+    const uint32_t nr = n_rows_s;
+    const size_t seg0 = (size_t)s * seg_rows + (size_t)c * kChunkRows;
+    for (uint32_t r = warp; r < nr; r += 8) {
+      const uint32_t sl = __ldg(slots + seg0 + r);
+      if (sl >= v.capacity) continue;
+      float* row = v.rows[0] + (size_t)sl * D;
+      float* stt = kAdaGrad ? v.state[0] + (size_t)sl * D : nullptr;
+      __nv_bfloat16* sh = v.shadow[0] ? reinterpret_cast<__nv_bfloat16*>(v.shadow[0]) + (size_t)sl * D : nullptr;
+      const __nv_bfloat16* gr = rows + (seg0 + r) * D;
+      for (int j = lane * 4; j < D; j += 128) {
+        const uint2 pk = *reinterpret_cast<const uint2*>(gr + j);
+        const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162*>(&pk.x), hi = *reinterpret_cast<const __nv_bfloat162*>(&pk.y);
+        const float2 a01 = __bfloat1622float2(lo), a23 = __bfloat1622float2(hi);
+        const float4 gv = make_float4(a01.x, a01.y, a23.x, a23.y);
+        if (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
+        float4 d;
+        if (kAdaGrad) {
+          float4 g2 = make_float4(gv.x * gv.x, gv.y * gv.y, gv.z * gv.z, gv.w * gv.w);
+          float4 a = atom_add_f4_sys(stt + j, g2);
+          d.x = -lr * gv.x * rsqrtf(a.x + g2.x + eps); d.y = -lr * gv.y * rsqrtf(a.y + g2.y + eps);
+          d.z = -lr * gv.z * rsqrtf(a.z + g2.z + eps); d.w = -lr * gv.w * rsqrtf(a.w + g2.w + eps);
+        } else {
+          d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
+        }
+        row_update_f4(row + j, sh ? sh + j : nullptr, d);
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // ---- bulk load (checkpoint resume; new capability, the reference never reads a dump back) ----
 __global__ void __launch_bounds__(256)
 table_load_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ keys,
@@ -922,6 +1113,47 @@ int ssb_push_send2(const SsbTableView* view, const SsbInboxView* inbox, const ui
   if (adagrad) { if (bf16_rows) SSB_SEND(true, true); else SSB_SEND(true, false); }
   else { if (bf16_rows) SSB_SEND(false, true); else SSB_SEND(false, false); }
 #undef SSB_SEND
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_push_send_chunks(const SsbTableView* view, const SsbChunkInboxView* inbox, const uint32_t* gslot, const float* grads,
+                         int64_t n, const uint32_t* n_dev, int32_t self_shard, float lr, float eps, int32_t adagrad, uint32_t tag,
+                         uint32_t* overflow, uint32_t* cursor, uint32_t* done, uint32_t* finished, void* stream) {
+  if (int e = check_view(view)) return e;
+  if (!inbox || inbox->seg_rows == 0 || inbox->seg_rows % ssb::kChunkRows != 0 ||
+      inbox->max_chunks != inbox->seg_rows / ssb::kChunkRows || (view->dim & 3) != 0 || !overflow || !cursor || !done ||
+      !finished || tag == 0)
+    return (int)cudaErrorInvalidValue;
+  if (n < 0) n = 0;
+  // the kernel always runs (also with n == 0): its last block publishes this step's totals to every owner
+  int blocks = ssb::grid_for(n > 0 ? n : 1, ssb::kSendRows, ssb::kNumSMs * 8);
+  ssb::SendChunkState st{cursor, done, finished};
+  if (adagrad)
+    ssb::push_send_chunks_kernel<true><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, tag, overflow, st);
+  else
+    ssb::push_send_chunks_kernel<false><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, tag, overflow, st);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
+
+int ssb_push_apply_chunks(const SsbTableView* local_view, const uint32_t* slots, const void* rows_bf16, const uint32_t* ready,
+                          const uint32_t* total, uint32_t seg_rows, int32_t world, int32_t self, uint32_t tag, float lr, float eps,
+                          int32_t adagrad, uint32_t spin_limit, uint32_t* err, void* stream) {
+  if (int e = check_view(local_view)) return e;
+  if (local_view->num_shards != 1 || (local_view->dim & 3) != 0 || seg_rows == 0 || seg_rows % ssb::kChunkRows != 0 || world < 1 ||
+      world > SSB_MAX_SHARDS || self < 0 || self >= world || !slots || !rows_bf16 || !ready || !total || !err || tag == 0)
+    return (int)cudaErrorInvalidValue;
+  if (adagrad && !local_view->state[0]) return (int)cudaErrorInvalidValue;
+  if (world == 1) return 0;
+  if (spin_limit == 0) spin_limit = 1u << 26;          // x 100 ns: several seconds
+  const uint32_t max_chunks = seg_rows / ssb::kChunkRows;
+  // one block per SM at most: the waiting blocks of this kernel must never fill the SMs the send kernel needs
+  const int blocks = (int)std::min<uint64_t>((uint64_t)max_chunks * (uint64_t)world, (uint64_t)ssb::kNumSMs);
+  if (adagrad)
+    ssb::push_apply_chunks_kernel<true><<<blocks, 256, 0, (cudaStream_t)stream>>>(*local_view, slots, (const __nv_bfloat16*)rows_bf16, ready, total, seg_rows, max_chunks, world, self, tag, lr, eps, spin_limit, err);
+  else
+    ssb::push_apply_chunks_kernel<false><<<blocks, 256, 0, (cudaStream_t)stream>>>(*local_view, slots, (const __nv_bfloat16*)rows_bf16, ready, total, seg_rows, max_chunks, world, self, tag, lr, eps, spin_limit, err);
   SSB_LAUNCH_CHECK();
   return 0;
 }

@@ -149,6 +149,33 @@ int ssb_push_bf16(const SsbTableView *view, const uint32_t *gslot, const void *g
 int ssb_flags_signal(const SsbInboxView *inbox, int32_t num_shards, int32_t self, uint32_t value, void *stream);
 int ssb_flags_wait(const uint32_t *my_flags, int32_t num_shards, uint32_t value, void *stream);
 
+/* Chunked inbox push: ship and apply overlap. The view describes THIS sender's sub-region of every owner's inbox:
+ * rows[o] (bf16 gradient rows [seg_rows][dim]), slots[o] ([seg_rows]), ready[o] ([max_chunks] words: chunk c of this
+ * sender is complete when it holds this step's tag), total[o] (2 words: {rows shipped, tag}). A chunk is 256 rows.
+ * ssb_push_send_chunks applies the rows this GPU owns directly and ships the others; `cursor` [SSB_MAX_SHARDS],
+ * `done` [SSB_MAX_SHARDS * max_chunks] and `finished` [1] are sender-local device words, zero before the first call
+ * (the kernel leaves them zero). ssb_push_apply_chunks runs on the owner, over ALL senders' sub-regions of its own
+ * inbox (slots / rows / ready / total are the owner's local arrays, sender-major), and applies every chunk as soon as
+ * its flag or the sender's total carries `tag` (bounded wait: on expiry err[0] is set to 1 and the item is skipped).
+ * Launch it on another stream than the send so that the two overlap. `tag` must differ from the tags of the two
+ * previous steps (the step number). ref: global_push_access.h:123-149 + server/init.h:116-132. */
+typedef struct SsbChunkInboxView {
+  void *rows[SSB_MAX_SHARDS];
+  uint32_t *slots[SSB_MAX_SHARDS];
+  uint32_t *ready[SSB_MAX_SHARDS];
+  uint32_t *total[SSB_MAX_SHARDS];
+  uint32_t seg_rows;    /* rows per (owner, sender) sub-region, a multiple of 256 */
+  uint32_t max_chunks;  /* seg_rows / 256 */
+} SsbChunkInboxView;
+int ssb_push_send_chunks(const SsbTableView *view, const SsbChunkInboxView *inbox, const uint32_t *gslot,
+                         const float *grads, int64_t n, const uint32_t *n_dev, int32_t self_shard, float lr, float eps,
+                         int32_t adagrad, uint32_t tag, uint32_t *overflow, uint32_t *cursor, uint32_t *done,
+                         uint32_t *finished, void *stream);
+int ssb_push_apply_chunks(const SsbTableView *local_view, const uint32_t *slots, const void *rows_bf16,
+                          const uint32_t *ready, const uint32_t *total, uint32_t seg_rows, int32_t world, int32_t self,
+                          uint32_t tag, float lr, float eps, int32_t adagrad, uint32_t spin_limit, uint32_t *err,
+                          void *stream);
+
 /* ---- K9: negative sampling (alias method, Philox4x32-10 counter RNG) ---------------------- */
 int ssb_neg_sample(const float *prob, const uint32_t *alias, uint32_t vocab, uint64_t seed,
                    uint64_t offset, uint32_t key_offset, uint32_t *out, int64_t n, void *stream);

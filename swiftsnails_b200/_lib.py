@@ -55,6 +55,17 @@ class SsbInboxView(C.Structure):
     ]
 
 
+class SsbChunkInboxView(C.Structure):
+    _fields_ = [
+        ("rows", C.c_void_p * MAX_SHARDS),
+        ("slots", C.c_void_p * MAX_SHARDS),
+        ("ready", C.c_void_p * MAX_SHARDS),
+        ("total", C.c_void_p * MAX_SHARDS),
+        ("seg_rows", C.c_uint32),
+        ("max_chunks", C.c_uint32),
+    ]
+
+
 _vp, _i64, _i32, _u32, _u64, _f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32, C.c_uint64, C.c_float
 
 # name -> (argtypes, kernel launches per call)
@@ -70,6 +81,8 @@ _KERNEL_SIGS = {
     "ssb_push_adagrad": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _f32, _i32, _vp], 1),
     "ssb_push_send": ([C.POINTER(SsbTableView), C.POINTER(SsbInboxView), _vp, _vp, _i64, _vp, _i32, _f32, _f32, _i32, _i32, _vp, _vp], 1),
     "ssb_push_send2": ([C.POINTER(SsbTableView), C.POINTER(SsbInboxView), _vp, _vp, _i64, _vp, _i32, _f32, _f32, _i32, _i32, _vp, _vp, _vp], 1),
+    "ssb_push_send_chunks": ([C.POINTER(SsbTableView), C.POINTER(SsbChunkInboxView), _vp, _vp, _i64, _vp, _i32, _f32, _f32, _i32, _u32, _vp, _vp, _vp, _vp, _vp], 1),
+    "ssb_push_apply_chunks": ([C.POINTER(SsbTableView), _vp, _vp, _vp, _vp, _u32, _i32, _i32, _u32, _f32, _f32, _i32, _u32, _vp, _vp], 1),
     "ssb_inbox_publish": ([C.POINTER(SsbInboxView), _i32, _i32, _vp, _u32, _vp], 1),
     "ssb_push_bf16_seg": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _i32, _vp, _f32, _f32, _i32, _vp], 1),
     "ssb_push_bf16": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _f32, _i32, _vp], 1),

@@ -333,6 +333,8 @@ class Word2VecTrainer:
         inbox = getattr(self.worker.table, "inbox", None)
         if inbox is not None:
             out["inbox_overflow"] = int(inbox.overflow.item())
+            if hasattr(inbox, "err"):
+                out["inbox_overflow"] += int(inbox.err.item())      # an apply wait ran out: rows were skipped
         return out
 
     def check_health(self):

@@ -180,6 +180,119 @@ class Inbox:
         # no clearing: every sender overwrites its count on its next publish (also with 0 rows)
 
 
+class ChunkInbox:
+    """Chunked owner-side inboxes: shipping and applying overlap (csrc/kernels/table.cu, push_send_chunks_kernel /
+    push_apply_chunks_kernel). Same idea as :class:`Inbox` — every rank owns two inboxes (step parity) in
+    peer-mapped memory, one private sub-region per sender, gradient rows as bf16 on the wire — but a sub-region is
+    cut into 256-row chunks: the send kernel raises a chunk's ready flag on the owner the moment the chunk is
+    complete and publishes the total at its end; the owner's apply kernel runs on a second stream NEXT TO its own
+    send kernel and applies (sender, chunk) items as they land. Flags carry the step number, nothing is cleared.
+    ref: global_push_access.h:123-149, system/server/init.h:116-132 ("send (key, grad)*, the server applies").
+
+    ``segment_ptrs``: base device pointers of every rank's inbox segment, for callers that bring their own
+    (peer-mapped or, in single-process tests that emulate several ranks on one GPU, plain) memory; default: a
+    :class:`PeerMemory` exchange over ``torch.distributed``."""
+
+    CHUNK = 256
+
+    @staticmethod
+    def layout(capacity, dim, world):
+        seg_rows = max(ChunkInbox.CHUNK, (int(capacity) + world - 1) // world)
+        seg_rows = (seg_rows + ChunkInbox.CHUNK - 1) // ChunkInbox.CHUNK * ChunkInbox.CHUNK
+        cap = seg_rows * world
+        max_chunks = seg_rows // ChunkInbox.CHUNK
+        rows_b = cap * dim * 2
+        slots_off = rows_b
+        ready_off = slots_off + cap * 4
+        total_off = ready_off + world * max_chunks * 4
+        per = (total_off + world * 8 + 4095) // 4096 * 4096
+        return {"seg_rows": seg_rows, "capacity": cap, "max_chunks": max_chunks, "slots_off": slots_off,
+                "ready_off": ready_off, "total_off": total_off, "per": per, "total": 2 * per}
+
+    def __init__(self, table: ShardedTable, capacity: int, device, world=None, rank=None, segment_ptrs=None, local_shard=None,
+                 spin_limit=0):
+        import ctypes as C
+
+        from .peer import tensor_from_ptr
+
+        self.table, self.device = table, device
+        if world is None:
+            import torch.distributed as dist
+
+            world, rank = dist.get_world_size(), dist.get_rank()
+        self.world, self.rank = int(world), int(rank)
+        D = table.dim
+        lay = self.layout(capacity, D, self.world)
+        self.lay = lay
+        self.seg_rows, self.capacity, self.max_chunks = lay["seg_rows"], lay["capacity"], lay["max_chunks"]
+        if segment_ptrs is None:
+            self.pm = PeerMemory(lay["total"], device)
+            segment_ptrs = [self.pm.segment_ptr(r) for r in range(self.world)]
+            seg = self.pm.local_tensor()
+            seg.zero_()
+        else:
+            seg = tensor_from_ptr(segment_ptrs[self.rank], lay["total"], device)
+        self.views, self.rows_l, self.slots_l, self.ready_l, self.total_l = [], [], [], [], []
+        for par in range(2):
+            v = _lib.SsbChunkInboxView()
+            for r in range(self.world):
+                b = segment_ptrs[r] + par * lay["per"]
+                v.rows[r] = b + self.rank * self.seg_rows * D * 2
+                v.slots[r] = b + lay["slots_off"] + self.rank * self.seg_rows * 4
+                v.ready[r] = b + lay["ready_off"] + self.rank * self.max_chunks * 4
+                v.total[r] = b + lay["total_off"] + self.rank * 8
+            v.seg_rows, v.max_chunks = self.seg_rows, self.max_chunks
+            self.views.append(v)
+            base = par * lay["per"]
+            self.rows_l.append(seg[base:base + self.capacity * D * 2].view(torch.bfloat16).view(self.capacity, D))
+            self.slots_l.append(seg[base + lay["slots_off"]:base + lay["slots_off"] + self.capacity * 4].view(torch.int32))
+            self.ready_l.append(seg[base + lay["ready_off"]:base + lay["ready_off"] + self.world * self.max_chunks * 4].view(torch.int32))
+            self.total_l.append(seg[base + lay["total_off"]:base + lay["total_off"] + self.world * 8].view(torch.int32))
+        shard = local_shard if local_shard is not None else table.owned[0]
+        self.local = ShardedTable(HashFrag(1, 1), table.capacity, D, [shard.ptrs()], device, seed=table.seed,
+                                  init_scale=table.init_scale, owned=[shard])
+        i32 = dict(dtype=torch.int32, device=device)
+        self.overflow = torch.zeros(1, **i32)
+        self.err = torch.zeros(1, **i32)             # an apply wait ran out (a sender never delivered)
+        self.cursor = torch.zeros(16, **i32)
+        self.done = torch.zeros(16 * self.max_chunks, **i32)
+        self.finished = torch.zeros(1, **i32)
+        self.apply_stream = torch.cuda.Stream(device=device)
+        self.spin_limit = int(spin_limit)
+        self.parity = 0
+        self.step = 0
+        self._C = C
+        torch.cuda.synchronize(device)
+
+    def send(self, gslot, grads, lr, eps=1e-8, adagrad=True, n_dev=None, n=None):
+        """Apply my own rows, ship the others (current stream). Returns (parity, tag) for :meth:`apply`."""
+        n = gslot.numel() if n is None else n
+        par = self.parity
+        self.parity ^= 1
+        self.step += 1
+        _lib.call("ssb_push_send_chunks", self.table._view_ref(), self._C.byref(self.views[par]), gslot.data_ptr(),
+                  grads.data_ptr(), n, _lib.ptr(n_dev), self.rank, float(lr), float(eps), 1 if adagrad else 0, self.step,
+                  self.overflow.data_ptr(), self.cursor.data_ptr(), self.done.data_ptr(), self.finished.data_ptr(),
+                  _lib.stream_ptr())
+        return par, self.step
+
+    def apply(self, par, tag, lr, eps=1e-8, adagrad=True):
+        """Apply every sender's chunks of my inbox as they land (current stream)."""
+        _lib.call("ssb_push_apply_chunks", self.local._view_ref(), self.slots_l[par].data_ptr(), self.rows_l[par].data_ptr(),
+                  self.ready_l[par].data_ptr(), self.total_l[par].data_ptr(), self.seg_rows, self.world, self.rank, int(tag),
+                  float(lr), float(eps), 1 if adagrad else 0, self.spin_limit, self.err.data_ptr(), _lib.stream_ptr())
+
+    def push(self, gslot, grads, lr, eps=1e-8, adagrad=True, n_dev=None, n=None):
+        cur = torch.cuda.current_stream()
+        start = torch.cuda.Event()
+        start.record(cur)
+        par, tag = self.send(gslot, grads, lr, eps, adagrad, n_dev, n)
+        self.apply_stream.wait_event(start)           # same dependencies as the send, not the send itself: they overlap
+        with torch.cuda.stream(self.apply_stream):
+            self.apply(par, tag, lr, eps, adagrad)
+        cur.wait_stream(self.apply_stream)            # the next push (and the caller) come after both
+
+
 def attach_inbox(table: ShardedTable, capacity: int, bf16_rows: bool = False, barrier: str = "flags"):
     """Give a peer-mapped table owner-side inboxes (no-op for a single process)."""
     import torch.distributed as dist
@@ -187,5 +300,9 @@ def attach_inbox(table: ShardedTable, capacity: int, bf16_rows: bool = False, ba
     if not dist.is_initialized() or dist.get_world_size() == 1:
         table.inbox = None
         return None
-    table.inbox = Inbox(table, capacity, table.device, bf16_rows=bf16_rows, barrier=barrier)
+    if barrier == "chunks":
+        table.inbox = ChunkInbox(table, capacity, table.device)
+        dist.barrier()
+    else:
+        table.inbox = Inbox(table, capacity, table.device, bf16_rows=bf16_rows, barrier=barrier)
     return table.inbox
