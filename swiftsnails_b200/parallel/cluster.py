@@ -189,6 +189,12 @@ class ChunkInbox:
     send kernel and applies (sender, chunk) items as they land. Flags carry the step number, nothing is cleared.
     ref: global_push_access.h:123-149, system/server/init.h:116-132 ("send (key, grad)*, the server applies").
 
+    Status: opt-in (``attach_inbox(..., barrier="chunks")``, ``bench.py --inbox-barrier chunks``). Correct on 2 GPUs
+    (no lost rows, same loss) but measured SLOWER than the flag hand-off there, 0.83 vs 0.59 ms/step: the apply
+    kernel is held to one block per SM so that its waiting blocks can never crowd the send kernel (and the rest
+    of the pipelined step) off the SMs, and one block per SM does not keep enough row updates in flight; a
+    variant with more blocks / a leaner chunk walk ran into its wait bound on 2 GPUs and was dropped.
+
     ``segment_ptrs``: base device pointers of every rank's inbox segment, for callers that bring their own
     (peer-mapped or, in single-process tests that emulate several ranks on one GPU, plain) memory; default: a
     :class:`PeerMemory` exchange over ``torch.distributed``."""
