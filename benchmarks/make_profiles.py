@@ -151,7 +151,7 @@ def main():
         name = re.sub(r"[<>, ]+", "_", name).strip("_")
         with open(os.path.join(sass_dir, name + ".sass"), "w") as f:
             f.write("\t\tFunction : %s\n" % k + "\n".join(lines) + "\n")
-        if "sgns_block_tc" in k:
+        if "tc20sgns_block_tc_kernelILb0E" in k:      # the production instantiation of the pipelined kernel
             with open(os.path.join(OUT, "sgns_block_tc_kernel.sass"), "w") as f:
                 f.write("\n".join(lines) + "\n")
     print("profiles written to", OUT)
