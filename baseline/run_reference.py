@@ -58,6 +58,27 @@ def ensure_built():
     return None
 
 
+ORACLE = os.path.join(REF, "bin", "ref_oracle")
+
+
+def ensure_oracle_built():
+    """Compile baseline/ref_apps/ref_oracle.cpp (the reference's own hashfrag / sparse table as a test oracle)
+    against the unmodified reference copy. Returns None or an error string."""
+    err = ensure_built()
+    if err:
+        return err
+    app = os.path.join(HERE, "ref_apps", "ref_oracle.cpp")
+    if os.path.exists(ORACLE) and os.path.getmtime(ORACLE) >= os.path.getmtime(app):
+        return None
+    lz = _libzmq()
+    cmd = ["g++", "-std=c++11", "-O1", "-pthread", "-w", "-I", os.path.join(HERE, "shim"), "-I", os.path.join(REF, "src"), app, "-o", ORACLE,
+           "-L" + os.path.dirname(lz), "-l:" + os.path.basename(lz), "-Wl,-rpath," + os.path.dirname(lz)]
+    p = subprocess.run(cmd, capture_output=True, text=True)
+    if p.returncode != 0:
+        return "oracle build failed: " + p.stderr.strip()[-400:]
+    return None
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))

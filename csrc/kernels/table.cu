@@ -40,12 +40,19 @@ __device__ __forceinline__ Probe probe_insert(const SsbTableView& v, uint32_t ke
   uint32_t* kbase = v.keys[p.owner];
   const uint32_t nb = v.capacity / SSB_BUCKET;
   uint32_t b = reduce_range(slot_hash(key), nb);
+  uint32_t lock_spins = 0;
   for (uint32_t probes = 0; probes < nb;) {
     uint32_t kv = ld_acquire_sys(kbase + (size_t)b * SSB_BUCKET + lane);
     unsigned m = __ballot_sync(0xffffffffu, kv == key);
     if (m) { p.slot = b * SSB_BUCKET + (__ffs(m) - 1); return p; }
     unsigned locked = __ballot_sync(0xffffffffu, kv == SSB_LOCKED_KEY);
-    if (locked) { __nanosleep(100); continue; }
+    if (locked) {
+      // the holder is a resident warp that is writing the row's initial value and never waits, so this resolves in
+      // microseconds; bounded all the same (~0.5 s): a slot that stays LOCKED is reported like a full table
+      if (++lock_spins > (1u << 22)) return p;
+      __nanosleep(100);
+      continue;
+    }
     unsigned empties = __ballot_sync(0xffffffffu, kv == SSB_EMPTY_KEY);
     if (empties) {
       if (!insert) return p;
@@ -79,11 +86,23 @@ __device__ __forceinline__ uint2 ld_shadow_u2(const void* p) {
   asm volatile("ld.relaxed.sys.global.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p) : "memory");
   return r;
 }
-// w += d on an owner-side row, keeping the bf16 mirror in step when there is one
+// w += d on an owner-side row, keeping the bf16 mirror in step when there is one.
+// kConcurrent: other warps may update the same row in the same launch (the segments of an inbox apply run side by
+// side and hot words arrive from every sender). Two such writers could leave the mirror at the value of whichever
+// STORE landed last rather than at the final row; so after writing the mirror the row is read back (an L2 hit) and,
+// if another update has gone in meanwhile, the mirror is written again from the fresh row. What remains is a
+// window of one in-flight store; a row that loses it is corrected the next time it is touched (hot rows: next step).
+template <bool kConcurrent = false>
 __device__ __forceinline__ void row_update_f4(float* row, __nv_bfloat16* shadow, float4 d) {
   if (shadow) {
     float4 o = atom_add_f4_sys(row, d);
-    *reinterpret_cast<uint2*>(shadow) = pack_bf16x4(make_float4(o.x + d.x, o.y + d.y, o.z + d.z, o.w + d.w));
+    const float4 mine = make_float4(o.x + d.x, o.y + d.y, o.z + d.z, o.w + d.w);
+    *reinterpret_cast<uint2*>(shadow) = pack_bf16x4(mine);
+    if (kConcurrent) {
+      const float4 now = ld_row_f4(row);
+      if (now.x != mine.x || now.y != mine.y || now.z != mine.z || now.w != mine.w)
+        *reinterpret_cast<uint2*>(shadow) = pack_bf16x4(now);
+    }
   } else {
     red_add_f4_sys(row, d);
   }
@@ -163,7 +182,7 @@ __device__ __forceinline__ void pull_emit(const SsbTableView& v, uint32_t key, b
         val = want ? ld_row_f1(row + j) : 0.f;
       } else if (valid) {
         val = init_value(key, j, v.seed, v.init_scale);
-        if (p.is_new) row[j] = val;
+        if (p.is_new) { row[j] = val; if (shadow) shadow[j] = __float2bfloat16_rn(val); }
       } else {
         val = 0.f;
       }
@@ -581,7 +600,7 @@ push_bf16_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restr
       } else {
         d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
       }
-      row_update_f4(row + j, sh ? sh + j : nullptr, d);
+      row_update_f4<true>(row + j, sh ? sh + j : nullptr, d);
     }
   }
 }
@@ -610,12 +629,19 @@ __global__ void inbox_publish_kernel(const __grid_constant__ SsbInboxView ib, in
   __syncthreads();
   if (value != 0 && o < num_shards) st_release_sys(ib.flags[o] + self, value);
 }
-__global__ void flags_wait_kernel(const uint32_t* __restrict__ my_flags, int num_shards, uint32_t value) {
+// spin_limit iterations of ~0.2 us each. err == nullptr: a wait that runs out traps (the launch fails); otherwise
+// err[0] is set to 1 and the kernel returns, so that a straggling rank (a host stall, a backup being written) costs
+// the others an error the host can read and act on instead of a sticky CUDA context error.
+__global__ void flags_wait_kernel(const uint32_t* __restrict__ my_flags, int num_shards, uint32_t value, uint32_t spin_limit,
+                                  uint32_t* __restrict__ err) {
   if ((int)threadIdx.x < num_shards) {
     uint32_t it = 0;
     while ((int32_t)(ld_acquire_sys(my_flags + threadIdx.x) - value) < 0) {
       __nanosleep(200);
-      if (++it > (1u << 24)) __trap();
+      if (++it > spin_limit) {
+        if (err) { atomicExch(err, 1u); break; }
+        __trap();
+      }
     }
   }
   __syncthreads();
@@ -893,7 +919,7 @@ push_apply_chunks_kernel(const __grid_constant__ SsbTableView v, const uint32_t*
         } else {
           d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
         }
-        row_update_f4(row + j, sh ? sh + j : nullptr, d);
+        row_update_f4<true>(row + j, sh ? sh + j : nullptr, d);
       }
     }
     __syncthreads();
@@ -1191,11 +1217,20 @@ int ssb_flags_signal(const SsbInboxView* inbox, int32_t num_shards, int32_t self
   return 0;
 }
 
-int ssb_flags_wait(const uint32_t* my_flags, int32_t num_shards, uint32_t value, void* stream) {
+int ssb_flags_wait2(const uint32_t* my_flags, int32_t num_shards, uint32_t value, uint32_t spin_limit, uint32_t* err, void* stream) {
   if (num_shards < 1 || num_shards > SSB_MAX_SHARDS) return (int)cudaErrorInvalidValue;
-  ssb::flags_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(my_flags, num_shards, value);
+  if (spin_limit == 0) {
+    // default ~27 s (2^27 x 0.2 us); SSB200_WAIT_LIMIT overrides (iterations)
+    static const uint32_t env_limit = [] { const char* e = getenv("SSB200_WAIT_LIMIT"); return e ? (uint32_t)strtoul(e, nullptr, 10) : 0u; }();
+    spin_limit = env_limit ? env_limit : (1u << 27);
+  }
+  ssb::flags_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(my_flags, num_shards, value, spin_limit, err);
   SSB_LAUNCH_CHECK();
   return 0;
+}
+
+int ssb_flags_wait(const uint32_t* my_flags, int32_t num_shards, uint32_t value, void* stream) {
+  return ssb_flags_wait2(my_flags, num_shards, value, 0, nullptr, stream);
 }
 
 int ssb_table_load(const SsbTableView* view, const uint32_t* keys, const float* rows, const float* state,

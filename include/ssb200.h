@@ -148,6 +148,10 @@ int ssb_push_bf16(const SsbTableView *view, const uint32_t *gslot, const void *g
  * owner (after a system fence); wait = spin (bounded) until all of my flags reached `value`. */
 int ssb_flags_signal(const SsbInboxView *inbox, int32_t num_shards, int32_t self, uint32_t value, void *stream);
 int ssb_flags_wait(const uint32_t *my_flags, int32_t num_shards, uint32_t value, void *stream);
+/* Same with an explicit bound (iterations of ~0.2 us; 0 = default ~27 s, or SSB200_WAIT_LIMIT) and an error word: when
+ * the wait runs out err[0] is set to 1 and the kernel returns (err == NULL: it traps, as ssb_flags_wait does). */
+int ssb_flags_wait2(const uint32_t *my_flags, int32_t num_shards, uint32_t value, uint32_t spin_limit, uint32_t *err,
+                    void *stream);
 
 /* Chunked inbox push: ship and apply overlap. The view describes THIS sender's sub-region of every owner's inbox:
  * rows[o] (bf16 gradient rows [seg_rows][dim]), slots[o] ([seg_rows]), ready[o] ([max_chunks] words: chunk c of this

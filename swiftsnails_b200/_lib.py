@@ -88,6 +88,7 @@ _KERNEL_SIGS = {
     "ssb_push_bf16": ([C.POINTER(SsbTableView), _vp, _vp, _i64, _vp, _f32, _f32, _i32, _vp], 1),
     "ssb_flags_signal": ([C.POINTER(SsbInboxView), _i32, _i32, _u32, _vp], 1),
     "ssb_flags_wait": ([_vp, _i32, _u32, _vp], 1),
+    "ssb_flags_wait2": ([_vp, _i32, _u32, _u32, _vp, _vp], 1),
     "ssb_dump_compact_range": ([_vp, _vp, _vp, _u32, _i32, _u32, _u32, _vp, _vp, _vp, _vp, _u32, _vp], 1),
     "ssb_red_probe": ([_vp, _u32, _i32, _i32, _i32, _vp], 1),
     "ssb_neg_sample": ([_vp, _vp, _u32, _u64, _u64, _u32, _vp, _i64, _vp], 1),

@@ -26,7 +26,29 @@ OBJ_DIR = os.path.join(ROOT, "build", "obj")
 BIN_DIR = os.path.join(ROOT, "swiftsnails_b200", "bin")
 
 NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-CXX = os.environ.get("CXX") or shutil.which("g++") or "g++"
+
+
+def _pick_cxx():
+    """The host compiler for the C++ core. The shared library is loaded into Python processes that already hold the
+    system libstdc++ (numpy, torch), so it must link libstdc++ DYNAMICALLY: a compiler that can only find libstdc++.a
+    would put a second, exported copy of the runtime inside libssb200_core.so, and iostream calls then mix the two
+    (std::ofstream in ssb_cpu_table_dump crashed that way). Such a compiler is passed over."""
+    cands = [os.environ.get("CXX"), shutil.which("g++"), "/usr/bin/g++"]
+    seen = []
+    for c in cands:
+        if not c or c in seen:
+            continue
+        seen.append(c)
+        try:
+            so = subprocess.run([c, "-print-file-name=libstdc++.so"], capture_output=True, text=True).stdout.strip()
+        except OSError:
+            continue
+        if os.path.isabs(so) and os.path.exists(so):
+            return c
+    return seen[0] if seen else "g++"
+
+
+CXX = _pick_cxx()
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -137,6 +137,7 @@ class Inbox:
         self.local = ShardedTable(HashFrag(1, 1), table.capacity, D, [shard.ptrs()], device, seed=table.seed,
                                   init_scale=table.init_scale, owned=[shard])
         self.overflow = torch.zeros(1, dtype=torch.int32, device=device)
+        self.err = torch.zeros(1, dtype=torch.int32, device=device)         # a hand-off wait ran out (a sender never showed up)
         self.cursor = torch.zeros(16, dtype=torch.int32, device=device)     # rows claimed per owner this step
         self.token = torch.zeros(1, dtype=torch.int32, device=device)
         self.parity = 0
@@ -160,7 +161,7 @@ class Inbox:
                   self.overflow.data_ptr(), self.cursor.data_ptr(), sp)
         if self.barrier == "flags":
             _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), self.step, sp)
-            _lib.call("ssb_flags_wait", self.flags_l.data_ptr(), self.world, self.step, sp)
+            _lib.call("ssb_flags_wait2", self.flags_l.data_ptr(), self.world, self.step, 0, self.err.data_ptr(), sp)
         else:
             _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), 0, sp)
             dist.all_reduce(self.token)      # every rank's shipment has landed in my inbox

@@ -473,6 +473,34 @@ def test_bf16_row_mirror_stays_in_step(device):
     assert torch.equal(bf, fp32.to(torch.bfloat16))
 
 
+@pytest.mark.parametrize("adagrad", [0, 1])
+def test_bf16_mirror_under_concurrent_inbox_segments(device, adagrad):
+    """Hot words reach an owner from every sender in one inbox apply: 7 segments, run side by side by one
+    ssb_push_bf16_seg launch, all update the SAME 64 rows. After every launch the mirror must equal bf16(row) exactly
+    (the apply re-reads the row after writing the mirror and rewrites it if another segment got in between)."""
+    from swiftsnails_b200 import _lib
+    from swiftsnails_b200.ops._util import u32_tensor
+    from swiftsnails_b200.ops.table import ShardedTable
+
+    dim, segs, hot, seg_rows = 128, 7, 64, 64
+    t = ShardedTable.local(4096, dim, device, num_shards=1, with_state=True, with_shadow=True)
+    keys = np.unique(_keys(400, seed=77))[:hot]
+    kd = u32_tensor(keys, device)
+    _, gslot = t.pull(kd)
+    slots = (gslot % t.capacity).to(torch.int32)
+    all_slots = slots.repeat(segs).contiguous()                      # segment y = the same 64 slots
+    counts = torch.full((segs,), seg_rows, dtype=torch.int32, device=device)
+    torch.manual_seed(5)
+    for it in range(60):
+        g = (torch.randn(segs * seg_rows, dim, device=device) * 0.3).to(torch.bfloat16)
+        _lib.call("ssb_push_bf16_seg", t._view_ref(), all_slots.data_ptr(), g.data_ptr(), seg_rows, segs, counts.data_ptr(),
+                  0.05, 1e-8, adagrad, _lib.stream_ptr())
+        fp32, _ = t.pull(kd, insert=False)
+        bf = torch.empty(hot, dim, dtype=torch.bfloat16, device=device)
+        t.pull(kd, rows_bf16=bf, want_fp32=False, insert=False)
+        assert torch.equal(bf, fp32.to(torch.bfloat16)), "mirror out of step after launch %d" % it
+
+
 def test_pull_bulk_copy_variant_passes_the_pull_tests(device):
     """SSB200_PULL_BULK=1 routes pulls through pull_bulk_kernel (cp.async.bulk rows into shared memory,
     lane-per-key resolve). The switch is read once per process, so the pull / slot-cache / push tests are
