@@ -86,8 +86,10 @@ int64_t ssb_dump_write_text(const char* path, const uint32_t* keys, const float*
 // accumulator), which is what the reference's dump prints when the table's Param carries one (the whole Param goes
 // through operator<<, parameter/sparsetable.h:49-56). state == nullptr writes plain rows. digits: significant digits per
 // number (6 = the reference's default ostream precision; 9 round-trips a float exactly).
-int64_t ssb_dump_write_text2(const char* path, const uint32_t* keys, const float* rows, const float* state, int64_t n, int dim,
-                             int append, int digits) {
+// state_dim: floats of optimizer state per entry (state words x dim; AdaGrad = dim, FTRL = 2 x dim)
+int64_t ssb_dump_write_text3(const char* path, const uint32_t* keys, const float* rows, const float* state, int64_t n, int dim,
+                             int state_dim, int append, int digits) {
+  if (state_dim <= 0) state_dim = dim;
   FILE* f = std::fopen(path, append ? "a" : "w");
   if (!f) return -1;
   std::vector<char> buf(1 << 20);
@@ -104,23 +106,29 @@ int64_t ssb_dump_write_text2(const char* path, const uint32_t* keys, const float
     for (int j = 0; j < dim; ++j) std::fprintf(f, "%.*g ", digits, r[j]);
     if (state) {
       std::fputs("\tAcc:\t", f);
-      const float* a = state + i * dim;
-      for (int j = 0; j < dim; ++j) std::fprintf(f, "%.*g ", digits, a[j]);
+      const float* a = state + i * state_dim;
+      for (int j = 0; j < state_dim; ++j) std::fprintf(f, "%.*g ", digits, a[j]);
     }
     std::fputc('\n', f);
   }
   std::fclose(f);
   return n;
 }
+int64_t ssb_dump_write_text2(const char* path, const uint32_t* keys, const float* rows, const float* state, int64_t n, int dim,
+                             int append, int digits) {
+  return ssb_dump_write_text3(path, keys, rows, state, n, dim, dim, append, digits);
+}
 // Reads either line form. state may be nullptr (an "Acc:" part is then skipped); rows / state shorter than dim are
 // zero-padded. *has_state (optional) is set to 1 if any line carried an "Acc:" part. Returns the rows read (<= max_n).
-int64_t ssb_dump_read_text2(const char* path, uint32_t* keys, float* rows, float* state, int64_t max_n, int dim, int* has_state) {
+int64_t ssb_dump_read_text3(const char* path, uint32_t* keys, float* rows, float* state, int64_t max_n, int dim, int state_dim,
+                            int* has_state) {
+  if (state_dim <= 0) state_dim = dim;
   FILE* f = std::fopen(path, "r");
   if (!f) return -1;
   LineFileReader reader;
   int64_t n = 0;
   if (has_state) *has_state = 0;
-  auto parse_vec = [dim](char* p, float* out) -> char* {
+  auto parse_vec = [](char* p, float* out, int dim) -> char* {
     for (int j = 0; j < dim; ++j) {
       char* end = nullptr;
       const float v = std::strtof(p, &end);
@@ -138,19 +146,22 @@ int64_t ssb_dump_read_text2(const char* path, uint32_t* keys, float* rows, float
     keys[n] = (uint32_t)std::strtoul(line, nullptr, 10);
     char* p = tab + 1;
     if (std::strncmp(p, "Vec:", 4) == 0) p += 4;
-    p = parse_vec(p, rows + n * dim);
-    float* st = state ? state + n * dim : nullptr;
+    p = parse_vec(p, rows + n * dim, dim);
+    float* st = state ? state + n * state_dim : nullptr;
     char* acc = std::strstr(p, "Acc:");
     if (acc) {
       if (has_state) *has_state = 1;
-      parse_vec(acc + 4, st);
+      parse_vec(acc + 4, st, state_dim);
     } else if (st) {
-      for (int j = 0; j < dim; ++j) st[j] = 0.f;
+      for (int j = 0; j < state_dim; ++j) st[j] = 0.f;
     }
     ++n;
   }
   std::fclose(f);
   return n;
+}
+int64_t ssb_dump_read_text2(const char* path, uint32_t* keys, float* rows, float* state, int64_t max_n, int dim, int* has_state) {
+  return ssb_dump_read_text3(path, keys, rows, state, max_n, dim, dim, has_state);
 }
 // returns the number of rows read (<= max_n); rows shorter than dim are zero-padded
 int64_t ssb_dump_read_text(const char* path, uint32_t* keys, float* rows, int64_t max_n, int dim) {

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/ssb200.h"
+#include "../../include/ssb200_rule.cuh"
 
 #define SSB_LAUNCH_CHECK()                                 \
   do {                                                     \
@@ -60,6 +61,16 @@ __host__ __device__ __forceinline__ float init_value(uint32_t key, uint32_t j, u
   return (u - 0.5f) * scale;
 }
 
+// Lazy init of element j of key's row under the table's init kind (SSB_INIT_*).
+__device__ __forceinline__ float init_of(const SsbTableView& v, uint32_t key, uint32_t j) {
+  switch (v.init_kind) {
+    case SSB_INIT_ZERO: return 0.f;
+    case SSB_INIT_CONSTANT: return v.init_scale;
+    case SSB_INIT_UNIFORM_POS: return (init_value(key, j, v.seed, 1.0f) + 0.5f) * v.init_scale;
+    default: return init_value(key, j, v.seed, v.init_scale);
+  }
+}
+
 // ---- memory-model helpers (system scope: the other side may be a peer GPU over NVLink) ----
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
@@ -82,43 +93,7 @@ __device__ __forceinline__ uint32_t cas_sys(uint32_t* p, uint32_t cmp, uint32_t 
                : "memory");
   return old;
 }
-// Streaming 16-byte load that bypasses L1 allocation (rows are read once per pull and may be
-// mutated by other GPUs between kernels).
-__device__ __forceinline__ float4 ld_row_f4(const float* p) {
-  float4 r;
-  asm volatile("ld.relaxed.sys.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
-               : "l"(p)
-               : "memory");
-  return r;
-}
-__device__ __forceinline__ float ld_row_f1(const float* p) {
-  float r;
-  asm volatile("ld.relaxed.sys.global.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");
-  return r;
-}
-// Vector reduction into (possibly remote) memory: REDG.E.ADD.F32x4 .SYS
-__device__ __forceinline__ void red_add_f4_sys(float* p, float4 v) {
-  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x),
-               "f"(v.y), "f"(v.z), "f"(v.w)
-               : "memory");
-}
-__device__ __forceinline__ void red_add_f1_sys(float* p, float v) {
-  asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
-}
-__device__ __forceinline__ float4 atom_add_f4_sys(float* p, float4 v) {
-  float4 r;
-  asm volatile("atom.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4], {%5,%6,%7,%8};"
-               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
-               : "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
-               : "memory");
-  return r;
-}
-__device__ __forceinline__ float atom_add_f1_sys(float* p, float v) {
-  float r;
-  asm volatile("atom.relaxed.sys.global.add.f32 %0, [%1], %2;" : "=f"(r) : "l"(p), "f"(v) : "memory");
-  return r;
-}
+// ld_row_f4/f1, red_add_f4/f1_sys, atom_add_f4/f1_sys: include/ssb200_rule.cuh (public: user update rules use them)
 // Local (gpu-scope) vector reduction — gradient accumulation into the worker's own buffer.
 __device__ __forceinline__ void red_add_f4_gpu(float* p, float4 v) {
   asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x),

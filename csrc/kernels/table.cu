@@ -86,28 +86,6 @@ __device__ __forceinline__ uint2 ld_shadow_u2(const void* p) {
   asm volatile("ld.relaxed.sys.global.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p) : "memory");
   return r;
 }
-// w += d on an owner-side row, keeping the bf16 mirror in step when there is one.
-// kConcurrent: other warps may update the same row in the same launch (the segments of an inbox apply run side by
-// side and hot words arrive from every sender). Two such writers could leave the mirror at the value of whichever
-// STORE landed last rather than at the final row; so after writing the mirror the row is read back (an L2 hit) and,
-// if another update has gone in meanwhile, the mirror is written again from the fresh row. What remains is a
-// window of one in-flight store; a row that loses it is corrected the next time it is touched (hot rows: next step).
-template <bool kConcurrent = false>
-__device__ __forceinline__ void row_update_f4(float* row, __nv_bfloat16* shadow, float4 d) {
-  if (shadow) {
-    float4 o = atom_add_f4_sys(row, d);
-    const float4 mine = make_float4(o.x + d.x, o.y + d.y, o.z + d.z, o.w + d.w);
-    *reinterpret_cast<uint2*>(shadow) = pack_bf16x4(mine);
-    if (kConcurrent) {
-      const float4 now = ld_row_f4(row);
-      if (now.x != mine.x || now.y != mine.y || now.z != mine.z || now.w != mine.w)
-        *reinterpret_cast<uint2*>(shadow) = pack_bf16x4(now);
-    }
-  } else {
-    red_add_f4_sys(row, d);
-  }
-}
-
 __device__ __forceinline__ uint32_t effective_n(int64_t n, const uint32_t* n_dev) {
   uint32_t ne = (uint32_t)n;
   if (n_dev) { uint32_t d = *n_dev; if (d < ne) ne = d; }
@@ -160,10 +138,10 @@ __device__ __forceinline__ void pull_emit(const SsbTableView& v, uint32_t key, b
       if (have && !p.is_new) {
         val = (have_pre && j < 128) ? preloaded : (want ? ld_row_f4(row + j) : make_float4(0, 0, 0, 0));
       } else if (valid) {
-        val.x = init_value(key, j, v.seed, v.init_scale);
-        val.y = init_value(key, j + 1, v.seed, v.init_scale);
-        val.z = init_value(key, j + 2, v.seed, v.init_scale);
-        val.w = init_value(key, j + 3, v.seed, v.init_scale);
+        val.x = init_of(v, key, j);
+        val.y = init_of(v, key, j + 1);
+        val.z = init_of(v, key, j + 2);
+        val.w = init_of(v, key, j + 3);
         if (p.is_new) {
           *reinterpret_cast<float4*>(row + j) = val;
           if (shadow) *reinterpret_cast<uint2*>(shadow + j) = pack_bf16x4(val);
@@ -181,7 +159,7 @@ __device__ __forceinline__ void pull_emit(const SsbTableView& v, uint32_t key, b
       if (have && !p.is_new) {
         val = want ? ld_row_f1(row + j) : 0.f;
       } else if (valid) {
-        val = init_value(key, j, v.seed, v.init_scale);
+        val = init_of(v, key, j);
         if (p.is_new) { row[j] = val; if (shadow) shadow[j] = __float2bfloat16_rn(val); }
       } else {
         val = 0.f;
@@ -505,105 +483,14 @@ gather_slots_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __re
 }
 
 // ---- push ---------------------------------------------------------------------------------
-// 32 registers = 8 blocks per SM: the AdaGrad path waits on the accumulator's `atom` for every chunk, so
-// resident warps are what hides that latency (at 40 registers / 6 blocks the same kernel ran 20 % slower).
-// kShadow: the shard keeps a bf16 mirror of its rows (read by remote pulls) that the update must refresh.
-template <bool kAdaGrad, bool kShadow>
-__global__ void __launch_bounds__(256, 8)
-push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot, float* grads,
-            int64_t n, const uint32_t* __restrict__ n_dev, float lr, float eps, int zero_grads) {
-  const int lane = threadIdx.x & 31;
-  const uint32_t ne = effective_n(n, n_dev);
-  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
-  const int D = v.dim;
-  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
-    uint32_t g = __ldg(gslot + w);
-    if (g == SSB_INVALID_SLOT) continue;
-    uint32_t o = g / v.capacity, s = g - o * v.capacity;
-    float* row = v.rows[o] + (size_t)s * D;
-    float* st = kAdaGrad ? v.state[o] + (size_t)s * D : nullptr;
-    __nv_bfloat16* sh = (kShadow && v.shadow[o]) ? reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)s * D : nullptr;
-    float* gr = grads + (size_t)w * D;
-    if ((D & 3) == 0) {
-      for (int j = lane * 4; j < D; j += 128) {
-        float4 gv = *reinterpret_cast<const float4*>(gr + j);
-        if (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
-        float4 d;
-        if (kAdaGrad) {
-          float4 g2 = make_float4(gv.x * gv.x, gv.y * gv.y, gv.z * gv.z, gv.w * gv.w);
-          float4 a = atom_add_f4_sys(st + j, g2);
-          d.x = -lr * gv.x * rsqrtf(a.x + g2.x + eps);
-          d.y = -lr * gv.y * rsqrtf(a.y + g2.y + eps);
-          d.z = -lr * gv.z * rsqrtf(a.z + g2.z + eps);
-          d.w = -lr * gv.w * rsqrtf(a.w + g2.w + eps);
-        } else {
-          d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
-        }
-        row_update_f4(row + j, (kShadow && sh) ? sh + j : nullptr, d);
-        if (zero_grads) *reinterpret_cast<float4*>(gr + j) = make_float4(0, 0, 0, 0);
-      }
-    } else {
-      for (int j = lane; j < D; j += 32) {
-        float gv = gr[j];
-        if (gv == 0.f) continue;
-        float d;
-        if (kAdaGrad) {
-          float g2 = gv * gv;
-          float a = atom_add_f1_sys(st + j, g2);
-          d = -lr * gv * rsqrtf(a + g2 + eps);
-        } else {
-          d = -lr * gv;
-        }
-        if (kShadow && sh) { float o1 = atom_add_f1_sys(row + j, d); sh[j] = __float2bfloat16_rn(o1 + d); }
-        else red_add_f1_sys(row + j, d);
-        if (zero_grads) gr[j] = 0.f;
-      }
-    }
-  }
-}
-
-// Owner-side apply of an inbox whose gradient rows travelled as bf16 (half the NVLink bytes); the
-// update itself is fp32 on fp32 rows / accumulators. D must be a multiple of 4.
-template <bool kAdaGrad>
-__global__ void __launch_bounds__(256)
-push_bf16_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot,
-                 const __nv_bfloat16* __restrict__ grads, int64_t n, const uint32_t* __restrict__ n_dev, float lr, float eps,
-                 int64_t seg_stride) {
-  // blockIdx.y = inbox segment (one per sender): segment y holds rows [y * seg_stride, y * seg_stride + n_dev[y])
-  if (n_dev) n_dev += blockIdx.y;
-  gslot += (size_t)blockIdx.y * seg_stride;
-  grads += (size_t)blockIdx.y * seg_stride * v.dim;
-  const int lane = threadIdx.x & 31;
-  const uint32_t ne = effective_n(n, n_dev);
-  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
-  const int D = v.dim;
-  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
-    uint32_t g = __ldg(gslot + w);
-    if (g == SSB_INVALID_SLOT) continue;
-    uint32_t o = g / v.capacity, s = g - o * v.capacity;
-    float* row = v.rows[o] + (size_t)s * D;
-    float* st = kAdaGrad ? v.state[o] + (size_t)s * D : nullptr;
-    const __nv_bfloat16* gr = grads + (size_t)w * D;
-    __nv_bfloat16* sh = v.shadow[o] ? reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)s * D : nullptr;
-    for (int j = lane * 4; j < D; j += 128) {
-      const uint2 pk = *reinterpret_cast<const uint2*>(gr + j);
-      const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162*>(&pk.x), hi = *reinterpret_cast<const __nv_bfloat162*>(&pk.y);
-      const float2 a01 = __bfloat1622float2(lo), a23 = __bfloat1622float2(hi);
-      const float4 gv = make_float4(a01.x, a01.y, a23.x, a23.y);
-      if (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
-      float4 d;
-      if (kAdaGrad) {
-        float4 g2 = make_float4(gv.x * gv.x, gv.y * gv.y, gv.z * gv.z, gv.w * gv.w);
-        float4 a = atom_add_f4_sys(st + j, g2);
-        d.x = -lr * gv.x * rsqrtf(a.x + g2.x + eps); d.y = -lr * gv.y * rsqrtf(a.y + g2.y + eps);
-        d.z = -lr * gv.z * rsqrtf(a.z + g2.z + eps); d.w = -lr * gv.w * rsqrtf(a.w + g2.w + eps);
-      } else {
-        d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
-      }
-      row_update_f4<true>(row + j, sh ? sh + j : nullptr, d);
-    }
-  }
-}
+// The push kernels proper — rule_push_kernel<Rule, kShadow> (a worker's fp32 gradient rows into the owners' rows),
+// rule_push_bf16_kernel<Rule> (owner-side apply of bf16 inbox segments) and rule_mirror_refresh_kernel — live in
+// the public header include/ssb200_rule.cuh together with the update rules (Sgd, AdaGrad, Ftrl), so that a user's
+// rule is instantiated into the same kernels without editing this file. Below: the kernels that SHIP gradient rows
+// to their owners; their "rows I own myself" branch applies the rule through the header's rule_apply_row.
+struct ShipOnly {};                 // Rule argument of the send kernels: ship remote rows, leave the local rows alone
+template <class Rule> struct applies_rule { static constexpr bool value = true; };
+template <> struct applies_rule<ShipOnly> { static constexpr bool value = false; };
 
 // Cross-GPU hand-off flags for the inbox push (replaces a collective as the barrier): after its
 // shipment kernel a rank stores the step number into flags[owner][rank] on every owner; an owner
@@ -658,12 +545,12 @@ __global__ void flags_wait_kernel(const uint32_t* __restrict__ my_flags, int num
 // the owner applies" (global_push_access.h:123-149, server/init.h:116-132) — this is its NVLink form.
 constexpr int kSendRows = 64;   // rows per block
 
-template <bool kAdaGrad, bool kBf16>
+template <class Rule, bool kBf16>
 __global__ void __launch_bounds__(256)
 push_send_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__ SsbInboxView ib,
                  const uint32_t* __restrict__ gslot, const float* __restrict__ grads, int64_t n,
-                 const uint32_t* __restrict__ n_dev, int self_shard, float lr, float eps, uint32_t* __restrict__ overflow,
-                 uint32_t* __restrict__ cursor) {
+                 const uint32_t* __restrict__ n_dev, int self_shard, const __grid_constant__ rule::Hyper h,
+                 uint32_t* __restrict__ overflow, uint32_t* __restrict__ cursor) {
   __shared__ uint32_t cnt[SSB_MAX_SHARDS], base[SSB_MAX_SHARDS];
   __shared__ uint32_t row_slot[kSendRows];
   __shared__ uint16_t row_owner[kSendRows], row_rank[kSendRows];
@@ -695,24 +582,10 @@ push_send_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__
       if (o == 0xFFFF) continue;
       const float* gr = grads + (size_t)r * D;
       if (o == self_shard) {
-        // local row: apply directly
-        float* row = v.rows[o] + (size_t)row_slot[k] * D;
-        float* st = kAdaGrad ? v.state[o] + (size_t)row_slot[k] * D : nullptr;
-        __nv_bfloat16* sh = v.shadow[o] ? reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)row_slot[k] * D : nullptr;
-        for (int j = lane * 4; j < D; j += 128) {
-          float4 gv = *reinterpret_cast<const float4*>(gr + j);
-          if (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
-          float4 d;
-          if (kAdaGrad) {
-            float4 g2 = make_float4(gv.x * gv.x, gv.y * gv.y, gv.z * gv.z, gv.w * gv.w);
-            float4 a = atom_add_f4_sys(st + j, g2);
-            d.x = -lr * gv.x * rsqrtf(a.x + g2.x + eps); d.y = -lr * gv.y * rsqrtf(a.y + g2.y + eps);
-            d.z = -lr * gv.z * rsqrtf(a.z + g2.z + eps); d.w = -lr * gv.w * rsqrtf(a.w + g2.w + eps);
-          } else {
-            d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
-          }
-          row_update_f4(row + j, sh ? sh + j : nullptr, d);
-        }
+        // local row: apply directly (this worker's gradient buffer holds a slot once: single writer, mirror in step)
+        if constexpr (applies_rule<Rule>::value)
+          rule_apply_row<Rule, true>(v, (uint32_t)o * v.capacity + row_slot[k], lane, h,
+                                     [gr](int j) { return *reinterpret_cast<const float4*>(gr + j); }, nullptr);
       } else {
         const uint32_t idx = base[o] + row_rank[k];
         if (idx >= ib.capacity) { if (lane == 0) atomicAdd(overflow, 1u); continue; }
@@ -753,11 +626,11 @@ struct SendChunkState {          // sender-local device memory, zero before the 
   uint32_t* finished;            // [1] blocks of the send kernel that are done
 };
 
-template <bool kAdaGrad>
+template <class Rule>
 __global__ void __launch_bounds__(256)
 push_send_chunks_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__ SsbChunkInboxView ib,
                         const uint32_t* __restrict__ gslot, const float* __restrict__ grads, int64_t n,
-                        const uint32_t* __restrict__ n_dev, int self_shard, float lr, float eps, uint32_t tag,
+                        const uint32_t* __restrict__ n_dev, int self_shard, const __grid_constant__ rule::Hyper h, uint32_t tag,
                         uint32_t* __restrict__ overflow, SendChunkState st) {
   __shared__ uint32_t cnt[SSB_MAX_SHARDS], base[SSB_MAX_SHARDS];
   __shared__ uint32_t row_slot[kSendRows];
@@ -790,24 +663,10 @@ push_send_chunks_kernel(const __grid_constant__ SsbTableView v, const __grid_con
       if (o == 0xFFFF) continue;
       const float* gr = grads + (size_t)r * D;
       if (o == self_shard) {
-        // local row: apply directly
-        float* row = v.rows[o] + (size_t)row_slot[k] * D;
-        float* stt = kAdaGrad ? v.state[o] + (size_t)row_slot[k] * D : nullptr;
-        __nv_bfloat16* sh = v.shadow[o] ? reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)row_slot[k] * D : nullptr;
-        for (int j = lane * 4; j < D; j += 128) {
-          float4 gv = *reinterpret_cast<const float4*>(gr + j);
-          if (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
-          float4 d;
-          if (kAdaGrad) {
-            float4 g2 = make_float4(gv.x * gv.x, gv.y * gv.y, gv.z * gv.z, gv.w * gv.w);
-            float4 a = atom_add_f4_sys(stt + j, g2);
-            d.x = -lr * gv.x * rsqrtf(a.x + g2.x + eps); d.y = -lr * gv.y * rsqrtf(a.y + g2.y + eps);
-            d.z = -lr * gv.z * rsqrtf(a.z + g2.z + eps); d.w = -lr * gv.w * rsqrtf(a.w + g2.w + eps);
-          } else {
-            d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
-          }
-          row_update_f4(row + j, sh ? sh + j : nullptr, d);
-        }
+        // local row: apply directly (this worker's gradient buffer holds a slot once: single writer, mirror in step)
+        if constexpr (applies_rule<Rule>::value)
+          rule_apply_row<Rule, true>(v, (uint32_t)o * v.capacity + row_slot[k], lane, h,
+                                     [gr](int j) { return *reinterpret_cast<const float4*>(gr + j); }, nullptr);
       } else {
         const uint32_t idx = base[o] + row_rank[k];
         if (idx >= ib.seg_rows) { if (lane == 0) atomicAdd(overflow, 1u); continue; }
@@ -866,12 +725,12 @@ push_send_chunks_kernel(const __grid_constant__ SsbTableView v, const __grid_con
 // waits (bounded) until its item is known — the chunk's ready flag carries this step's tag, or the sender's total
 // does (then the chunk holds min(C, total - c*C) rows, possibly none) — and applies it to the local shard.
 // A wait that runs out sets err[0] and gives up on the item (reported by the host) instead of trapping.
-template <bool kAdaGrad>
+template <class Rule>
 __global__ void __launch_bounds__(256)
 push_apply_chunks_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ slots,
                          const __nv_bfloat16* __restrict__ rows, const uint32_t* __restrict__ ready,
                          const uint32_t* __restrict__ total, uint32_t seg_rows, uint32_t max_chunks, int world, int self,
-                         uint32_t tag, float lr, float eps, uint32_t spin_limit, uint32_t* __restrict__ err) {
+                         uint32_t tag, const __grid_constant__ rule::Hyper h, uint32_t spin_limit, uint32_t* __restrict__ err) {
   __shared__ uint32_t n_rows_s;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int D = v.dim;
@@ -900,27 +759,14 @@ push_apply_chunks_kernel(const __grid_constant__ SsbTableView v, const uint32_t*
     for (uint32_t r = warp; r < nr; r += 8) {
       const uint32_t sl = __ldg(slots + seg0 + r);
       if (sl >= v.capacity) continue;
-      float* row = v.rows[0] + (size_t)sl * D;
-      float* stt = kAdaGrad ? v.state[0] + (size_t)sl * D : nullptr;
-      __nv_bfloat16* sh = v.shadow[0] ? reinterpret_cast<__nv_bfloat16*>(v.shadow[0]) + (size_t)sl * D : nullptr;
       const __nv_bfloat16* gr = rows + (seg0 + r) * D;
-      for (int j = lane * 4; j < D; j += 128) {
+      // several senders' chunks can hold the same row: no mirror writes here, the launcher refreshes it afterwards
+      rule_apply_row<Rule, false>(v, sl, lane, h, [gr](int j) {
         const uint2 pk = *reinterpret_cast<const uint2*>(gr + j);
-        const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162*>(&pk.x), hi = *reinterpret_cast<const __nv_bfloat162*>(&pk.y);
-        const float2 a01 = __bfloat1622float2(lo), a23 = __bfloat1622float2(hi);
-        const float4 gv = make_float4(a01.x, a01.y, a23.x, a23.y);
-        if (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
-        float4 d;
-        if (kAdaGrad) {
-          float4 g2 = make_float4(gv.x * gv.x, gv.y * gv.y, gv.z * gv.z, gv.w * gv.w);
-          float4 a = atom_add_f4_sys(stt + j, g2);
-          d.x = -lr * gv.x * rsqrtf(a.x + g2.x + eps); d.y = -lr * gv.y * rsqrtf(a.y + g2.y + eps);
-          d.z = -lr * gv.z * rsqrtf(a.z + g2.z + eps); d.w = -lr * gv.w * rsqrtf(a.w + g2.w + eps);
-        } else {
-          d = make_float4(-lr * gv.x, -lr * gv.y, -lr * gv.z, -lr * gv.w);
-        }
-        row_update_f4<true>(row + j, sh ? sh + j : nullptr, d);
-      }
+        const float2 a01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.x));
+        const float2 a23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.y));
+        return make_float4(a01.x, a01.y, a23.x, a23.y);
+      }, nullptr);
     }
     __syncthreads();
   }
@@ -946,8 +792,9 @@ table_load_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __rest
       for (int j = lane; j < D; j += 32) sh[j] = __float2bfloat16_rn(rows[(size_t)w * D + j]);
     }
     if (state && v.state[p.owner]) {
-      float* st = v.state[p.owner] + (size_t)p.slot * D;
-      for (int j = lane; j < D; j += 32) st[j] = state[(size_t)w * D + j];
+      const int SD = rule_state_stride(v);          // state_words * D floats per entry
+      float* st = v.state[p.owner] + (size_t)p.slot * SD;
+      for (int j = lane; j < SD; j += 32) st[j] = state[(size_t)w * SD + j];
     }
     if (p.is_new) { publish(v, p, key, lane); if (lane == 0 && stats) atomicAdd(stats + 0, 1u); }
   }
@@ -993,7 +840,7 @@ dump_compact_kernel(const uint32_t* __restrict__ keys, const float* __restrict__
 // shard of any size streams through bounded host / device buffers with rows and state aligned.
 __global__ void __launch_bounds__(256)
 dump_compact_range_kernel(const uint32_t* __restrict__ keys, const float* __restrict__ rows, const float* __restrict__ state,
-                          uint32_t bucket_lo, uint32_t bucket_hi, int D, uint32_t* __restrict__ out_keys,
+                          uint32_t bucket_lo, uint32_t bucket_hi, int D, int SD, uint32_t* __restrict__ out_keys,
                           float* __restrict__ out_rows, float* __restrict__ out_state, uint32_t* __restrict__ n_live,
                           uint32_t max_out) {
   const int lane = threadIdx.x & 31;
@@ -1016,10 +863,9 @@ dump_compact_range_kernel(const uint32_t* __restrict__ keys, const float* __rest
       const uint32_t dst = base + __popc(live & ((1u << src) - 1));
       if (dst >= max_out) break;
       const size_t slot = (size_t)b * SSB_BUCKET + src;
-      for (int j = lane; j < D; j += 32) {
-        out_rows[(size_t)dst * D + j] = rows[slot * D + j];
-        if (out_state) out_state[(size_t)dst * D + j] = state[slot * D + j];
-      }
+      for (int j = lane; j < D; j += 32) out_rows[(size_t)dst * D + j] = rows[slot * D + j];
+      if (out_state)
+        for (int j = lane; j < SD; j += 32) out_state[(size_t)dst * SD + j] = state[slot * SD + j];
     }
   }
 }
@@ -1092,30 +938,20 @@ int ssb_gather_slots(const SsbTableView* view, const uint32_t* gslot, int64_t n,
   return 0;
 }
 
+static int map_rule_err(int e) { return e < 0 ? (int)cudaErrorInvalidValue : e; }
+
 int ssb_push_sgd(const SsbTableView* view, const uint32_t* gslot, float* grads, int64_t n,
                  const uint32_t* n_dev, float lr, int zero_grads, void* stream) {
   if (int e = check_view(view)) return e;
-  if (n <= 0) return 0;
-  if (view->shadow[0])
-    ssb::push_kernel<false, true><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, grads, n, n_dev, lr, 0.f, zero_grads);
-  else
-    ssb::push_kernel<false, false><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, grads, n, n_dev, lr, 0.f, zero_grads);
-  SSB_LAUNCH_CHECK();
-  return 0;
+  const ssb::rule::Hyper h{lr, 0.f, 0.f, 0.f, 0.f, 0u};
+  return map_rule_err(ssb::launch_rule_push<ssb::rule::Sgd>(view, gslot, grads, n, n_dev, &h, zero_grads, -1, stream, ssb::row_grid(n)));
 }
 
 int ssb_push_adagrad(const SsbTableView* view, const uint32_t* gslot, float* grads, int64_t n,
                      const uint32_t* n_dev, float lr, float eps, int zero_grads, void* stream) {
   if (int e = check_view(view)) return e;
-  for (int i = 0; i < view->num_shards; ++i)
-    if (!view->state[i]) return (int)cudaErrorInvalidValue;
-  if (n <= 0) return 0;
-  if (view->shadow[0])
-    ssb::push_kernel<true, true><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, grads, n, n_dev, lr, eps, zero_grads);
-  else
-    ssb::push_kernel<true, false><<<ssb::row_grid(n), 256, 0, (cudaStream_t)stream>>>(*view, gslot, grads, n, n_dev, lr, eps, zero_grads);
-  SSB_LAUNCH_CHECK();
-  return 0;
+  const ssb::rule::Hyper h{lr, eps, 0.f, 0.f, 0.f, 0u};
+  return map_rule_err(ssb::launch_rule_push<ssb::rule::AdaGrad>(view, gslot, grads, n, n_dev, &h, zero_grads, -1, stream, ssb::row_grid(n)));
 }
 
 int ssb_push_send2(const SsbTableView* view, const SsbInboxView* inbox, const uint32_t* gslot, const float* grads,
@@ -1135,9 +971,15 @@ int ssb_push_send2(const SsbTableView* view, const SsbInboxView* inbox, const ui
   if (!inbox || inbox->capacity == 0 || (view->dim & 3) != 0) return (int)cudaErrorInvalidValue;
   if (n <= 0) return 0;
   int blocks = ssb::grid_for(n, ssb::kSendRows, ssb::kNumSMs * 8);
-#define SSB_SEND(A, B) ssb::push_send_kernel<A, B><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, overflow, cursor)
-  if (adagrad) { if (bf16_rows) SSB_SEND(true, true); else SSB_SEND(true, false); }
-  else { if (bf16_rows) SSB_SEND(false, true); else SSB_SEND(false, false); }
+  // `adagrad` is a rule id: 0 SGD, 1 AdaGrad, -1 ship only (the caller applies its own rows with any rule of
+  // include/ssb200_rule.cuh: ssb_rule_<name>_push(..., only_shard = self_shard))
+  const ssb::rule::Hyper h{lr, eps, 0.f, 0.f, 0.f, 0u};
+  if (adagrad == 1 && ssb::rule_check(view, 1)) return (int)cudaErrorInvalidValue;
+#define SSB_SEND(R, B) ssb::push_send_kernel<R, B><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, h, overflow, cursor)
+  if (adagrad == 1) { if (bf16_rows) SSB_SEND(ssb::rule::AdaGrad, true); else SSB_SEND(ssb::rule::AdaGrad, false); }
+  else if (adagrad == 0) { if (bf16_rows) SSB_SEND(ssb::rule::Sgd, true); else SSB_SEND(ssb::rule::Sgd, false); }
+  else if (adagrad == -1) { if (bf16_rows) SSB_SEND(ssb::ShipOnly, true); else SSB_SEND(ssb::ShipOnly, false); }
+  else return (int)cudaErrorInvalidValue;
 #undef SSB_SEND
   SSB_LAUNCH_CHECK();
   return 0;
@@ -1155,10 +997,14 @@ int ssb_push_send_chunks(const SsbTableView* view, const SsbChunkInboxView* inbo
   // the kernel always runs (also with n == 0): its last block publishes this step's totals to every owner
   int blocks = ssb::grid_for(n > 0 ? n : 1, ssb::kSendRows, ssb::kNumSMs * 8);
   ssb::SendChunkState st{cursor, done, finished};
-  if (adagrad)
-    ssb::push_send_chunks_kernel<true><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, tag, overflow, st);
+  const ssb::rule::Hyper h{lr, eps, 0.f, 0.f, 0.f, 0u};
+  if (adagrad == 1 && ssb::rule_check(view, 1)) return (int)cudaErrorInvalidValue;
+  if (adagrad == 1)
+    ssb::push_send_chunks_kernel<ssb::rule::AdaGrad><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, h, tag, overflow, st);
+  else if (adagrad == 0)
+    ssb::push_send_chunks_kernel<ssb::rule::Sgd><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, h, tag, overflow, st);
   else
-    ssb::push_send_chunks_kernel<false><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, lr, eps, tag, overflow, st);
+    ssb::push_send_chunks_kernel<ssb::ShipOnly><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, h, tag, overflow, st);
   SSB_LAUNCH_CHECK();
   return 0;
 }
@@ -1176,11 +1022,17 @@ int ssb_push_apply_chunks(const SsbTableView* local_view, const uint32_t* slots,
   const uint32_t max_chunks = seg_rows / ssb::kChunkRows;
   // one block per SM at most: the waiting blocks of this kernel must never fill the SMs the send kernel needs
   const int blocks = (int)std::min<uint64_t>((uint64_t)max_chunks * (uint64_t)world, (uint64_t)ssb::kNumSMs);
+  const ssb::rule::Hyper h{lr, eps, 0.f, 0.f, 0.f, 0u};
   if (adagrad)
-    ssb::push_apply_chunks_kernel<true><<<blocks, 256, 0, (cudaStream_t)stream>>>(*local_view, slots, (const __nv_bfloat16*)rows_bf16, ready, total, seg_rows, max_chunks, world, self, tag, lr, eps, spin_limit, err);
+    ssb::push_apply_chunks_kernel<ssb::rule::AdaGrad><<<blocks, 256, 0, (cudaStream_t)stream>>>(*local_view, slots, (const __nv_bfloat16*)rows_bf16, ready, total, seg_rows, max_chunks, world, self, tag, h, spin_limit, err);
   else
-    ssb::push_apply_chunks_kernel<false><<<blocks, 256, 0, (cudaStream_t)stream>>>(*local_view, slots, (const __nv_bfloat16*)rows_bf16, ready, total, seg_rows, max_chunks, world, self, tag, lr, eps, spin_limit, err);
+    ssb::push_apply_chunks_kernel<ssb::rule::Sgd><<<blocks, 256, 0, (cudaStream_t)stream>>>(*local_view, slots, (const __nv_bfloat16*)rows_bf16, ready, total, seg_rows, max_chunks, world, self, tag, h, spin_limit, err);
   SSB_LAUNCH_CHECK();
+  if (local_view->shadow[0]) {     // rows listed by several senders had several writers: set the mirror from the final rows
+    dim3 grid((unsigned)std::max(1, ssb::kNumSMs * 4 / world), (unsigned)world);
+    ssb::rule_mirror_refresh_kernel<0><<<grid, 256, 0, (cudaStream_t)stream>>>(*local_view, slots, seg_rows, total, seg_rows, 2);
+    SSB_LAUNCH_CHECK();
+  }
   return 0;
 }
 
@@ -1189,13 +1041,11 @@ int ssb_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, const voi
   if (int e = check_view(view)) return e;
   if ((view->dim & 3) != 0 || num_segs < 1 || num_segs > SSB_MAX_SHARDS || (num_segs > 1 && !counts)) return (int)cudaErrorInvalidValue;
   if (seg_rows <= 0) return 0;
-  dim3 grid(ssb::grid_for(seg_rows, 8, ssb::kNumSMs * 8 / (num_segs > 1 ? 2 : 1)), num_segs);
+  const int gx = ssb::grid_for(seg_rows, 8, ssb::kNumSMs * 8 / (num_segs > 1 ? 2 : 1));
+  const ssb::rule::Hyper h{lr, eps, 0.f, 0.f, 0.f, 0u};
   if (adagrad)
-    ssb::push_bf16_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(*view, gslot, (const __nv_bfloat16*)grads_bf16, seg_rows, counts, lr, eps, seg_rows);
-  else
-    ssb::push_bf16_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(*view, gslot, (const __nv_bfloat16*)grads_bf16, seg_rows, counts, lr, eps, seg_rows);
-  SSB_LAUNCH_CHECK();
-  return 0;
+    return map_rule_err(ssb::launch_rule_push_bf16_seg<ssb::rule::AdaGrad>(view, gslot, grads_bf16, seg_rows, counts, num_segs, seg_rows, &h, stream, gx));
+  return map_rule_err(ssb::launch_rule_push_bf16_seg<ssb::rule::Sgd>(view, gslot, grads_bf16, seg_rows, counts, num_segs, seg_rows, &h, stream, gx));
 }
 
 int ssb_push_bf16(const SsbTableView* view, const uint32_t* gslot, const void* grads_bf16, int64_t n, const uint32_t* n_dev,
@@ -1244,7 +1094,8 @@ int ssb_table_load(const SsbTableView* view, const uint32_t* keys, const float* 
 
 int ssb_dump_compact_range(const uint32_t* keys, const float* rows, const float* state, uint32_t capacity, int32_t dim,
                            uint32_t slot_lo, uint32_t slot_hi, uint32_t* out_keys, float* out_rows, float* out_state,
-                           uint32_t* n_live, uint32_t max_out, void* stream) {
+                           uint32_t* n_live, uint32_t max_out, int32_t state_dim, void* stream) {
+  if (state_dim <= 0) state_dim = dim;       // floats of optimizer state per entry (state_words * dim)
   if (capacity == 0 || capacity % SSB_BUCKET != 0 || slot_lo % SSB_BUCKET != 0 || slot_hi % SSB_BUCKET != 0 ||
       slot_lo > slot_hi || slot_hi > capacity || dim < 1 || !keys || !rows || !out_keys || !out_rows || !n_live ||
       (out_state && !state))
@@ -1254,7 +1105,7 @@ int ssb_dump_compact_range(const uint32_t* keys, const float* rows, const float*
   if (slot_lo == slot_hi) return 0;
   const uint32_t b_lo = slot_lo / SSB_BUCKET, b_hi = slot_hi / SSB_BUCKET;
   ssb::dump_compact_range_kernel<<<ssb::row_grid(b_hi - b_lo), 256, 0, (cudaStream_t)stream>>>(
-      keys, rows, state, b_lo, b_hi, dim, out_keys, out_rows, out_state, n_live, max_out);
+      keys, rows, state, b_lo, b_hi, dim, state_dim, out_keys, out_rows, out_state, n_live, max_out);
   SSB_LAUNCH_CHECK();
   return 0;
 }

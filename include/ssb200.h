@@ -26,7 +26,8 @@ extern "C" {
 typedef struct SsbTableView {
   uint32_t *keys[SSB_MAX_SHARDS];  /* [capacity] per shard, SSB_EMPTY_KEY when free          */
   float *rows[SSB_MAX_SHARDS];     /* [capacity][dim] parameter rows                          */
-  float *state[SSB_MAX_SHARDS];    /* [capacity][dim] AdaGrad accumulators, or NULL           */
+  float *state[SSB_MAX_SHARDS];    /* [capacity][state_words][dim] optimizer state (AdaGrad
+                                      accumulator = 1 word; FTRL z, n = 2 words), or NULL        */
   void *shadow[SSB_MAX_SHARDS];    /* [capacity][dim] bf16 mirror of rows, or NULL. Kept in step by
                                       every owner-side writer (insert, load, local/inbox push); a
                                       pull that only wants bf16 reads it: half the row bytes over
@@ -38,8 +39,18 @@ typedef struct SsbTableView {
   int32_t num_shards;
   uint64_t seed;                   /* deterministic lazy init: row = f(key, seed)             */
   float init_scale;                /* init value = (u01 - 0.5) * init_scale                   */
+  int32_t state_words;             /* floats of optimizer state per weight (0 reads as 1)     */
+  int32_t init_kind;               /* SSB_INIT_*: how the pull kernels create a missing row   */
   int32_t pad_;
 } SsbTableView;
+
+/* Lazy row init kinds (ref: PullAccessMethod::init_param, sparse_access_method.h:21). Element j of key's row:
+ * UNIFORM (u01(key, j, seed) - 0.5) * init_scale (the word2vec app's randInit, vec1.h:223-226); ZERO 0 (sparse LR,
+ * FTRL); CONSTANT init_scale; UNIFORM_POS u01 * init_scale. */
+#define SSB_INIT_UNIFORM 0
+#define SSB_INIT_ZERO 1
+#define SSB_INIT_CONSTANT 2
+#define SSB_INIT_UNIFORM_POS 3
 
 /* ---- K1: key hashing / routing / bucketing ------------------------------------------------
  * ref: utils/HashFunction.h:16-24, parameter/hashfrag.h:48-53, global_pull_access.h:58-72 */
@@ -247,7 +258,7 @@ int ssb_memset_async(void *p, int value, uint64_t bytes, void *stream);
  * ref: parameter/sparsetable.h:49-56 — the reference dumps the whole Param (row + whatever state it carries). */
 int ssb_dump_compact_range(const uint32_t *keys, const float *rows, const float *state, uint32_t capacity, int32_t dim,
                            uint32_t slot_lo, uint32_t slot_hi, uint32_t *out_keys, float *out_rows, float *out_state,
-                           uint32_t *n_live, uint32_t max_out, void *stream);
+                           uint32_t *n_live, uint32_t max_out, int32_t state_dim /* state_words * dim; 0 = dim */, void *stream);
 /* ---- K11: parameter dump -----------------------------------------------------------------
  * Compacts the live slots of one shard: out_keys[*n_live], out_rows[*n_live][dim].        */
 int ssb_dump_compact(const uint32_t *keys, const float *rows, uint32_t capacity, int32_t dim,

@@ -40,6 +40,11 @@ int64_t ssb_dump_write_text2(const char *path, const uint32_t *keys, const float
                              int dim, int append, int digits);
 int64_t ssb_dump_read_text2(const char *path, uint32_t *keys, float *rows, float *state, int64_t max_n, int dim,
                             int *has_state);
+/* The same with state_dim floats of optimizer state per entry (state words x dim: AdaGrad dim, FTRL 2 x dim). */
+int64_t ssb_dump_write_text3(const char *path, const uint32_t *keys, const float *rows, const float *state, int64_t n,
+                             int dim, int state_dim, int append, int digits);
+int64_t ssb_dump_read_text3(const char *path, uint32_t *keys, float *rows, float *state, int64_t max_n, int dim,
+                            int state_dim, int *has_state);
 
 /* CPU sparse table with the stock SGD / AdaGrad access methods — ref: parameter/sparsetable.h */
 void *ssb_cpu_table_new(int shard_num, int dim, int adagrad, float lr, float eps, uint64_t seed,

@@ -1,0 +1,366 @@
+// ssb200_rule.cuh — the device-side update rule: the seam where a user's optimizer enters the push path.
+//
+// ref: core/parameter/sparse_access_method.h:21-46 — the reference's user supplies a PullAccessMethod
+//      (init_param / get_pull_value) and a PushAccessMethod (apply_push_value) as C++ classes that the server
+//      calls once per key on the host. Here the rule is a stateless struct of __device__ functions that the push
+//      kernels are instantiated with; everything else (slot decode, atomics on rows that other GPUs update at the
+//      same time, the bf16 row mirror, bf16 gradients that crossed NVLink) stays in the kernels of this header.
+//
+// Writing a rule (see Sgd / AdaGrad / Ftrl below for three complete ones):
+//
+//   struct MyRule {
+//     static constexpr int  kStateWords  = 1;      // floats of optimizer state per weight (0, 1, 2 ...)
+//     static constexpr bool kSkipZeroGrad = true;  // a zero gradient changes nothing (true for almost every rule)
+//     static constexpr int  kInit = SSB_INIT_UNIFORM;   // how a missing row is created by the pull kernels
+//     // Four consecutive weights of one row. `w` points at the weights, `st` at state word 0 of the same four
+//     // weights, word k is at st + k * D. Other warps (other senders' segments, other GPUs) may update the same
+//     // row at the same moment (Hogwild, as in the reference's server): touch state with the atomics below.
+//     // Return the INCREMENT to add to the weights; the kernel adds it atomically and keeps the mirror in step.
+//     static __device__ float4 apply4(const float* w, float* st, int D, float4 g, const Hyper& h);
+//     static __device__ float  apply1(const float* w, float* st, int D, float g, const Hyper& h);   // D % 4 != 0
+//   };
+//   SSB200_EXPORT_RULE(myrule, MyRule)       // in a .cu of your own: extern "C" ssb_rule_myrule_* entry points
+//
+// `swiftsnails_b200.ops.rules.Rule.from_source("myrule", path)` compiles such a file for sm_100a and loads it;
+// `framework.PushMethod("myrule", lr=..)` / `ShardedTable.push_rule` then use it by name. No file of the framework
+// is edited. The table must have been created with `with_state >= kStateWords`.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "ssb200.h"
+
+namespace ssb {
+
+// ---- system-scope accesses to rows / state (the other writer may be a peer GPU over NVLink) --------------------
+// Streaming 16-byte load that bypasses L1 allocation (rows are mutated by other SMs / GPUs).
+__device__ __forceinline__ float4 ld_row_f4(const float* p) {
+  float4 r;
+  asm volatile("ld.relaxed.sys.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ float ld_row_f1(const float* p) {
+  float r;
+  asm volatile("ld.relaxed.sys.global.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");
+  return r;
+}
+// Vector reduction into (possibly remote) memory: REDG.E.ADD.F32x4 .SYS
+__device__ __forceinline__ void red_add_f4_sys(float* p, float4 v) {
+  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x),
+               "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void red_add_f1_sys(float* p, float v) {
+  asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+// The same, returning the value before the add.
+__device__ __forceinline__ float4 atom_add_f4_sys(float* p, float4 v) {
+  float4 r;
+  asm volatile("atom.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4], {%5,%6,%7,%8};"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ float atom_add_f1_sys(float* p, float v) {
+  float r;
+  asm volatile("atom.relaxed.sys.global.add.f32 %0, [%1], %2;" : "=f"(r) : "l"(p), "f"(v) : "memory");
+  return r;
+}
+
+namespace rule {
+
+// Hyper-parameters, passed to the kernel by value. lr / eps have their usual meaning; a, b, c are the rule's own
+// (Ftrl: a = l1, b = l2; a rule with momentum would put its coefficient there).
+struct Hyper {
+  float lr, eps, a, b, c;
+  uint32_t step;        // the caller's step counter (rules with bias correction)
+};
+
+// w -= lr * g.  ref: the word2vec app's SGD push (apps/word2vec/word2vec.h, `param -= lr * grad`).
+struct Sgd {
+  static constexpr int kStateWords = 0;
+  static constexpr bool kSkipZeroGrad = true;
+  static constexpr int kInit = SSB_INIT_UNIFORM;
+  static __device__ __forceinline__ float4 apply4(const float*, float*, int, float4 g, const Hyper& h) {
+    return make_float4(-h.lr * g.x, -h.lr * g.y, -h.lr * g.z, -h.lr * g.w);
+  }
+  static __device__ __forceinline__ float apply1(const float*, float*, int, float g, const Hyper& h) { return -h.lr * g; }
+};
+
+// acc += g^2 ; w -= lr * g / sqrt(acc + eps).  One vector atomic claims "my" accumulator value, so concurrent
+// updates of one weight each see a distinct, growing accumulator (no lost g^2).
+struct AdaGrad {
+  static constexpr int kStateWords = 1;
+  static constexpr bool kSkipZeroGrad = true;
+  static constexpr int kInit = SSB_INIT_UNIFORM;
+  static __device__ __forceinline__ float4 apply4(const float*, float* st, int, float4 g, const Hyper& h) {
+    const float4 g2 = make_float4(g.x * g.x, g.y * g.y, g.z * g.z, g.w * g.w);
+    const float4 a = atom_add_f4_sys(st, g2);
+    return make_float4(-h.lr * g.x * rsqrtf(a.x + g2.x + h.eps), -h.lr * g.y * rsqrtf(a.y + g2.y + h.eps),
+                       -h.lr * g.z * rsqrtf(a.z + g2.z + h.eps), -h.lr * g.w * rsqrtf(a.w + g2.w + h.eps));
+  }
+  static __device__ __forceinline__ float apply1(const float*, float* st, int, float g, const Hyper& h) {
+    const float g2 = g * g;
+    const float a = atom_add_f1_sys(st, g2);
+    return -h.lr * g * rsqrtf(a + g2 + h.eps);
+  }
+};
+
+// FTRL-proximal (McMahan et al. 2013), the usual optimizer of sparse logistic regression on a parameter server.
+// Per weight: n += g^2 ; sigma = (sqrt(n) - sqrt(n_old)) / alpha ; z += g - sigma * w ;
+//             w = 0 if |z| <= l1 else -(z - sign(z) * l1) / ((beta + sqrt(n)) / alpha + l2).
+// State word 0 = z, word 1 = n; both only ever receive ADDS, so they go in with atomics and no update is lost when
+// several senders hit one weight; the weight read for sigma * w may be one update old (Hogwild, as on the
+// reference's server). alpha = h.lr, beta = h.eps, l1 = h.a, l2 = h.b. Rows start at zero (kInit).
+struct Ftrl {
+  static constexpr int kStateWords = 2;
+  static constexpr bool kSkipZeroGrad = true;
+  static constexpr int kInit = SSB_INIT_ZERO;
+  static __device__ __forceinline__ float weight(float z, float n, const Hyper& h) {
+    const float az = fabsf(z);
+    if (az <= h.a) return 0.f;
+    return -(z - copysignf(h.a, z)) / ((h.eps + sqrtf(n)) / h.lr + h.b);
+  }
+  static __device__ __forceinline__ float apply1(const float* w, float* st, int D, float g, const Hyper& h) {
+    const float g2 = g * g;
+    const float n_old = atom_add_f1_sys(st + D, g2);
+    const float w_cur = ld_row_f1(w);
+    const float sigma = (sqrtf(n_old + g2) - sqrtf(n_old)) / h.lr;
+    const float dz = g - sigma * w_cur;
+    const float z_old = atom_add_f1_sys(st, dz);
+    return weight(z_old + dz, n_old + g2, h) - w_cur;
+  }
+  static __device__ __forceinline__ float4 apply4(const float* w, float* st, int D, float4 g, const Hyper& h) {
+    const float4 g2 = make_float4(g.x * g.x, g.y * g.y, g.z * g.z, g.w * g.w);
+    const float4 n_old = atom_add_f4_sys(st + D, g2);
+    const float4 w_cur = ld_row_f4(w);
+    const float inv = 1.f / h.lr;
+    const float4 dz = make_float4(g.x - (sqrtf(n_old.x + g2.x) - sqrtf(n_old.x)) * inv * w_cur.x,
+                                  g.y - (sqrtf(n_old.y + g2.y) - sqrtf(n_old.y)) * inv * w_cur.y,
+                                  g.z - (sqrtf(n_old.z + g2.z) - sqrtf(n_old.z)) * inv * w_cur.z,
+                                  g.w - (sqrtf(n_old.w + g2.w) - sqrtf(n_old.w)) * inv * w_cur.w);
+    const float4 z_old = atom_add_f4_sys(st, dz);
+    return make_float4(weight(z_old.x + dz.x, n_old.x + g2.x, h) - w_cur.x, weight(z_old.y + dz.y, n_old.y + g2.y, h) - w_cur.y,
+                       weight(z_old.z + dz.z, n_old.z + g2.z, h) - w_cur.z, weight(z_old.w + dz.w, n_old.w + g2.w, h) - w_cur.w);
+  }
+};
+
+}  // namespace rule
+
+// ---- the kernels a rule is instantiated into ---------------------------------------------------------------------
+__device__ __forceinline__ uint2 rule_pack_bf16x4(float4 v) {
+  __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+  uint2 pk;
+  pk.x = *reinterpret_cast<uint32_t*>(&lo);
+  pk.y = *reinterpret_cast<uint32_t*>(&hi);
+  return pk;
+}
+__device__ __forceinline__ uint32_t rule_effective_n(int64_t n, const uint32_t* n_dev) {
+  uint32_t ne = (uint32_t)n;
+  if (n_dev) { uint32_t d = *n_dev; if (d < ne) ne = d; }
+  return ne;
+}
+// floats of state per row as the table was allocated (0 in old views means 1)
+__device__ __forceinline__ int rule_state_stride(const SsbTableView& v) { return (v.state_words > 0 ? v.state_words : 1) * v.dim; }
+
+// One row, one warp: apply the rule to every 4-weight group with a non-zero gradient.
+// kMirror: this launch is the ONLY writer of the row (a worker's dedup'd gradient buffer holds a slot once), so the
+// bf16 mirror can be written from the value the atomic returned. Launches with several writers per row (inbox
+// segments) pass kMirror = false and run rule_mirror_refresh_kernel afterwards.
+template <class Rule, bool kMirror, class GradLoad>
+__device__ __forceinline__ void rule_apply_row(const SsbTableView& v, uint32_t g, int lane, const rule::Hyper& h, GradLoad load4,
+                                               float* zero_fp32_grads) {
+  const int D = v.dim;
+  const uint32_t o = g / v.capacity, s = g - o * v.capacity;
+  float* row = v.rows[o] + (size_t)s * D;
+  float* st = (Rule::kStateWords > 0) ? v.state[o] + (size_t)s * rule_state_stride(v) : nullptr;
+  __nv_bfloat16* sh = (kMirror && v.shadow[o]) ? reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)s * D : nullptr;
+  for (int j = lane * 4; j < D; j += 128) {
+    const float4 gv = load4(j);
+    if (Rule::kSkipZeroGrad && gv.x == 0.f && gv.y == 0.f && gv.z == 0.f && gv.w == 0.f) continue;
+    const float4 d = Rule::apply4(row + j, st ? st + j : nullptr, D, gv, h);
+    if (kMirror && sh) {
+      const float4 o4 = atom_add_f4_sys(row + j, d);
+      *reinterpret_cast<uint2*>(sh + j) = rule_pack_bf16x4(make_float4(o4.x + d.x, o4.y + d.y, o4.z + d.z, o4.w + d.w));
+    } else {
+      red_add_f4_sys(row + j, d);
+    }
+    if (zero_fp32_grads) *reinterpret_cast<float4*>(zero_fp32_grads + j) = make_float4(0, 0, 0, 0);
+  }
+}
+
+// Push of a worker's fp32 gradient rows straight into the owners' rows (local HBM or a peer's over NVLink).
+// only_shard >= 0: apply only the rows that shard owns (the worker's own rows when the rest goes through the inbox).
+// 32 registers = 8 blocks per SM for Sgd / AdaGrad: rules that wait on an `atom` per group hide it with resident warps
+// (at 40 registers / 6 blocks the AdaGrad push ran 20 % slower). Rules with two or more state words get 48 registers.
+template <class Rule> constexpr int rule_min_blocks() { return Rule::kStateWords >= 2 ? 5 : 8; }
+template <class Rule, bool kShadow>
+__global__ void __launch_bounds__(256, rule_min_blocks<Rule>())
+rule_push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot, float* grads, int64_t n,
+                 const uint32_t* __restrict__ n_dev, const __grid_constant__ rule::Hyper h, int zero_grads, int only_shard) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t ne = rule_effective_n(n, n_dev);
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const int D = v.dim;
+  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
+    const uint32_t g = __ldg(gslot + w);
+    if (g == SSB_INVALID_SLOT) continue;
+    if (only_shard >= 0 && (int)(g / v.capacity) != only_shard) continue;
+    float* gr = grads + (size_t)w * D;
+    if ((D & 3) == 0) {
+      rule_apply_row<Rule, kShadow>(v, g, lane, h, [gr](int j) { return *reinterpret_cast<const float4*>(gr + j); },
+                                    zero_grads ? gr : nullptr);
+    } else {
+      const uint32_t o = g / v.capacity, s = g - o * v.capacity;
+      float* row = v.rows[o] + (size_t)s * D;
+      float* st = (Rule::kStateWords > 0) ? v.state[o] + (size_t)s * rule_state_stride(v) : nullptr;
+      __nv_bfloat16* sh = (kShadow && v.shadow[o]) ? reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)s * D : nullptr;
+      for (int j = lane; j < D; j += 32) {
+        const float gv = gr[j];
+        if (Rule::kSkipZeroGrad && gv == 0.f) continue;
+        const float d = Rule::apply1(row + j, st ? st + j : nullptr, D, gv, h);
+        if (kShadow && sh) { const float o1 = atom_add_f1_sys(row + j, d); sh[j] = __float2bfloat16_rn(o1 + d); }
+        else red_add_f1_sys(row + j, d);
+        if (zero_grads) gr[j] = 0.f;
+      }
+    }
+  }
+}
+
+// Owner-side apply of inbox segments whose gradient rows travelled as bf16 (half the NVLink bytes); the rule runs in
+// fp32 on fp32 rows / state. blockIdx.y = segment (one per sender): segment y holds rows
+// [y * seg_stride, y * seg_stride + n_dev[y]). Hot rows arrive from every sender, so a row can have several writers
+// in this launch: the mirror is NOT written here (see rule_mirror_refresh_kernel). D % 4 == 0.
+template <class Rule>
+__global__ void __launch_bounds__(256)
+rule_push_bf16_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot,
+                      const __nv_bfloat16* __restrict__ grads, int64_t n, const uint32_t* __restrict__ n_dev,
+                      const __grid_constant__ rule::Hyper h, int64_t seg_stride) {
+  if (n_dev) n_dev += blockIdx.y;
+  gslot += (size_t)blockIdx.y * seg_stride;
+  grads += (size_t)blockIdx.y * seg_stride * v.dim;
+  const int lane = threadIdx.x & 31;
+  const uint32_t ne = rule_effective_n(n, n_dev);
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const int D = v.dim;
+  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
+    const uint32_t g = __ldg(gslot + w);
+    if (g == SSB_INVALID_SLOT) continue;
+    const __nv_bfloat16* gr = grads + (size_t)w * D;
+    rule_apply_row<Rule, false>(v, g, lane, h, [gr](int j) {
+      const uint2 pk = *reinterpret_cast<const uint2*>(gr + j);
+      const float2 a01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.x));
+      const float2 a23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.y));
+      return make_float4(a01.x, a01.y, a23.x, a23.y);
+    }, nullptr);
+  }
+}
+
+// mirror[slot] = bf16(row[slot]) for every slot of the given segments. Runs in stream order AFTER a launch that had
+// several writers per row: every writer of that launch is done, so whichever warp refreshes a row (a row listed by
+// three senders is refreshed three times) stores the same, final value — the mirror is bit-exactly bf16(row).
+// The rows were just written, so the reads are L2 hits.
+template <int kUnused = 0>
+__global__ void __launch_bounds__(256)
+rule_mirror_refresh_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot, int64_t n,
+                           const uint32_t* __restrict__ n_dev, int64_t seg_stride, int n_dev_stride) {
+  if (n_dev) n_dev += (size_t)blockIdx.y * n_dev_stride;
+  gslot += (size_t)blockIdx.y * seg_stride;
+  const int lane = threadIdx.x & 31;
+  const uint32_t ne = rule_effective_n(n, n_dev);
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const int D = v.dim;
+  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
+    const uint32_t g = __ldg(gslot + w);
+    if (g == SSB_INVALID_SLOT) continue;
+    const uint32_t o = g / v.capacity, s = g - o * v.capacity;
+    if (o >= (uint32_t)v.num_shards || !v.shadow[o]) continue;
+    const float* row = v.rows[o] + (size_t)s * D;
+    __nv_bfloat16* sh = reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)s * D;
+    if ((D & 3) == 0) {
+      for (int j = lane * 4; j < D; j += 128) *reinterpret_cast<uint2*>(sh + j) = rule_pack_bf16x4(ld_row_f4(row + j));
+    } else {
+      for (int j = lane; j < D; j += 32) sh[j] = __float2bfloat16_rn(ld_row_f1(row + j));
+    }
+  }
+}
+
+// ---- host-side launchers -----------------------------------------------------------------------------------------
+inline int rule_grid(int64_t rows, int max_blocks_per_sm = 8) {
+  int64_t b = (rows + 7) / 8;                  // 8 warps per block, one row per warp per trip
+  const int64_t cap = 148LL * max_blocks_per_sm;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+inline bool rule_view_has_shadow(const SsbTableView* v) {
+  for (int i = 0; i < v->num_shards; ++i) if (v->shadow[i]) return true;
+  return false;
+}
+inline int rule_check(const SsbTableView* v, int state_words) {
+  if (!v || v->dim <= 0 || v->num_shards <= 0 || v->num_shards > SSB_MAX_SHARDS) return -1;
+  if (state_words > 0) {
+    if ((v->state_words > 0 ? v->state_words : 1) < state_words) return -3;      // table allocated with too little state
+    for (int i = 0; i < v->num_shards; ++i) if (!v->state[i]) return -3;
+  }
+  return 0;
+}
+
+template <class Rule>
+int launch_rule_push(const SsbTableView* view, const uint32_t* gslot, float* grads, int64_t n, const uint32_t* n_dev,
+                     const rule::Hyper* hyper, int zero_grads, int only_shard, void* stream, int grid = 0) {
+  if (int e = rule_check(view, Rule::kStateWords)) return e;
+  if (!hyper) return -1;
+  if (n <= 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (grid <= 0) grid = rule_grid(n);
+  if (rule_view_has_shadow(view))
+    rule_push_kernel<Rule, true><<<grid, 256, 0, s>>>(*view, gslot, grads, n, n_dev, *hyper, zero_grads, only_shard);
+  else
+    rule_push_kernel<Rule, false><<<grid, 256, 0, s>>>(*view, gslot, grads, n, n_dev, *hyper, zero_grads, only_shard);
+  return (int)cudaGetLastError();
+}
+
+// Segmented bf16 apply (+ mirror refresh when the shards keep a mirror). segments = 1, seg_stride = 0: one flat list.
+template <class Rule>
+int launch_rule_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, const void* grads_bf16, int64_t seg_rows,
+                              const uint32_t* n_dev, int segments, int64_t seg_stride, const rule::Hyper* hyper, void* stream,
+                              int gx = 0) {
+  if (int e = rule_check(view, Rule::kStateWords)) return e;
+  if (!hyper || (view->dim & 3) || segments <= 0 || (segments > 1 && !n_dev)) return -1;
+  if (seg_rows <= 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (gx <= 0) gx = rule_grid(seg_rows) / segments;
+  if (gx < 1) gx = 1;
+  dim3 grid((unsigned)gx, (unsigned)segments);
+  rule_push_bf16_kernel<Rule><<<grid, 256, 0, s>>>(*view, gslot, reinterpret_cast<const __nv_bfloat16*>(grads_bf16), seg_rows,
+                                                   n_dev, *hyper, seg_stride);
+  if (rule_view_has_shadow(view))
+    rule_mirror_refresh_kernel<0><<<grid, 256, 0, s>>>(*view, gslot, seg_rows, n_dev, seg_stride, 1);
+  return (int)cudaGetLastError();
+}
+
+}  // namespace ssb
+
+// extern "C" entry points of a rule, found by name from Python (ops/rules.py):
+//   ssb_rule_<name>_info(int out[4])            -> {kStateWords, kInit, 0, 0}
+//   ssb_rule_<name>_push(...)                   -> fp32 gradient rows, local or direct-remote
+//   ssb_rule_<name>_push_bf16_seg(...)          -> owner-side apply of bf16 inbox segments
+#define SSB200_EXPORT_RULE(name, Rule)                                                                                      \
+  extern "C" int ssb_rule_##name##_info(int32_t* out) {                                                                     \
+    out[0] = Rule::kStateWords; out[1] = Rule::kInit; out[2] = 0; out[3] = 0;                                              \
+    return 0;                                                                                                               \
+  }                                                                                                                         \
+  extern "C" int ssb_rule_##name##_push(const SsbTableView* view, const uint32_t* gslot, float* grads, int64_t n,           \
+                                        const uint32_t* n_dev, const ssb::rule::Hyper* hyper, int32_t zero_grads,          \
+                                        int32_t only_shard, void* stream) {                                                \
+    return ssb::launch_rule_push<Rule>(view, gslot, grads, n, n_dev, hyper, zero_grads, only_shard, stream);                \
+  }                                                                                                                         \
+  extern "C" int ssb_rule_##name##_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, const void* grads_bf16,   \
+                                                 int64_t seg_rows, const uint32_t* n_dev, int32_t segments,                \
+                                                 int64_t seg_stride, const ssb::rule::Hyper* hyper, void* stream) {        \
+    return ssb::launch_rule_push_bf16_seg<Rule>(view, gslot, grads_bf16, seg_rows, n_dev, segments, seg_stride, hyper,      \
+                                                stream);                                                                   \
+  }

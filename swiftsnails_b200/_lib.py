@@ -40,6 +40,8 @@ class SsbTableView(C.Structure):
         ("num_shards", C.c_int32),
         ("seed", C.c_uint64),
         ("init_scale", C.c_float),
+        ("state_words", C.c_int32),
+        ("init_kind", C.c_int32),
         ("pad_", C.c_int32),
     ]
 
@@ -89,7 +91,7 @@ _KERNEL_SIGS = {
     "ssb_flags_signal": ([C.POINTER(SsbInboxView), _i32, _i32, _u32, _vp], 1),
     "ssb_flags_wait": ([_vp, _i32, _u32, _vp], 1),
     "ssb_flags_wait2": ([_vp, _i32, _u32, _u32, _vp, _vp], 1),
-    "ssb_dump_compact_range": ([_vp, _vp, _vp, _u32, _i32, _u32, _u32, _vp, _vp, _vp, _vp, _u32, _vp], 1),
+    "ssb_dump_compact_range": ([_vp, _vp, _vp, _u32, _i32, _u32, _u32, _vp, _vp, _vp, _vp, _u32, _i32, _vp], 1),
     "ssb_red_probe": ([_vp, _u32, _i32, _i32, _i32, _vp], 1),
     "ssb_neg_sample": ([_vp, _vp, _u32, _u64, _u64, _u32, _vp, _i64, _vp], 1),
     "ssb_sgns_make_pairs": ([_vp, _vp, _i64, _i32, _i32, _u64, _u64, _vp, _vp, _vp, _vp], 1),

@@ -88,6 +88,45 @@ class AdaGradPushMethod:
                                n=cache.n_keys)
 
 
+class PushMethod:
+    """A push method chosen BY NAME: any device-side update rule of ``include/ssb200_rule.cuh`` — the built-in
+    "sgd", "adagrad", "ftrl", or a user's rule loaded with ``ops.rules.Rule.from_source`` — with its
+    hyper-parameters (lr, eps, a, b, c; FTRL: lr = alpha, eps = beta, a = l1, b = l2).
+    ref: PushAccessMethod::apply_push_value, parameter/sparse_access_method.h:36-46 — the user's class there, the
+    user's ``__device__`` struct here. ``PushMethod("adagrad", lr=0.05).apply(table, cache)``."""
+
+    def __init__(self, name: str, **hyper):
+        from .ops import rules
+
+        self.rule = name if isinstance(name, rules.Rule) else rules.Rule.get(name)
+        self.name = self.rule.name
+        self.hyper = dict(hyper)
+        if "lr" not in self.hyper:
+            raise ValueError("PushMethod needs lr=")
+        self.step = 0
+
+    @property
+    def state_words(self) -> int:
+        """Optimizer-state words per weight the table must be created with (``with_state=``)."""
+        return self.rule.state_words
+
+    @property
+    def init_kind(self) -> int:
+        """How the rule wants missing rows created (``init_kind=`` of the table; ops.rules.INIT_*)."""
+        return self.rule.init_kind
+
+    def apply(self, table: ShardedTable, cache: DeviceParamCache):
+        self.step += 1
+        inbox = getattr(table, "inbox", None)
+        if inbox is not None:
+            inbox.push(cache.gslot, cache.grads, n_dev=cache.n_unique, n=cache.n_keys, rule=self.rule, step=self.step,
+                       **self.hyper)
+            cache.grads[:cache.n_keys].zero_()
+        else:
+            table.push_rule(self.rule, cache.gslot, cache.grads, n_dev=cache.n_unique, zero_grads=True, n=cache.n_keys,
+                            step=self.step, **self.hyper)
+
+
 def pull_with_barrier(table: ShardedTable, keys: torch.Tensor, cache: DeviceParamCache):
     """Fetch the rows of ``keys`` (duplicates allowed) into ``cache`` and reset its gradients.
     ref: global_pull_access.h:40-55.  Returns when the kernels are enqueued; stream order is the barrier."""

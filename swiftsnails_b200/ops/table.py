@@ -30,9 +30,11 @@ def round_capacity(rows_expected: int, load_factor: float = 0.5) -> int:
 class DeviceShard:
     """Storage of one shard on one device."""
 
-    def __init__(self, capacity: int, dim: int, device, with_state: bool, alloc=None, with_shadow: bool = False):
+    def __init__(self, capacity: int, dim: int, device, with_state, alloc=None, with_shadow: bool = False):
+        # with_state: False / True (one word per weight: AdaGrad) or the number of optimizer-state words per weight
         assert capacity % _lib.BUCKET == 0
         self.capacity, self.dim, self.device = int(capacity), int(dim), device
+        self.state_words = int(with_state)
         if alloc is None:
             def alloc(shape, dtype):
                 return torch.empty(shape, dtype=dtype, device=device)
@@ -40,8 +42,8 @@ class DeviceShard:
         self.keys.fill_(-1)  # 0xFFFFFFFF = empty
         self.rows = alloc((capacity, dim), torch.float32)
         self.state = None
-        if with_state:
-            self.state = alloc((capacity, dim), torch.float32)
+        if self.state_words:
+            self.state = alloc((capacity, self.state_words * dim), torch.float32)      # [cap][words][dim]
             self.state.zero_()
         # optional bf16 mirror of the rows (read by bf16-only pulls: half the row bytes)
         self.shadow = alloc((capacity, dim), torch.bfloat16) if with_shadow else None
@@ -63,7 +65,7 @@ class ShardedTable:
     Use :meth:`local` for single-process tables (1..16 shards on one GPU)."""
 
     def __init__(self, hashfrag: HashFrag, capacity: int, dim: int, shard_ptrs, device, seed=0x5EED,
-                 init_scale=None, owned=None, rank=0):
+                 init_scale=None, owned=None, rank=0, state_words=None, init_kind=0):
         if hashfrag.num_nodes != len(shard_ptrs):
             raise ValueError("hashfrag has %d nodes but %d shards given" % (hashfrag.num_nodes, len(shard_ptrs)))
         if len(shard_ptrs) > _lib.MAX_SHARDS:
@@ -87,8 +89,14 @@ class ShardedTable:
         v.num_shards = self.num_shards
         v.seed = self.seed
         v.init_scale = self.init_scale
-        self.view = v
         self.has_state = all(p[2] for p in shard_ptrs)
+        # optimizer-state words per weight ([cap][words][dim]); peers must have allocated the same
+        self.state_words = int(state_words if state_words is not None else
+                               (self.owned[0].state_words if self.owned else (1 if self.has_state else 0)))
+        self.init_kind = int(init_kind)             # ops.rules.INIT_*: how a pull creates a missing row
+        v.state_words = max(self.state_words, 1)
+        v.init_kind = self.init_kind
+        self.view = v
         self.has_shadow = all(len(p) > 3 and p[3] for p in shard_ptrs)
         self.stats = torch.zeros(4, dtype=torch.int32, device=device)  # [inserts, misses/full, -, -]
         # (base ptr, total 256-byte rows, rows per shard segment, first mirror row in a segment) when the
@@ -171,6 +179,17 @@ class ShardedTable:
         _lib.call("ssb_push_adagrad", self._view_ref(), gslot.data_ptr(), grads.data_ptr(), n, _lib.ptr(n_dev),
                   float(lr), float(eps), 1 if zero_grads else 0, _lib.stream_ptr())
 
+    def push_rule(self, rule, gslot, grads, n_dev=None, zero_grads=True, n=None, only_shard=-1, **hyper):
+        """Push with a named device-side update rule (ops.rules / include/ssb200_rule.cuh): ``rule`` is a name
+        ("sgd", "adagrad", "ftrl", or one loaded with ``Rule.from_source``) or a ``Rule``; ``hyper`` = lr, eps, a, b,
+        c, step. ref: PushAccessMethod::apply_push_value, sparse_access_method.h:36-46."""
+        from . import rules
+
+        r = rule if isinstance(rule, rules.Rule) else rules.Rule.get(rule)
+        if r.state_words > self.state_words or (r.state_words and not self.has_state):
+            raise ValueError("rule %r needs with_state=%d, the table has %d" % (r.name, r.state_words, self.state_words))
+        r.push(self, gslot, grads, r.hyper(**hyper), n_dev=n_dev, zero_grads=zero_grads, n=n, only_shard=only_shard)
+
     # -- dump / load ---------------------------------------------------------------------------
     def dump_shard(self, shard: DeviceShard, with_rows=True):
         """Compact the live entries of an owned shard -> (keys uint32 np, rows float32 np)."""
@@ -195,19 +214,20 @@ class ShardedTable:
         row to the same index; device and host staging are sized by ``max_bytes``, not by the shard (config 4
         is 6.4 GB of rows + 6.4 GB of state per shard)."""
         want_state = bool(with_state) and shard.state is not None
-        per_slot = 4 + shard.dim * 4 * (2 if want_state else 1)
+        sdim = shard.dim * max(shard.state_words, 1)           # floats of optimizer state per entry
+        per_slot = 4 + shard.dim * 4 + (sdim * 4 if want_state else 0)
         chunk = max(_lib.BUCKET, (int(max_bytes) // per_slot) // _lib.BUCKET * _lib.BUCKET)
         chunk = min(chunk, shard.capacity)
         dev = shard.device
         n_live = torch.zeros(1, dtype=torch.int32, device=dev)
         out_keys = torch.empty(chunk, dtype=torch.int32, device=dev)
         out_rows = torch.empty((chunk, shard.dim), dtype=torch.float32, device=dev)
-        out_state = torch.empty((chunk, shard.dim), dtype=torch.float32, device=dev) if want_state else None
+        out_state = torch.empty((chunk, sdim), dtype=torch.float32, device=dev) if want_state else None
         for lo in range(0, shard.capacity, chunk):
             hi = min(lo + chunk, shard.capacity)
             _lib.call("ssb_dump_compact_range", shard.keys.data_ptr(), shard.rows.data_ptr(),
                       shard.state.data_ptr() if want_state else None, shard.capacity, shard.dim, lo, hi,
-                      out_keys.data_ptr(), out_rows.data_ptr(), _lib.ptr(out_state), n_live.data_ptr(), chunk,
+                      out_keys.data_ptr(), out_rows.data_ptr(), _lib.ptr(out_state), n_live.data_ptr(), chunk, sdim,
                       _lib.stream_ptr())
             n = int(n_live.item())
             if n == 0:
@@ -216,8 +236,12 @@ class ShardedTable:
                    out_state[:n].cpu().numpy() if want_state else None)
 
     def load(self, keys, rows, state=None):
-        """Insert (key,row[,state]) entries (checkpoint resume; not in the reference)."""
+        """Insert (key,row[,state]) entries (checkpoint resume; not in the reference). ``state`` is
+        [n, state_words * dim]."""
         check_cuda(keys, rows)
+        if state is not None and state.numel() != keys.numel() * self.dim * max(self.state_words, 1):
+            raise ValueError("state has %d floats per entry, the table keeps %d"
+                             % (state.numel() // max(keys.numel(), 1), self.dim * max(self.state_words, 1)))
         _lib.call("ssb_table_load", self._view_ref(), keys.data_ptr(), rows.data_ptr(), _lib.ptr(state),
                   keys.numel(), self.stats.data_ptr(), _lib.stream_ptr())
 

@@ -26,14 +26,14 @@ def shard_layout(capacity, dim, with_state, with_shadow=False):
     rows_off = (keys_bytes + unit - 1) // unit * unit
     rows_bytes = capacity * pitch
     state_off = rows_off + rows_bytes
-    shadow_off = state_off + (rows_bytes if with_state else 0)
+    shadow_off = state_off + rows_bytes * int(with_state)       # with_state = optimizer-state words per weight (True = 1)
     total = shadow_off + (rows_bytes // 2 if with_shadow else 0)
     return {"keys_off": 0, "rows_off": rows_off, "state_off": state_off if with_state else None,
             "shadow_off": shadow_off if with_shadow else None, "total": total, "pitch": pitch}
 
 
 def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, frag_num=1024, seed=0x5EED,
-               load_factor=0.5, force_peer=False, with_shadow=False):
+               load_factor=0.5, force_peer=False, with_shadow=False, init_kind=0):
     import torch.distributed as dist
 
     world = dist.get_world_size() if dist.is_initialized() else 1
@@ -43,7 +43,7 @@ def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, f
     if world == 1 and not force_peer:
         shard = DeviceShard(capacity, dim, device, with_state, with_shadow=with_shadow)
         return ShardedTable(hf, capacity, dim, [shard.ptrs()], device, seed=seed, init_scale=init_scale,
-                            owned=[shard], rank=0)
+                            owned=[shard], rank=0, init_kind=init_kind)
     lay = shard_layout(capacity, dim, with_state, with_shadow)
     pm = PeerMemory(lay["total"], device, align_to=lay["pitch"])
     seg = pm.local_tensor()
@@ -71,7 +71,7 @@ def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, f
         ptrs.append((b + lay["keys_off"], b + lay["rows_off"], (b + lay["state_off"]) if with_state else 0,
                      (b + lay["shadow_off"]) if with_shadow else 0))
     table = ShardedTable(hf, capacity, dim, ptrs, device, seed=seed, init_scale=init_scale, owned=[shard],
-                         rank=rank)
+                         rank=rank, init_kind=init_kind)
     table.peer_memory = pm
     table.layout = lay
     if with_shadow and dim == 128 and pm.stride % 256 == 0 and lay["shadow_off"] % 256 == 0:
@@ -135,7 +135,7 @@ class Inbox:
         self.flags_l = seg[flags_off:flags_off + 4 * self.world].view(torch.int32)
         shard = table.owned[0]
         self.local = ShardedTable(HashFrag(1, 1), table.capacity, D, [shard.ptrs()], device, seed=table.seed,
-                                  init_scale=table.init_scale, owned=[shard])
+                                  init_scale=table.init_scale, owned=[shard], init_kind=table.init_kind)
         self.overflow = torch.zeros(1, dtype=torch.int32, device=device)
         self.err = torch.zeros(1, dtype=torch.int32, device=device)         # a hand-off wait ran out (a sender never showed up)
         self.cursor = torch.zeros(16, dtype=torch.int32, device=device)     # rows claimed per owner this step
@@ -146,7 +146,9 @@ class Inbox:
         torch.cuda.synchronize(device)
         dist.barrier()
 
-    def push(self, gslot, grads, lr, eps=1e-8, adagrad=True, n_dev=None, n=None):
+    def push(self, gslot, grads, lr, eps=1e-8, adagrad=True, n_dev=None, n=None, rule=None, **hyper):
+        """``rule``: a named device-side update rule (ops.rules) instead of the built-in SGD / AdaGrad: the send
+        kernel then only ships, this rank's own rows and the inbox are applied by the rule's own entry points."""
         import torch.distributed as dist
 
         C = self._C
@@ -156,16 +158,26 @@ class Inbox:
         self.step += 1
         sp = _lib.stream_ptr()
         view = C.byref(self.views[par])
+        hy = None
+        if rule is not None:
+            from ..ops import rules as _rules
+
+            rule = rule if isinstance(rule, _rules.Rule) else _rules.Rule.get(rule)
+            hy = rule.hyper(lr=lr, eps=eps, **hyper)
         _lib.call("ssb_push_send2", self.table._view_ref(), view, gslot.data_ptr(), grads.data_ptr(), n,
-                  _lib.ptr(n_dev), self.rank, float(lr), float(eps), 1 if adagrad else 0, 1 if self.bf16_rows else 0,
-                  self.overflow.data_ptr(), self.cursor.data_ptr(), sp)
+                  _lib.ptr(n_dev), self.rank, float(lr), float(eps), -1 if rule is not None else (1 if adagrad else 0),
+                  1 if self.bf16_rows else 0, self.overflow.data_ptr(), self.cursor.data_ptr(), sp)
+        if rule is not None:         # my own rows (the rest travels)
+            rule.push(self.table, gslot, grads, hy, n_dev=n_dev, zero_grads=False, n=n, only_shard=self.rank)
         if self.barrier == "flags":
             _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), self.step, sp)
             _lib.call("ssb_flags_wait2", self.flags_l.data_ptr(), self.world, self.step, 0, self.err.data_ptr(), sp)
         else:
             _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), 0, sp)
             dist.all_reduce(self.token)      # every rank's shipment has landed in my inbox
-        if self.bf16_rows:
+        if self.bf16_rows and rule is not None:
+            rule.push_bf16_seg(self.local, self.slots_l[par], self.rows_l[par], self.seg_rows, self.count_l[par], self.world, hy)
+        elif self.bf16_rows:
             _lib.call("ssb_push_bf16_seg", self.local._view_ref(), self.slots_l[par].data_ptr(), self.rows_l[par].data_ptr(),
                       self.seg_rows, self.world, self.count_l[par].data_ptr(), float(lr), float(eps), 1 if adagrad else 0, sp)
         else:
@@ -174,7 +186,9 @@ class Inbox:
                 if r == self.rank:
                     continue                 # own rows were applied directly by the send kernel
                 sl, rw, cn = self.slots_l[par][r * S:(r + 1) * S], self.rows_l[par][r * S:(r + 1) * S], self.count_l[par][r:r + 1]
-                if adagrad:
+                if rule is not None:
+                    rule.push(self.local, sl, rw, hy, n_dev=cn, zero_grads=False, n=S)
+                elif adagrad:
                     self.local.push_adagrad(sl, rw, lr, eps, n_dev=cn, zero_grads=False, n=S)
                 else:
                     self.local.push_sgd(sl, rw, lr, n_dev=cn, zero_grads=False, n=S)

@@ -120,6 +120,17 @@ def adagrad_ref(w, acc, g, lr, eps):
     return w, acc
 
 
+def ftrl_ref(w, z, n, g, alpha, beta, l1, l2):
+    """One FTRL-proximal step (McMahan et al. 2013) on float64 numpy arrays; returns (w, z, n)."""
+    import numpy as np
+
+    n_new = n + g * g
+    sigma = (np.sqrt(n_new) - np.sqrt(n)) / alpha
+    z_new = z + g - sigma * w
+    w_new = np.where(np.abs(z_new) <= l1, 0.0, -(z_new - np.sign(z_new) * l1) / ((beta + np.sqrt(n_new)) / alpha + l2))
+    return w_new, z_new, n_new
+
+
 def sgns_block_ref(params, inv_in, inv_out, neg_idx, sent_len, window, seed, offset, neg_k, tile=128, halo=8,
                    n_neg=16):
     """fp32 PyTorch reference of the block-formulation SGNS step (csrc/kernels/sgns_tc.cu):

@@ -134,6 +134,41 @@ def main():
         assert torch.allclose(w2, wo, rtol=1e-4, atol=1e-5), ("inbox variant differs", kw)
         assert int(ib2.overflow.item()) == 0
 
+    # ---- 2c. a named device-side rule over the ranks: FTRL (two state words, rows created as zeros) through
+    #          framework.PushMethod, bf16 inbox; keys disjoint between ranks, gradients exact in bf16 -> exact oracle
+    from swiftsnails_b200.framework import DeviceParamCache, PushMethod, pull_with_barrier, push_with_barrier
+    from swiftsnails_b200.utils.reference import ftrl_ref
+
+    dist.barrier()
+    m = PushMethod("ftrl", lr=0.1, eps=1.0, a=0.02, b=0.0)
+    tf = make_table(20_000, dim, dev, with_state=m.state_words, init_kind=m.init_kind, frag_num=64, with_shadow=True)
+    attach_inbox(tf, 40_000, bf16_rows=True)
+    kf = np.unique(np.random.default_rng(300 + rank).integers(0, 2 ** 30, 8_000, dtype=np.int64).astype(np.uint32)) * world + rank
+    cache_f = DeviceParamCache(len(kf), dim, dev)
+    wf = np.zeros((len(kf), dim)); zf = np.zeros_like(wf); nf = np.zeros_like(wf)
+    rngf = np.random.default_rng(400 + rank)
+    for it in range(3):
+        pull_with_barrier(tf, u32_tensor(kf, dev), cache_f)
+        nu = int(cache_f.n_unique.item())
+        assert nu == len(kf)
+        uq_np = to_u32_numpy(cache_f.unique[:nu])
+        order = np.argsort(uq_np)                        # oracle rows are kept in sorted-key order
+        gq = rngf.integers(-8, 9, (nu, dim)).astype(np.float32) / 64.0
+        g_dev = torch.zeros(nu, dim, device=dev)
+        g_dev[torch.from_numpy(order).to(dev)] = torch.from_numpy(gq).to(dev)
+        cache_f.grads[:nu] = g_dev
+        push_with_barrier(tf, cache_f, m)
+        wf, zf, nf = ftrl_ref(wf, zf, nf, gq.astype(np.float64), 0.1, 1.0, 0.02, 0.0)
+        torch.cuda.synchronize(); dist.barrier()
+    got_f, gsl_f = tf.pull(u32_tensor(np.sort(kf), dev), insert=False)
+    assert np.allclose(got_f.cpu().numpy(), wf, rtol=3e-4, atol=3e-6), "FTRL over the inbox differs from the oracle"
+    assert 0 < int((to_u32_numpy(gsl_f) // tf.capacity != rank).sum()) < len(kf)      # some rows really travelled
+    bf_f = torch.empty(len(kf), dim, dtype=torch.bfloat16, device=dev)
+    tf.pull(u32_tensor(np.sort(kf), dev), rows_bf16=bf_f, want_fp32=False, insert=False)
+    assert torch.equal(bf_f, got_f.to(torch.bfloat16)), "mirror != bf16(row) after the rule's inbox apply"
+    assert int(tf.inbox.overflow.item()) == 0 and int(tf.inbox.err.item()) == 0
+    out["named_rule_ftrl_ok"] = True
+
     # ---- 3. NVLink copy probe (kernel ld/st on a peer mapping), timed on the device
     pm = table.peer_memory
     nbytes = min(pm.stride, 256 << 20) // 16 * 16

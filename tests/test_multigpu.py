@@ -31,4 +31,5 @@ def test_two_rank_peer_table(native_built):
     assert line, p.stdout[-2000:]
     res = json.loads(line[0][len("MGPU_RESULT "):])
     assert res["pull_ok"] and res["push_ok"] and res["slot_cache_ok"] and res["p2p_read_gbs"] > 50
+    assert res["inbox_ok"] and res["named_rule_ftrl_ok"] and res["fused_pull_ok"]
     print(res)
