@@ -215,6 +215,19 @@ int ssb_sgns_tiles(const float *params, float *grads, int32_t dim, const uint32_
 int ssb_lr_fwd_bwd(const float *params, float *grads, const uint32_t *inv, const float *x,
                    const float *labels, int64_t n_ex, int32_t n_feat, float *loss_out,
                    void *stream);
+/* K6 fused: one sparse-LR training step (resolve keys -> gather each touched weight once -> forward / backward ->
+ * apply the update rule once per touched key) as ONE persistent cooperative kernel; see csrc/kernels/lr.cu.
+ * view->dim must be 1. keys [n_ex][n_feat] (SSB_EMPTY_KEY = empty position), x [n_ex][n_feat] or NULL (ones),
+ * labels [n_ex]. Worker-side scratch, allocated once: slot_of[slot_of_size] (filled with SSB_INVALID_SLOT; NULL =
+ * probe every key), entries[num_shards * capacity] of 16 bytes (zeroed), inst_slot[n_feat * n_ex],
+ * touched[max_touched], counters[4] (out: [0] touched slots, [2] touched-list overflow, [3] keys without a slot —
+ * both must stay 0). step: non-zero, different from the previous call's. rule_id: 0 SGD, 1 AdaGrad, 2 FTRL; hyper
+ * points to an ssb::rule::Hyper {lr, eps, a, b, c, step}. blocks_per_sm: 0 = as many as fit.
+ * ref: core/framework/SwiftWorker.h:19-57 (the worker loop), parameter/sparse_access_method.h:33-46. */
+int ssb_lr_fused_step(const SsbTableView *view, const uint32_t *keys, const float *x, const float *labels, int64_t n_ex,
+                      int32_t n_feat, uint32_t *slot_of, uint64_t slot_of_size, void *entries, uint32_t *inst_slot,
+                      uint32_t *touched, uint32_t max_touched, uint32_t *counters, uint32_t step, float *loss_out,
+                      int32_t rule_id, const void *hyper, int32_t blocks_per_sm, void *stream);
 
 /* ---- K5 on tensor cores (tcgen05 / TMEM / TMA gather4), dim == 128 only ---------------------
  * One tile = 128 consecutive centre tokens against their 144 context rows + 16 shared negatives.

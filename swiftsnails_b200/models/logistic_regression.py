@@ -28,6 +28,10 @@ class LRConfig:
     lr: float = 0.05
     adagrad_eps: float = 1e-8
     seed: int = 1
+    optimizer: str = "adagrad"      # update rule by name (include/ssb200_rule.cuh): sgd | adagrad | ftrl
+    l1: float = 0.0                 # FTRL only
+    l2: float = 0.0
+    fused: bool = True              # one cooperative kernel per step (K6 fused) instead of dedup -> pull -> fwd/bwd -> push
 
     @property
     def n_feat(self):
@@ -63,8 +67,14 @@ def criteo_like_batch(cfg: LRConfig, n_examples: int, seed: int = 0):
 
 class LRWorker:
     def __init__(self, cfg: LRConfig, table: ShardedTable, device):
-        assert table.dim == 1 and table.has_state
+        assert table.dim == 1 and (table.has_state or cfg.optimizer == "sgd")
         self.cfg, self.table, self.device = cfg, table, device
+        self.loss = torch.zeros(2, dtype=torch.float32, device=device)
+        self.fused = None
+        if cfg.fused:
+            self.fused = lr_ops.FusedLRState(table, cfg.batch_size, cfg.n_feat, cfg.feature_bits, device)
+            self.n_unique = self.fused.counters[0:1]
+            return
         n = cfg.batch_size * cfg.n_feat
         i32 = dict(dtype=torch.int32, device=device)
         self.unique = torch.empty(n, **i32)
@@ -73,13 +83,20 @@ class LRWorker:
         self.gslot = torch.empty(n, **i32)
         self.params = torch.empty((n, 1), dtype=torch.float32, device=device)
         self.grads = torch.zeros((n, 1), dtype=torch.float32, device=device)
-        self.loss = torch.zeros(2, dtype=torch.float32, device=device)
         self.dedup = Deduper(n, device)
         self.n = n
 
     def step(self, keys: torch.Tensor, vals: torch.Tensor, labels: torch.Tensor):
         """keys int32 [B, n_feat] (uint32 bits), vals float32 [B, n_feat], labels float32 [B]."""
         cfg = self.cfg
+        if self.fused is not None:
+            hy = dict(lr=cfg.lr, eps=cfg.adagrad_eps)
+            if cfg.optimizer == "ftrl":
+                hy = dict(lr=cfg.lr, eps=1.0, a=cfg.l1, b=cfg.l2)
+            lr_ops.lr_fused_step(self.fused, keys, vals, labels, self.loss, rule=cfg.optimizer, **hy)
+            return self.loss
+        if cfg.optimizer != "adagrad":
+            raise ValueError("the unfused path implements AdaGrad only; use fused=True for %r" % cfg.optimizer)
         self.dedup(keys.reshape(-1), unique=self.unique, inverse=self.inverse, n_unique=self.n_unique)
         self.table.pull(self.unique, n_dev=self.n_unique, rows_out=self.params, gslot_out=self.gslot,
                         grads_zero=self.grads, n=self.n)
@@ -90,6 +107,13 @@ class LRWorker:
 
     def reset_loss(self):
         self.loss.zero_()
+
+    def health(self):
+        """Counters that must stay zero (read on the host): touched-list overflow, keys that found no slot."""
+        if self.fused is None:
+            return {"table_full": int(self.table.stats[1].item())}
+        c = self.fused.counters.tolist()
+        return {"touched": c[0], "touched_overflow": c[2], "table_full": c[3] + int(self.table.stats[1].item())}
 
     def mean_loss(self):
         s, n = self.loss.tolist()

@@ -9,3 +9,50 @@ def lr_fwd_bwd(params, grads, inv, x, labels, n_feat, loss_out):
     _lib.call("ssb_lr_fwd_bwd", params.data_ptr(), grads.data_ptr(), inv.data_ptr(),
               None if x is None else x.data_ptr(), labels.data_ptr(), n_ex, n_feat, loss_out.data_ptr(),
               _lib.stream_ptr())
+
+
+RULE_IDS = {"sgd": 0, "adagrad": 1, "ftrl": 2}
+
+
+class FusedLRState:
+    """Worker-side scratch of the fused sparse-LR step (csrc/kernels/lr.cu, K6 fused), allocated once:
+    the dense key -> global-slot map (4 bytes per feature id: 1 GB at 2^28), one 16-byte entry per global slot
+    ({tag, weight, gradient sum}: 2 GB at 2^27 slots), the per-instance slot stash and the touched list."""
+
+    def __init__(self, table, batch_size, n_feat, feature_bits, device, max_touched=None):
+        import torch
+
+        self.table, self.device = table, device
+        self.batch_size, self.n_feat = int(batch_size), int(n_feat)
+        i32 = dict(dtype=torch.int32, device=device)
+        self.slot_of = torch.full((1 << feature_bits,), -1, **i32) if feature_bits else None
+        self.entries = torch.zeros((table.num_shards * table.capacity, 4), **i32)
+        self.inst_slot = torch.empty(self.batch_size * self.n_feat, **i32)
+        self.max_touched = int(max_touched or self.batch_size * self.n_feat)
+        self.touched = torch.empty(self.max_touched, **i32)
+        self.counters = torch.zeros(4, **i32)
+        self.step = 0
+
+    def nbytes(self):
+        return sum(t.numel() * 4 for t in (self.slot_of, self.entries, self.inst_slot, self.touched) if t is not None)
+
+
+def lr_fused_step(state: FusedLRState, keys, x, labels, loss_out, rule="adagrad", blocks_per_sm=0, **hyper):
+    """One training step. keys int32 [B, n_feat] (uint32 bits, -1 = empty position), x float32 [B, n_feat] or None,
+    labels float32 [B]; hyper = lr, eps, a, b (ops.rules.Hyper)."""
+    from .rules import Hyper
+    import ctypes as C
+
+    n_ex = labels.numel()
+    if n_ex > state.batch_size or keys.numel() != n_ex * state.n_feat:
+        raise ValueError("batch of %d x %d does not fit the state (%d x %d)" % (n_ex, keys.numel() // max(n_ex, 1),
+                                                                                 state.batch_size, state.n_feat))
+    state.step += 1
+    hy = Hyper(float(hyper.get("lr", 0.05)), float(hyper.get("eps", 1e-8)), float(hyper.get("a", 0.0)),
+               float(hyper.get("b", 0.0)), float(hyper.get("c", 0.0)), state.step)
+    t = state.table
+    _lib.call("ssb_lr_fused_step", t._view_ref(), keys.data_ptr(), None if x is None else x.data_ptr(), labels.data_ptr(),
+              n_ex, state.n_feat, _lib.ptr(state.slot_of), 0 if state.slot_of is None else state.slot_of.numel(),
+              state.entries.data_ptr(), state.inst_slot.data_ptr(), state.touched.data_ptr(), state.max_touched,
+              state.counters.data_ptr(), state.step, loss_out.data_ptr(), RULE_IDS[rule], C.addressof(hy), int(blocks_per_sm),
+              _lib.stream_ptr())
