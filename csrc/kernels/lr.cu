@@ -62,40 +62,35 @@ extern "C" int ssb_lr_fwd_bwd(const float* params, float* grads, const uint32_t*
 // K6 fused: one sparse-LR training step as ONE persistent cooperative kernel.
 //
 // ref: the loop shape is the reference worker's (core/framework/SwiftWorker.h:19-57: collect the minibatch's keys ->
-// pull -> compute -> push, the server applies the update rule per key once per minibatch, parameter/
+// pull -> compute -> push; the server applies the update rule per key once per minibatch, parameter/
 // sparse_access_method.h:33-46). The reference does this with a request/response round trip per server; the unfused
-// path here (dedup -> pull -> lr_fwd_bwd -> push) with four launches and a sort-free hash dedup. This kernel does it
-// in four phases separated by grid-wide barriers, with the TABLE ITSELF as the dedup domain:
+// path here (dedup -> pull -> lr_fwd_bwd -> push) with four launches. This kernel runs four phases separated by
+// grid-wide barriers and dedups through a worker-side ENTRY per feature id:
 //
-//   A  resolve   lane = example, loop over its features: key -> global slot through a dense key->slot map (4 bytes
-//                per feature id, filled on first sight by the ordinary probe / insert protocol); the first lane to
-//                touch a slot in this step (tag exchange, pre-checked with a plain load) appends it to the step's
-//                touched list; the slot is stashed per instance ([feature][example], coalesced).
-//   B  gather    one lane per TOUCHED slot: read the weight from the owner shard (own HBM or a peer's over NVLink,
-//                once per unique key and rank) into the worker-side entry of that slot.
-//   C  compute   lane = example: dot over the stashed slots, sigmoid, log-loss, g = p - y; the per-feature gradient
-//                g * x goes to a block-local shared-memory table of 64-bit fixed-point sums (native integer smem
-//                atomics; features shared by a whole warp — the numeric fields — are warp-reduced first), spilling
-//                to the entry's accumulator in global memory; the block flushes its table at the end of the phase.
-//                Hot features therefore cost one global atomic per block, not one per example.
-//   D  push      one lane per touched slot: take the accumulated gradient (and zero it), apply the update rule
-//                (Rule::apply1 of include/ssb200_rule.cuh: SGD, AdaGrad, FTRL) to the owner's weight and state.
+//   A  resolve   lane = example, loop over its features. One 16-byte entry per feature id {tag, idx, slot}: `slot`
+//                is the feature's global table slot (found once, by the ordinary probe / insert protocol); `tag` is
+//                the last step that touched the feature and `idx` its position in that step's compact arrays. A
+//                lane that finds a stale tag allocates an index and installs (step, idx) with one 64-bit CAS; the
+//                loser of a race takes the winner's idx (its own allocation stays a hole). The idx is stashed per
+//                instance ([feature][example], coalesced). One random 16-byte read per instance, mostly L2 hits.
+//   B  gather    one lane per allocated idx: read the weight from the owner shard (own HBM or a peer's over NVLink —
+//                once per unique key and rank) into wc[idx].
+//   C  compute   lane = example: dot over wc[stash], sigmoid, log-loss, g = p - y; g * x is added to a block-local
+//                shared-memory table of 64-bit fixed-point sums (two native 32-bit smem atomics; a feature the whole
+//                warp shares — the numeric fields — is warp-reduced first), spilling to gc[idx]; the block flushes
+//                its table at the end of the phase. The compact wc / gc arrays (4 bytes per touched key) stay in L2.
+//   D  push      one lane per allocated idx: take gc[idx] (and zero it), apply the update rule (Rule::apply1 of
+//                include/ssb200_rule.cuh: SGD, AdaGrad, FTRL) to the owner's weight and state.
 //
-// Worker-side memory (allocated once, sized for 180 GB of HBM): slot_of[2^feature_bits] (1 GB at 2^28) and one
-// 16-byte entry {tag, w, gacc} per global slot (2 GB at 2^27 slots).
-// The grid is launched cooperatively (all blocks co-resident), so the barriers cannot deadlock; they are bounded.
+// Worker-side memory, allocated once and sized for 180 GB of HBM: 16 bytes per feature id (4 GB at 2^28). Without a
+// dense feature space (entry_count == capacity * shards) the entry index is the global slot and every instance
+// probes the table (slower, general). Chunks of 32 examples are handed out dynamically, so warps finish together.
+// The grid is launched cooperatively (all blocks co-resident): the barriers cannot deadlock, and they are bounded.
 // ================================================================================================================
 #include "table_probe.cuh"
 
 namespace ssb {
 namespace lrf {
-
-struct __align__(16) Entry {
-  uint32_t tag;    // step number of the last step that touched this slot
-  float w;         // the weight as pulled in this step
-  float gacc;      // this worker's gradient sum for the step (zero between steps)
-  uint32_t pad;
-};
 
 struct Args {
   SsbTableView v;
@@ -104,20 +99,22 @@ struct Args {
   const float* labels;       // [n_ex] in {0, 1}
   int64_t n_ex;
   int n_feat;
-  uint32_t* slot_of;         // [slot_of_size] key -> global slot, SSB_INVALID_SLOT = not seen yet; nullptr = always probe
-  uint64_t slot_of_size;
-  Entry* ent;                // [num_shards * capacity]
-  uint32_t* inst_slot;       // [n_feat][n_ex] stash
-  uint32_t* touched;         // [max_touched]
+  uint4* ent;                // [entry_count] {tag, idx, slot, -}; zero tag, slot = SSB_INVALID_SLOT initially
+  uint64_t dense_keys;       // > 0: entries are indexed by key (< dense_keys); 0: by global slot
+  uint32_t* stash;           // [n_feat][n_ex] idx of every instance
+  uint32_t* touched;         // [max_touched] idx -> global slot (SSB_INVALID_SLOT = hole)
+  float* wc;                 // [max_touched] weights of this step
+  float* gc;                 // [max_touched] gradient sums of this step (zero between steps)
   uint32_t max_touched;
-  uint32_t* counters;        // [0] touched count, [1] grid barrier, [2] touched overflow, [3] table full / unresolved
-  uint32_t step;             // != 0, different from the previous step's
+  uint32_t* counters;        // [0] allocated idx, [1] grid barrier, [2] idx overflow, [3] keys without a slot,
+                             // [4] / [5] chunk tickets of phases A / C, [8..12] globaltimer stamps (block 0)
+  uint32_t step;             // != 0, different from every earlier step's
   float* loss_out;           // [2]: sum of log-loss, examples
   rule::Hyper h;
 };
 
 constexpr int kThreads = 256;
-constexpr int kAggBits = 11, kAggSize = 1 << kAggBits;      // block-local gradient table: 2048 x (4 + 8) bytes
+constexpr int kAggBits = 10, kAggSize = 1 << kAggBits;      // block-local gradient table: 1024 x (4 + 4 + 4) bytes
 constexpr float kFixScale = 68719476736.0f;                  // 2^36: |block sum| < 2^27 fits int64 with room
 constexpr uint32_t kAggEmpty = 0xFFFFFFFFu;
 
@@ -125,6 +122,16 @@ __device__ __forceinline__ uint32_t ld_acquire_gpu_u32(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
+}
+__device__ __forceinline__ uint4 ld_entry(const uint4* p) {          // strong load: other warps install tags concurrently
+  uint4 r;
+  asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ float ld_strong_f32(const float* p) {
+  float r;
+  asm volatile("ld.relaxed.gpu.global.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");
+  return r;
 }
 
 // All blocks are co-resident (cooperative launch). `phase` counts the barriers passed so far.
@@ -145,13 +152,16 @@ __device__ __forceinline__ void grid_barrier(uint32_t* bar, uint32_t& phase) {
   __syncthreads();
 }
 
-// key -> global slot for one lane's key; lanes that miss the map go through the warp-cooperative probe one by one.
-__device__ __forceinline__ uint32_t resolve(const Args& a, uint32_t key, bool valid, int lane) {
+__device__ __forceinline__ int64_t next_chunk(uint32_t* ticket, int lane) {
+  uint32_t c = 0;
+  if (lane == 0) c = atomicAdd(ticket, 1u);
+  return (int64_t)__shfl_sync(0xffffffffu, c, 0);
+}
+
+// The slow path of phase A for the lanes in `need`: find (or insert) the key's table slot, one key at a time with
+// the warp-cooperative probe. Returns this lane's global slot (SSB_INVALID_SLOT if the table is full).
+__device__ __forceinline__ uint32_t probe_lanes(const Args& a, uint32_t key, unsigned need, int lane) {
   uint32_t gs = SSB_INVALID_SLOT;
-  const bool mapped = valid && a.slot_of && key < a.slot_of_size;
-  // entries only ever change from INVALID to their final value (other warps of this launch may be writing them)
-  if (mapped) gs = *reinterpret_cast<volatile const uint32_t*>(a.slot_of + key);
-  unsigned need = __ballot_sync(0xffffffffu, valid && gs == SSB_INVALID_SLOT);
   while (need) {
     const int src = __ffs(need) - 1;
     need &= need - 1;
@@ -159,8 +169,9 @@ __device__ __forceinline__ uint32_t resolve(const Args& a, uint32_t key, bool va
     Probe p = probe_insert(a.v, k, true, lane);
     if (p.slot != SSB_INVALID_SLOT && p.is_new) {
       if (lane == 0) {
-        a.v.rows[p.owner][p.slot] = init_of(a.v, k, 0);      // dim 1; the state is zero since allocation
-        if (a.v.shadow[p.owner]) reinterpret_cast<__nv_bfloat16*>(a.v.shadow[p.owner])[p.slot] = __float2bfloat16_rn(init_of(a.v, k, 0));
+        const float w0 = init_of(a.v, k, 0);                      // dim 1; the state is zero since allocation
+        a.v.rows[p.owner][p.slot] = w0;
+        if (a.v.shadow[p.owner]) reinterpret_cast<__nv_bfloat16*>(a.v.shadow[p.owner])[p.slot] = __float2bfloat16_rn(w0);
       }
       publish(a.v, p, k, lane);
     }
@@ -168,11 +179,13 @@ __device__ __forceinline__ uint32_t resolve(const Args& a, uint32_t key, bool va
     if (lane == src) {
       gs = g;
       if (g == SSB_INVALID_SLOT) atomicAdd(a.counters + 3, 1u);
-      else if (mapped) a.slot_of[key] = g;
     }
   }
   return gs;
 }
+
+constexpr int kGroup = 4;       // features handled together in phase A: kGroup independent entry reads in flight per lane
+constexpr int kReserve = 64;    // compact indices a warp reserves at a time (<= 64: retired with two stores per lane)
 
 template <class Rule>
 __global__ void __launch_bounds__(kThreads)
@@ -185,60 +198,136 @@ lr_fused_step_kernel(const __grid_constant__ Args a) {
   const int F = a.n_feat;
   const int64_t n_ex = a.n_ex;
   const int64_t chunks = (n_ex + 31) / 32;
-  const int64_t gwarp = (int64_t)blockIdx.x * (kThreads / 32) + warp, nwarps = (int64_t)gridDim.x * (kThreads / 32);
   uint32_t phase = 0;
+  auto stamp = [&](int i) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      uint32_t t;
+      asm volatile("mov.u32 %0, %%globaltimer_lo;" : "=r"(t));
+      a.counters[8 + i] = t;
+    }
+  };
+  stamp(0);
   for (int i = threadIdx.x; i < kAggSize; i += kThreads) { agg_key[i] = kAggEmpty; agg_lo[i] = 0u; agg_hi[i] = 0u; }
 
-  // ---- A: resolve + touched list ------------------------------------------------------------------------------
-  for (int64_t c = gwarp; c < chunks; c += nwarps) {
+  // ---- A: resolve + compact index -----------------------------------------------------------------------------
+  // Compact indices come from a warp-private reservation (kReserve at a time from the one global counter: one
+  // global atomic per kReserve new keys instead of one per group); what a warp leaves unused becomes holes.
+  uint32_t res_base = 0, res_left = 0;          // warp-uniform
+  const int n_groups = (F + kGroup - 1) / kGroup;
+  for (int64_t c = next_chunk(a.counters + 4, lane); c < chunks; c = next_chunk(a.counters + 4, lane)) {
     const int64_t e = c * 32 + lane;
     const bool live = e < n_ex;
     const uint32_t* ke = a.keys + (live ? e : 0) * F;
+    // warps start at different feature groups, so the features every example has (the numeric fields) are not hit
+    // by all warps at the same moment: the first warp installs the tag, the others then see it with a plain load
+    const int rot = (int)(c % n_groups);
 #pragma unroll 1
-    for (int f = 0; f < F; ++f) {
-      const uint32_t key = live ? __ldg(ke + f) : SSB_EMPTY_KEY;
-      const bool valid = live && key < SSB_LOCKED_KEY;
-      const uint32_t gs = resolve(a, key, valid, lane);
-      bool first = false;
-      if (gs != SSB_INVALID_SLOT) {
-        Entry* en = a.ent + gs;
-        if (*reinterpret_cast<volatile uint32_t*>(&en->tag) != a.step) first = atomicExch(&en->tag, a.step) != a.step;
+    for (int gi = 0; gi < n_groups; ++gi) {
+      const int f0 = ((gi + rot) % n_groups) * kGroup;
+      uint32_t key[kGroup], ei[kGroup];
+      uint4 E[kGroup];
+      bool valid[kGroup];
+#pragma unroll
+      for (int g = 0; g < kGroup; ++g) {
+        key[g] = (live && f0 + g < F) ? __ldg(ke + f0 + g) : SSB_EMPTY_KEY;
+        valid[g] = key[g] < SSB_LOCKED_KEY;
       }
-      const unsigned fm = __ballot_sync(0xffffffffu, first);
-      if (fm) {
-        uint32_t base = 0;
-        if (lane == __ffs(fm) - 1) base = atomicAdd(a.counters + 0, (uint32_t)__popc(fm));
-        base = __shfl_sync(0xffffffffu, base, __ffs(fm) - 1);
-        if (first) {
-          const uint32_t pos = base + __popc(fm & ((1u << lane) - 1));
-          if (pos < a.max_touched) a.touched[pos] = gs; else atomicAdd(a.counters + 2, 1u);
+      if (a.dense_keys) {
+#pragma unroll
+        for (int g = 0; g < kGroup; ++g) {
+          if (valid[g] && key[g] >= a.dense_keys) { valid[g] = false; atomicAdd(a.counters + 3, 1u); }   // outside the declared space
+          ei[g] = key[g];
+        }
+      } else {
+#pragma unroll
+        for (int g = 0; g < kGroup; ++g) {
+          ei[g] = probe_lanes(a, key[g], __ballot_sync(0xffffffffu, valid[g]), lane);
+          valid[g] = valid[g] && ei[g] != SSB_INVALID_SLOT;
         }
       }
-      if (live) a.inst_slot[(size_t)f * n_ex + e] = gs;
+#pragma unroll
+      for (int g = 0; g < kGroup; ++g) E[g] = valid[g] ? ld_entry(a.ent + ei[g]) : make_uint4(a.step, SSB_INVALID_SLOT, 0u, 0u);
+#pragma unroll
+      for (int g = 0; g < kGroup; ++g) {
+        uint32_t gs = a.dense_keys ? E[g].z : ei[g];
+        uint32_t idx = E[g].y;
+        if (a.dense_keys) {            // first sight of this feature id: find / insert its table slot, remember it
+          const unsigned need = __ballot_sync(0xffffffffu, valid[g] && gs == SSB_INVALID_SLOT);
+          if (need) {
+            const uint32_t got = probe_lanes(a, key[g], need, lane);
+            if (valid[g] && gs == SSB_INVALID_SLOT) {
+              gs = got;
+              if (gs != SSB_INVALID_SLOT) reinterpret_cast<uint32_t*>(a.ent + ei[g])[2] = gs; else valid[g] = false;
+            }
+          }
+        }
+        const bool stale = valid[g] && E[g].x != a.step;
+        const unsigned sm = __ballot_sync(0xffffffffu, stale);
+        if (sm) {
+          // one lane per distinct entry among the stale lanes does the install; its peers take its result
+          unsigned peers = 0;
+          if (stale) peers = __match_any_sync(sm, ei[g]);
+          const bool leader = stale && (__ffs(peers) - 1 == lane);
+          const unsigned lm = __ballot_sync(0xffffffffu, leader);
+          const uint32_t cnt = (uint32_t)__popc(lm);
+          if (cnt > res_left) {                      // warp-uniform: retire the rest of the reservation, take a new one
+            if ((uint32_t)lane < res_left && res_base + lane < a.max_touched) a.touched[res_base + lane] = SSB_INVALID_SLOT;
+            if (res_left > 32 && (uint32_t)lane + 32 < res_left && res_base + lane + 32 < a.max_touched)
+              a.touched[res_base + lane + 32] = SSB_INVALID_SLOT;
+            uint32_t nb = 0;
+            if (lane == 0) nb = atomicAdd(a.counters + 0, (uint32_t)kReserve);
+            res_base = __shfl_sync(0xffffffffu, nb, 0);
+            res_left = kReserve;
+          }
+          if (leader) {
+            const uint32_t my = res_base + __popc(lm & ((1u << lane) - 1));
+            if (my < a.max_touched) {
+              const unsigned long long expect = ((unsigned long long)E[g].y << 32) | E[g].x;
+              const unsigned long long want = ((unsigned long long)my << 32) | a.step;
+              const unsigned long long old = atomicCAS(reinterpret_cast<unsigned long long*>(a.ent + ei[g]), expect, want);
+              if (old == expect) { idx = my; a.touched[my] = gs; }
+              else { idx = (uint32_t)(old >> 32); a.touched[my] = SSB_INVALID_SLOT; }     // another warp was first: a hole
+            } else {
+              atomicAdd(a.counters + 2, 1u);
+              idx = SSB_INVALID_SLOT;
+            }
+          }
+          res_base += cnt;
+          res_left -= cnt;
+          if (stale) idx = __shfl_sync(sm, idx, __ffs(peers) - 1);
+        }
+        if (live && f0 + g < F) a.stash[(size_t)(f0 + g) * n_ex + e] = valid[g] ? idx : SSB_INVALID_SLOT;
+      }
     }
   }
+  if ((uint32_t)lane < res_left && res_base + lane < a.max_touched) a.touched[res_base + lane] = SSB_INVALID_SLOT;
+  if (res_left > 32 && (uint32_t)lane + 32 < res_left && res_base + lane + 32 < a.max_touched)
+    a.touched[res_base + lane + 32] = SSB_INVALID_SLOT;
   grid_barrier(a.counters + 1, phase);
+  stamp(1);
 
-  // ---- B: one weight read per touched slot ---------------------------------------------------------------------
-  const uint32_t n_touched = min(*reinterpret_cast<volatile uint32_t*>(a.counters + 0), a.max_touched);
-  for (uint32_t i = blockIdx.x * kThreads + threadIdx.x; i < n_touched; i += gridDim.x * kThreads) {
+  // ---- B: one weight read per touched key ----------------------------------------------------------------------
+  const uint32_t n_idx = min(*reinterpret_cast<volatile uint32_t*>(a.counters + 0), a.max_touched);
+  for (uint32_t i = blockIdx.x * kThreads + threadIdx.x; i < n_idx; i += gridDim.x * kThreads) {
     const uint32_t gs = a.touched[i];
+    if (gs == SSB_INVALID_SLOT) continue;
     const uint32_t o = gs / a.v.capacity, s = gs - o * a.v.capacity;
-    a.ent[gs].w = ld_row_f1(a.v.rows[o] + s);
+    a.wc[i] = ld_row_f1(a.v.rows[o] + s);
   }
   grid_barrier(a.counters + 1, phase);
+  stamp(2);
 
   // ---- C: forward / backward -----------------------------------------------------------------------------------
   float loss_acc = 0.f;
-  for (int64_t c = gwarp; c < chunks; c += nwarps) {
+  for (int64_t c = next_chunk(a.counters + 5, lane); c < chunks; c = next_chunk(a.counters + 5, lane)) {
     const int64_t e = c * 32 + lane;
     const bool live = e < n_ex;
     const float* xe = a.x ? a.x + (live ? e : 0) * F : nullptr;
     float z = 0.f;
 #pragma unroll 4
     for (int f = 0; f < F; ++f) {
-      const uint32_t gs = live ? a.inst_slot[(size_t)f * n_ex + e] : SSB_INVALID_SLOT;
-      if (gs != SSB_INVALID_SLOT) z += *reinterpret_cast<volatile float*>(&a.ent[gs].w) * (xe ? __ldg(xe + f) : 1.0f);
+      const uint32_t idx = live ? a.stash[(size_t)f * n_ex + e] : SSB_INVALID_SLOT;
+      if (idx != SSB_INVALID_SLOT) z += ld_strong_f32(a.wc + idx) * (xe ? __ldg(xe + f) : 1.0f);
     }
     float g = 0.f;
     if (live) {
@@ -246,14 +335,14 @@ lr_fused_step_kernel(const __grid_constant__ Args a) {
       g = fast_sigmoid(z) - y;
       loss_acc += y * neg_log_sigmoid(z) + (1.f - y) * neg_log_sigmoid(-z);
     }
-#pragma unroll 1
+#pragma unroll 2
     for (int f = 0; f < F; ++f) {
-      const uint32_t gs = live ? a.inst_slot[(size_t)f * n_ex + e] : SSB_INVALID_SLOT;
-      float cgrad = (gs != SSB_INVALID_SLOT) ? g * (xe ? __ldg(xe + f) : 1.0f) : 0.f;
-      uint32_t tgt = gs;
+      const uint32_t idx = live ? a.stash[(size_t)f * n_ex + e] : SSB_INVALID_SLOT;
+      float cgrad = (idx != SSB_INVALID_SLOT) ? g * (xe ? __ldg(xe + f) : 1.0f) : 0.f;
+      uint32_t tgt = idx;
       // a feature the whole warp shares (a numeric field): one add for the warp
-      const uint32_t gs0 = __shfl_sync(0xffffffffu, gs, 0);
-      if (__all_sync(0xffffffffu, gs == gs0)) {
+      const uint32_t idx0 = __shfl_sync(0xffffffffu, idx, 0);
+      if (__all_sync(0xffffffffu, idx == idx0)) {
         cgrad = warp_sum(cgrad);
         if (lane != 0) tgt = SSB_INVALID_SLOT;
       }
@@ -267,8 +356,9 @@ lr_fused_step_kernel(const __grid_constant__ Args a) {
         const uint32_t old = atomicAdd(&agg_lo[hsh], dl);
         const uint32_t up = dh + ((uint32_t)(old + dl) < old ? 1u : 0u);        // carry out of the low word
         if (up) atomicAdd(&agg_hi[hsh], up);
-      } else
-        atomicAdd(&a.ent[tgt].gacc, cgrad);
+      } else {
+        atomicAdd(a.gc + tgt, cgrad);
+      }
     }
   }
   __syncthreads();
@@ -277,7 +367,7 @@ lr_fused_step_kernel(const __grid_constant__ Args a) {
     if (k != kAggEmpty) {
       const long long fx = (long long)(((unsigned long long)agg_hi[i] << 32) | (unsigned long long)agg_lo[i]);
       const float vsum = (float)((double)fx * (1.0 / (double)kFixScale));
-      if (vsum != 0.f) atomicAdd(&a.ent[k].gacc, vsum);
+      if (vsum != 0.f) atomicAdd(a.gc + k, vsum);
     }
   }
   loss_acc = warp_sum(loss_acc);
@@ -290,15 +380,16 @@ lr_fused_step_kernel(const __grid_constant__ Args a) {
     if (blockIdx.x == 0) atomicAdd(a.loss_out + 1, (float)n_ex);
   }
   grid_barrier(a.counters + 1, phase);
+  stamp(3);
 
-  // ---- D: push, once per touched slot --------------------------------------------------------------------------
+  // ---- D: push, once per touched key ---------------------------------------------------------------------------
   const int SW = (a.v.state_words > 0 ? a.v.state_words : 1);
-  for (uint32_t i = blockIdx.x * kThreads + threadIdx.x; i < n_touched; i += gridDim.x * kThreads) {
+  for (uint32_t i = blockIdx.x * kThreads + threadIdx.x; i < n_idx; i += gridDim.x * kThreads) {
     const uint32_t gs = a.touched[i];
-    Entry* en = a.ent + gs;
-    const float g = *reinterpret_cast<volatile float*>(&en->gacc);
+    if (gs == SSB_INVALID_SLOT) continue;
+    const float g = ld_strong_f32(a.gc + i);
     if (g == 0.f) continue;
-    en->gacc = 0.f;
+    a.gc[i] = 0.f;
     const uint32_t o = gs / a.v.capacity, s = gs - o * a.v.capacity;
     float* row = a.v.rows[o] + s;
     float* st = (Rule::kStateWords > 0) ? a.v.state[o] + (size_t)s * SW : nullptr;
@@ -310,6 +401,7 @@ lr_fused_step_kernel(const __grid_constant__ Args a) {
       red_add_f1_sys(row, d);
     }
   }
+  stamp(4);        // block 0's own end: the other blocks finish within the same few microseconds
 }
 
 template <class Rule>
@@ -327,7 +419,7 @@ int launch(const Args& a, int blocks_per_sm, cudaStream_t stream) {
   if (blocks_per_sm > 0) blocks = std::min(max_blocks, blocks_per_sm * kNumSMs);
   const int64_t chunks = (a.n_ex + 31) / 32;
   blocks = (int)std::max<int64_t>(1, std::min<int64_t>(blocks, (chunks + kThreads / 32 - 1) / (kThreads / 32)));
-  cudaError_t e = cudaMemsetAsync(a.counters, 0, 4 * sizeof(uint32_t), stream);
+  cudaError_t e = cudaMemsetAsync(a.counters, 0, 8 * sizeof(uint32_t), stream);      // [8..12] are overwritten by the kernel
   if (e != cudaSuccess) return (int)e;
   void* params[] = {(void*)&a};
   e = cudaLaunchCooperativeKernel((const void*)lr_fused_step_kernel<Rule>, dim3(blocks), dim3(kThreads), params, 0, stream);
@@ -337,20 +429,22 @@ int launch(const Args& a, int blocks_per_sm, cudaStream_t stream) {
 }  // namespace lrf
 }  // namespace ssb
 
-// rule_id: 0 SGD, 1 AdaGrad, 2 FTRL (include/ssb200_rule.cuh). counters: 4 x uint32 device scratch (zeroed here):
-// [0] touched slots, [2] touched-list overflow (must stay 0), [3] keys that found no slot (table full; must stay 0).
+// rule_id: 0 SGD, 1 AdaGrad, 2 FTRL (include/ssb200_rule.cuh). counters: 16 x uint32 device scratch ([0..7] zeroed here):
+// [0] allocated compact indices, [2] index overflow (must stay 0), [3] keys without a slot (table full or key outside
+// the declared feature space; must stay 0).
 extern "C" int ssb_lr_fused_step(const SsbTableView* view, const uint32_t* keys, const float* x, const float* labels, int64_t n_ex,
-                                 int32_t n_feat, uint32_t* slot_of, uint64_t slot_of_size, void* entries, uint32_t* inst_slot,
-                                 uint32_t* touched, uint32_t max_touched, uint32_t* counters, uint32_t step, float* loss_out,
+                                 int32_t n_feat, void* entries, uint64_t dense_keys, uint32_t* stash, uint32_t* touched,
+                                 float* wc, float* gc, uint32_t max_touched, uint32_t* counters, uint32_t step, float* loss_out,
                                  int32_t rule_id, const void* hyper, int32_t blocks_per_sm, void* stream) {
-  if (!view || view->dim != 1 || !keys || !labels || n_feat < 1 || !entries || !inst_slot || !touched || !counters || !loss_out ||
-      !hyper || step == 0 || max_touched == 0)
+  if (!view || view->dim != 1 || !keys || !labels || n_feat < 1 || !entries || !stash || !touched || !wc || !gc || !counters ||
+      !loss_out || !hyper || step == 0 || max_touched == 0)
     return (int)cudaErrorInvalidValue;
   if (n_ex <= 0) return 0;
   ssb::lrf::Args a;
-  a.v = *view; a.keys = keys; a.x = x; a.labels = labels; a.n_ex = n_ex; a.n_feat = n_feat; a.slot_of = slot_of;
-  a.slot_of_size = slot_of ? slot_of_size : 0; a.ent = reinterpret_cast<ssb::lrf::Entry*>(entries); a.inst_slot = inst_slot;
-  a.touched = touched; a.max_touched = max_touched; a.counters = counters; a.step = step; a.loss_out = loss_out; a.h = *static_cast<const ssb::rule::Hyper*>(hyper);
+  a.v = *view; a.keys = keys; a.x = x; a.labels = labels; a.n_ex = n_ex; a.n_feat = n_feat;
+  a.ent = reinterpret_cast<uint4*>(entries); a.dense_keys = dense_keys; a.stash = stash; a.touched = touched; a.wc = wc; a.gc = gc;
+  a.max_touched = max_touched; a.counters = counters; a.step = step; a.loss_out = loss_out;
+  a.h = *static_cast<const ssb::rule::Hyper*>(hyper);
   cudaStream_t s = (cudaStream_t)stream;
   switch (rule_id) {
     case 0: return ssb::lrf::launch<ssb::rule::Sgd>(a, blocks_per_sm, s);

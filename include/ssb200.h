@@ -218,15 +218,17 @@ int ssb_lr_fwd_bwd(const float *params, float *grads, const uint32_t *inv, const
 /* K6 fused: one sparse-LR training step (resolve keys -> gather each touched weight once -> forward / backward ->
  * apply the update rule once per touched key) as ONE persistent cooperative kernel; see csrc/kernels/lr.cu.
  * view->dim must be 1. keys [n_ex][n_feat] (SSB_EMPTY_KEY = empty position), x [n_ex][n_feat] or NULL (ones),
- * labels [n_ex]. Worker-side scratch, allocated once: slot_of[slot_of_size] (filled with SSB_INVALID_SLOT; NULL =
- * probe every key), entries[num_shards * capacity] of 16 bytes (zeroed), inst_slot[n_feat * n_ex],
- * touched[max_touched], counters[4] (out: [0] touched slots, [2] touched-list overflow, [3] keys without a slot —
- * both must stay 0). step: non-zero, different from the previous call's. rule_id: 0 SGD, 1 AdaGrad, 2 FTRL; hyper
- * points to an ssb::rule::Hyper {lr, eps, a, b, c, step}. blocks_per_sm: 0 = as many as fit.
+ * labels [n_ex]. Worker-side scratch, allocated once: entries = 16 bytes {tag, idx, slot, -} per feature id
+ * (dense_keys > 0: keys must be < dense_keys) or per global slot (dense_keys == 0: every instance probes the
+ * table), initialised to {0, 0, SSB_INVALID_SLOT, 0}; stash[n_feat * n_ex]; touched / wc / gc [max_touched]
+ * (gc zeroed once; max_touched >= n_ex * n_feat is always enough); counters[16] (out: [0] compact indices used,
+ * [2] index overflow, [3] keys without a slot — both must stay 0; [8..12] globaltimer stamps of the phases).
+ * step: non-zero, different from every earlier call's. rule_id: 0 SGD, 1 AdaGrad, 2 FTRL; hyper points to an
+ * ssb::rule::Hyper {lr, eps, a, b, c, step}. blocks_per_sm: 0 = as many as fit.
  * ref: core/framework/SwiftWorker.h:19-57 (the worker loop), parameter/sparse_access_method.h:33-46. */
 int ssb_lr_fused_step(const SsbTableView *view, const uint32_t *keys, const float *x, const float *labels, int64_t n_ex,
-                      int32_t n_feat, uint32_t *slot_of, uint64_t slot_of_size, void *entries, uint32_t *inst_slot,
-                      uint32_t *touched, uint32_t max_touched, uint32_t *counters, uint32_t step, float *loss_out,
+                      int32_t n_feat, void *entries, uint64_t dense_keys, uint32_t *stash, uint32_t *touched, float *wc,
+                      float *gc, uint32_t max_touched, uint32_t *counters, uint32_t step, float *loss_out,
                       int32_t rule_id, const void *hyper, int32_t blocks_per_sm, void *stream);
 
 /* ---- K5 on tensor cores (tcgen05 / TMEM / TMA gather4), dim == 128 only ---------------------

@@ -101,7 +101,7 @@ _KERNEL_SIGS = {
                                   _vp, _i32, _vp], 1),
     "ssb_dedup_static": ([_vp, _i64, _vp, _vp, _vp, _vp], 2),
     "ssb_lr_fwd_bwd": ([_vp, _vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp], 1),
-    "ssb_lr_fused_step": ([C.POINTER(SsbTableView), _vp, _vp, _vp, _i64, _i32, _vp, _u64, _vp, _vp, _vp, _u32, _vp, _u32, _vp,
+    "ssb_lr_fused_step": ([C.POINTER(SsbTableView), _vp, _vp, _vp, _i64, _i32, _vp, _u64, _vp, _vp, _vp, _vp, _u32, _vp, _u32, _vp,
                            _i32, _vp, _i32, _vp], 1),
     "ssb_dump_compact": ([_vp, _vp, _u32, _i32, _vp, _vp, _vp, _u32, _vp], 1),
     "ssb_table_load": ([C.POINTER(SsbTableView), _vp, _vp, _vp, _i64, _vp, _vp], 1),

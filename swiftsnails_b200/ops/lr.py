@@ -15,9 +15,10 @@ RULE_IDS = {"sgd": 0, "adagrad": 1, "ftrl": 2}
 
 
 class FusedLRState:
-    """Worker-side scratch of the fused sparse-LR step (csrc/kernels/lr.cu, K6 fused), allocated once:
-    the dense key -> global-slot map (4 bytes per feature id: 1 GB at 2^28), one 16-byte entry per global slot
-    ({tag, weight, gradient sum}: 2 GB at 2^27 slots), the per-instance slot stash and the touched list."""
+    """Worker-side scratch of the fused sparse-LR step (csrc/kernels/lr.cu, K6 fused), allocated once: one 16-byte
+    entry {tag, idx, slot} per feature id (``feature_bits`` > 0: 4 GB at 2^28) or per global table slot
+    (``feature_bits`` = 0: any 32-bit key, every instance probes the table), the per-instance index stash and the
+    compact per-step arrays (slot, weight, gradient sum of every touched key)."""
 
     def __init__(self, table, batch_size, n_feat, feature_bits, device, max_touched=None):
         import torch
@@ -25,16 +26,27 @@ class FusedLRState:
         self.table, self.device = table, device
         self.batch_size, self.n_feat = int(batch_size), int(n_feat)
         i32 = dict(dtype=torch.int32, device=device)
-        self.slot_of = torch.full((1 << feature_bits,), -1, **i32) if feature_bits else None
-        self.entries = torch.zeros((table.num_shards * table.capacity, 4), **i32)
-        self.inst_slot = torch.empty(self.batch_size * self.n_feat, **i32)
+        self.dense_keys = (1 << feature_bits) if feature_bits else 0
+        n_ent = self.dense_keys or table.num_shards * table.capacity
+        self.entries = torch.zeros((n_ent, 4), **i32)
+        self.entries[:, 2] = -1                                   # slot not known yet
+        self.stash = torch.empty(self.batch_size * self.n_feat, **i32)
         self.max_touched = int(max_touched or self.batch_size * self.n_feat)
         self.touched = torch.empty(self.max_touched, **i32)
-        self.counters = torch.zeros(4, **i32)
+        self.wc = torch.empty(self.max_touched, dtype=torch.float32, device=device)
+        self.gc = torch.zeros(self.max_touched, dtype=torch.float32, device=device)
+        self.counters = torch.zeros(16, **i32)
         self.step = 0
 
+    def phase_us(self):
+        """Device time of the last step's phases (resolve, gather, compute, push) in microseconds, from the
+        kernel's own globaltimer stamps (block 0)."""
+        t = [x & 0xFFFFFFFF for x in self.counters[8:13].tolist()]
+        d = [((t[i + 1] - t[i]) & 0xFFFFFFFF) / 1e3 for i in range(4)]
+        return dict(zip(("resolve", "gather", "compute", "push"), d))
+
     def nbytes(self):
-        return sum(t.numel() * 4 for t in (self.slot_of, self.entries, self.inst_slot, self.touched) if t is not None)
+        return sum(t.numel() * 4 for t in (self.entries, self.stash, self.touched, self.wc, self.gc))
 
 
 def lr_fused_step(state: FusedLRState, keys, x, labels, loss_out, rule="adagrad", blocks_per_sm=0, **hyper):
@@ -52,7 +64,6 @@ def lr_fused_step(state: FusedLRState, keys, x, labels, loss_out, rule="adagrad"
                float(hyper.get("b", 0.0)), float(hyper.get("c", 0.0)), state.step)
     t = state.table
     _lib.call("ssb_lr_fused_step", t._view_ref(), keys.data_ptr(), None if x is None else x.data_ptr(), labels.data_ptr(),
-              n_ex, state.n_feat, _lib.ptr(state.slot_of), 0 if state.slot_of is None else state.slot_of.numel(),
-              state.entries.data_ptr(), state.inst_slot.data_ptr(), state.touched.data_ptr(), state.max_touched,
-              state.counters.data_ptr(), state.step, loss_out.data_ptr(), RULE_IDS[rule], C.addressof(hy), int(blocks_per_sm),
-              _lib.stream_ptr())
+              n_ex, state.n_feat, state.entries.data_ptr(), state.dense_keys, state.stash.data_ptr(), state.touched.data_ptr(),
+              state.wc.data_ptr(), state.gc.data_ptr(), state.max_touched, state.counters.data_ptr(), state.step,
+              loss_out.data_ptr(), RULE_IDS[rule], C.addressof(hy), int(blocks_per_sm), _lib.stream_ptr())
