@@ -72,11 +72,11 @@ def dist_env():
 def run_ours(args):
     import numpy as np
     import torch
-    import torch.distributed as dist
 
     from swiftsnails_b200 import _lib
     from swiftsnails_b200.models.word2vec import (Word2VecConfig, Word2VecTrainer, Word2VecWorker,
                                                   synthetic_corpus)
+    from swiftsnails_b200.parallel import group as ps_group
     from swiftsnails_b200.ops._util import u32_tensor
     from swiftsnails_b200.parallel.cluster import make_table
     from swiftsnails_b200.utils.clocks import ClockSampler
@@ -87,8 +87,11 @@ def run_ours(args):
             raise SystemExit("launch with torchrun for --gpus > 1")
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+    # The job is run by the master, as in the reference: every rank registers with swift_master over ZeroMQ and gets
+    # its rank, the route and the fragment map from it (parallel/group.py). No torch.distributed / NCCL on this
+    # path; only the NCCL baseline arm (and the collective hand-off variant of the inbox) initialises it.
+    grp = ps_group.init("torch" if (args.impl == "nccl" or args.inbox_barrier == "nccl") else "master", frag_num=max(1024, world))
+    rank = grp.rank
 
     tile_impl = args.tile_impl
     if tile_impl == "auto":
@@ -125,24 +128,20 @@ def run_ours(args):
             table.pull(all_keys[c:c + (1 << 20)], want_fp32=False) if args.impl == "nccl" else table.resolve(all_keys[c:c + (1 << 20)])
         del all_keys
         torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
+        grp.barrier()
     # two disjoint halves of the corpus: the device-timed arm and the end-to-end arm never see the same batch
     corpus = synthetic_corpus(cfg.vocab, 2 * (K + W) * B, s=cfg.zipf_s, seed=100 + rank)
     host_all = torch.from_numpy(corpus.view(np.int32)).reshape(2 * (K + W), B).pin_memory()
     host, host_e2e = host_all[:K + W], host_all[K + W:]
 
     def barrier():
-        if world > 1:
-            dist.barrier()
+        # this GPU idle, then every rank here (a host-side round through the master, ~0.1 ms of skew at most,
+        # against windows of >= 10 ms; the reported time is the max over ranks)
         torch.cuda.synchronize()
+        grp.barrier()
 
     def max_over_ranks(ms):
-        if world == 1:
-            return ms
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return float(grp.all_reduce(float(ms), "max"))
 
     NW = max(1, args.windows)
 
@@ -289,9 +288,7 @@ def run_ours(args):
         if hasattr(table.inbox, "err"):
             health["inbox_overflow"] += int(table.inbox.err.item())      # an apply wait ran out: rows were skipped
     if world > 1:
-        ht = torch.tensor([health["table_full"], health["inbox_overflow"]], dtype=torch.int64, device=dev)
-        dist.all_reduce(ht)
-        health = {"table_full": int(ht[0].item()), "inbox_overflow": int(ht[1].item())}
+        health = {k: int(grp.all_reduce(v, "sum")) for k, v in health.items()}
 
     words = float(K) * B * world
     value = words / (ms / 1e3)
@@ -310,6 +307,8 @@ def run_ours(args):
                        "bf16_row_mirror": with_shadow, "worker_slot_cache": bool(cfg.slot_cache),
                        "inbox_push": bool(use_inbox), "inbox_rows_bf16": bool(use_inbox and args.inbox_bf16),
                        "inbox_handoff": args.inbox_barrier if use_inbox else None,
+                       "control_plane": {"single": "one process", "master": "swift_master over ZeroMQ (registration, route, fragment map, barriers); no torch.distributed / NCCL",
+                                         "torch": "torch.distributed (NCCL)"}[grp.kind],
                        "same_switches_at_every_gpu_count": "slot cache, bf16 row mirror and bf16 inbox rows are on for every N; the inbox itself only exists with peers (N > 1)",
                        "timed_windows": NW, "window_ms_per_step": [round(x / K, 5) for x in win_ms],
                        "e2e_window_ms_per_step": [round(x / K, 5) for x in e2e_ms],
@@ -330,8 +329,15 @@ def run_ours(args):
         }
         print(json.dumps(out))
     if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        grp.barrier()
+        if grp.kind == "torch":
+            import torch.distributed as dist
+
+            dist.destroy_process_group()
+        else:
+            grp.finish()          # WORKER_FINISH_WORK -> SERVER_TOLD_TO_TERMINATE -> ack (no dump in the benchmark)
+            grp.close()
     if health["table_full"] or health["inbox_overflow"]:
         raise SystemExit("bench.py: updates were lost during the run: %r" % (health,))
 

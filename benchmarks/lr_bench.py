@@ -3,7 +3,7 @@
 batches (13 numeric + 26 categorical features per example), AdaGrad on the owner shard.
 Prints examples/s and feature-keys/s (device-timed, max over ranks)."""
 import argparse, json, os, sys
-import numpy as np, torch, torch.distributed as dist
+import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
@@ -22,8 +22,9 @@ def main():
     a = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     dev = torch.device("cuda", local); torch.cuda.set_device(dev)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+    from swiftsnails_b200.parallel import group as ps_group
+    grp = ps_group.init("master")            # ranks register with swift_master over ZeroMQ; no torch.distributed
+    rank = grp.rank
     cfg = LRConfig(feature_bits=a.feature_bits, batch_size=a.batch, fused=bool(a.fused), optimizer=a.optimizer)
     # touched features are far fewer than 2^28; size the table for 64M rows in total
     table = make_table((1 << 26) // world, 1, dev, with_state=(2 if a.optimizer == "ftrl" else True), init_scale=0.0,
@@ -35,7 +36,7 @@ def main():
     for s in range(a.warmup):
         w.step(*dev_data[s % n_batches])
     torch.cuda.synchronize()
-    if world > 1: dist.barrier()
+    grp.barrier()
     w.reset_loss()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -43,8 +44,7 @@ def main():
         w.step(*dev_data[s % n_batches])
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+    ms = float(grp.all_reduce(float(ms), "max"))
     if rank == 0:
         ex = a.steps * a.batch * world
         print(json.dumps({"bench": "sparse_lr_adagrad", "n_gpus": world, "feature_bits": a.feature_bits, "batch_per_gpu": a.batch,
@@ -52,8 +52,10 @@ def main():
                           "feature_keys_per_s": ex * cfg.n_feat / (ms * 1e-3), "unique_keys_last_step": int(w.n_unique.item()),
                           "mean_loss": w.mean_loss(), "fused": bool(a.fused), "optimizer": a.optimizer, "health": w.health(),
                           "phase_us_last_step": (w.fused.phase_us() if w.fused is not None else None)}))
-    if world > 1:
-        dist.barrier(); dist.destroy_process_group()
+    torch.cuda.synchronize()
+    grp.barrier()
+    grp.finish()
+    grp.close()
 
 
 if __name__ == "__main__":

@@ -280,6 +280,60 @@ long long ssb_corpus_count_words(const char* path, uint32_t vocab, unsigned long
 long ssb_corpus_next(void* h, uint32_t* out) { return static_cast<CorpusLoader*>(h)->next(out); }
 void ssb_corpus_close(void* h) { delete static_cast<CorpusLoader*>(h); }
 
+// ---- sparse-LR example files: `label key:value key:value …` (value defaults to 1), the format the CPU worker's lr
+// app reads (csrc/apps/algorithms.h, LogisticRegressionAlg::parse_record). Parses the lines whose index % split_n ==
+// split_i into padded arrays for the GPU step: keys[n][max_feat] (0xFFFFFFFF = empty position), vals[n][max_feat],
+// labels[n] (1 if label > 0). keys == NULL: only count. key_mod > 0: keys are taken modulo key_mod (hashed space).
+// out_stats[0] = examples, [1] = features dropped because a line had more than max_feat. Returns examples or -1.
+long long ssb_lr_parse_file(const char* path, int max_feat, uint32_t* keys, float* vals, float* labels, long long max_examples,
+                            unsigned long long key_mod, int split_n, int split_i, long long* out_stats) {
+  if (!path || max_feat < 1 || split_n < 1 || split_i < 0 || split_i >= split_n) return -1;
+  MappedFile mf(path);
+  if (!mf.opened()) return -1;
+  const char* p = mf.data();
+  if (!p) { if (out_stats) { out_stats[0] = 0; out_stats[1] = 0; } return 0; }     // empty file
+  const char* end = p + mf.size();
+  long long n = 0, dropped = 0, line_no = 0;
+  while (p < end) {
+    const char* eol = static_cast<const char*>(std::memchr(p, '\n', (size_t)(end - p)));
+    if (!eol) eol = end;
+    const char* q = p;
+    while (q < eol && (*q == ' ' || *q == '\t' || *q == '\r')) ++q;
+    const bool is_example = q < eol && (std::isdigit((unsigned char)*q) || *q == '-' || *q == '+' || *q == '.');
+    if (is_example) {
+      const bool mine = (line_no % split_n) == split_i;
+      ++line_no;
+      if (mine) {
+        if (keys && n >= max_examples) break;
+        char* e = nullptr;
+        const float lab = std::strtof(q, &e);
+        q = e;
+        int f = 0;
+        uint32_t* kr = keys ? keys + n * max_feat : nullptr;
+        float* vr = vals ? vals + n * max_feat : nullptr;
+        while (q < eol) {
+          while (q < eol && (*q == ' ' || *q == '\t' || *q == '\r')) ++q;
+          if (q >= eol || !std::isdigit((unsigned char)*q)) break;
+          unsigned long long k = std::strtoull(q, &e, 10);
+          q = e;
+          float v = 1.f;
+          if (q < eol && *q == ':') { v = std::strtof(q + 1, &e); q = e; }
+          if (key_mod) k %= key_mod;
+          if (f < max_feat) { if (kr) { kr[f] = (uint32_t)k; vr[f] = v; } ++f; } else ++dropped;
+        }
+        if (kr) {
+          for (; f < max_feat; ++f) { kr[f] = 0xFFFFFFFFu; vr[f] = 0.f; }
+          labels[n] = lab > 0 ? 1.f : 0.f;
+        }
+        ++n;
+      }
+    }
+    p = eol + 1;
+  }
+  if (out_stats) { out_stats[0] = n; out_stats[1] = dropped; }
+  return n;
+}
+
 // ---- roles (one role per process; they use the process-wide transfer) ----------------------------
 int ssb_run_master(const char* config_path) {
   if (ssb_config_load(config_path) != 0) return -1;
@@ -298,6 +352,65 @@ int ssb_run_worker(const char* config_path, const char* app, const char* data_pa
   int rc = run_worker(app, data_path ? data_path : "");
   if (global_config().get_config("local_train", "0").to_int32() == 0) ps_transfer().shutdown();
   return rc;
+}
+
+
+// ---- a GPU rank's control plane: register with the master, route, fragment map, group exchange, shutdown ----------
+// ref: system/node_init.h:16-152, master/terminate.h:15-109, server/terminate.h:16-54; see system/group_exchange.h.
+static GpuNode* g_node = nullptr;
+
+// master_addr "tcp://ip:port"; listen_addr "" = an ephemeral port on the first non-loopback interface, or e.g.
+// "tcp://127.0.0.1:0". Returns the rank (>= 0) or a negative number.
+int ssb_node_start(const char* master_addr, const char* listen_addr, int init_timeout_s) {
+  if (g_node) return -2;
+  if (!master_addr || !*master_addr) return -1;
+  global_config().set("master_addr", master_addr);
+  if (listen_addr && *listen_addr) global_config().set("listen_addr", listen_addr);
+  if (init_timeout_s > 0) global_config().set("init_timeout", std::to_string(init_timeout_s));
+  g_node = new GpuNode();
+  return g_node->start();
+}
+int ssb_node_rank(void) { return g_node ? g_node->rank() : -1; }
+int ssb_node_world(void) { return g_node ? g_node->world() : -1; }
+// The fragment map the master built (NODE_ASKFOR_HASHFRAG). out[0] = nodes, out[1] = fragments; map_out may be
+// NULL (size query). Returns the number of fragments, -1 without a node, -2 if cap is too small.
+int ssb_node_hashfrag(int* out, uint32_t* map_out, int cap) {
+  if (!g_node) return -1;
+  auto& hf = shared_hashfrag();
+  if (out) { out[0] = hf.num_nodes(); out[1] = hf.num_frags(); }
+  if (!map_out) return hf.num_frags();
+  if (cap < hf.num_frags()) return -2;
+  for (int i = 0; i < hf.num_frags(); ++i) map_out[i] = (uint32_t)hf.map_table()[(size_t)i];
+  return hf.num_frags();
+}
+// All-gather through the master: out receives the ranks' byte strings back to back, lens[r] their lengths.
+// Returns the total bytes, -1 without a node, -2 timed out, -3 out too small.
+long ssb_node_exchange(const void* buf, long len, void* out, long out_cap, long* lens, int timeout_s) {
+  if (!g_node) return -1;
+  std::vector<std::string> parts;
+  if (!g_node->exchange(std::string(static_cast<const char*>(buf), (size_t)len), parts, 1000L * timeout_s)) return -2;
+  long total = 0;
+  for (auto& p : parts) total += (long)p.size();
+  if (total > out_cap) return -3;
+  char* o = static_cast<char*>(out);
+  for (size_t r = 0; r < parts.size(); ++r) {
+    std::memcpy(o, parts[r].data(), parts[r].size());
+    o += parts[r].size();
+    if (lens) lens[r] = (long)parts[r].size();
+  }
+  return total;
+}
+// WORKER_FINISH_WORK, then wait for SERVER_TOLD_TO_TERMINATE. 0 ok, -2 timed out. Afterwards: dump, ssb_node_dump_done().
+int ssb_node_finish(int timeout_s) {
+  if (!g_node) return -1;
+  return g_node->finish(1000L * timeout_s) ? 0 : -2;
+}
+void ssb_node_dump_done(void) { if (g_node) g_node->dump_done(); }
+void ssb_node_stop(void) {
+  if (!g_node) return;
+  ps_transfer().shutdown();
+  delete g_node;
+  g_node = nullptr;
 }
 
 }  // extern "C"

@@ -2,6 +2,7 @@
 // ref: /root/reference/src/core/framework/SwiftMaster.h:8-29.
 #pragma once
 #include "../system/master_init.h"
+#include "../system/group_exchange.h"
 #include "../system/master_terminate.h"
 namespace ssb {
 
@@ -10,6 +11,7 @@ class SwiftMaster {
   SwiftMaster() = default;
   void operator()() {
     terminate_.register_handler();  // before the route goes out: a fast worker may finish early
+    group_.register_handler();      // GPU ranks all-gather through the master (group_exchange.h)
     init_();
     LOG(WARNING) << "master: cluster is up (" << init_.server_count() << " servers, " << init_.worker_count() << " workers)";
     terminate_();
@@ -18,6 +20,7 @@ class SwiftMaster {
  private:
   MasterTransferInit init_;
   MasterTerminate terminate_;
+  MasterGroupExchange group_;
 };
 
 }  // namespace ssb

@@ -21,15 +21,21 @@ class MasterTerminate {
     transfer_.message_class().add(WORKER_FINISH_WORK, [this](std::shared_ptr<Request>, Request& rsp) {
       rsp.cont << (int32_t)1234;
       int done = ++finished_workers_;
-      if (done >= transfer_.route().worker_num() && transfer_.route().worker_num() > 0) workers_done_.set_state_valid();
+      if (done >= expected_workers() && expected_workers() > 0) workers_done_.set_state_valid();
     });
+  }
+  // `colocated_workers: 1` (GPU jobs: every registered server process also hosts a worker, group_exchange.h): a
+  // WORKER_FINISH_WORK is expected from every server as well as from every worker node.
+  int expected_workers() {
+    int n = transfer_.route().worker_num();
+    if (global_config().get_config("colocated_workers", "0").to_int32() != 0) n += transfer_.route().server_num() - 1;
+    return n;
   }
 
  private:
   void wait_workers() {  // ref: master/terminate.h:44-62
     register_handler();
-    if (transfer_.route().worker_num() == 0 || finished_workers_.load() >= transfer_.route().worker_num())
-      workers_done_.set_state_valid();
+    if (expected_workers() == 0 || finished_workers_.load() >= expected_workers()) workers_done_.set_state_valid();
     long alive_s = global_config().get_config("master_longest_alive_duration", "0").to_int32();
     if (alive_s > 0)
       workers_done_.time_limit(1000L * alive_s, [] { LOG(FATAL) << "master_longest_alive_duration exceeded"; });

@@ -72,10 +72,30 @@ long long ssb_corpus_count_words(const char *path, uint32_t vocab, unsigned long
 long ssb_corpus_next(void *h, uint32_t *out);
 void ssb_corpus_close(void *h);
 
+/* sparse-LR example files `label key:value …` -> padded arrays for the GPU step (keys == NULL: count only);
+ * the format of the CPU worker's lr app (csrc/apps/algorithms.h). Lines with index % split_n == split_i. */
+long long ssb_lr_parse_file(const char *path, int max_feat, uint32_t *keys, float *vals, float *labels,
+                            long long max_examples, unsigned long long key_mod, int split_n, int split_i,
+                            long long *out_stats);
+
 /* roles — ref: core/framework/SwiftMaster.h, SwiftServer.h, SwiftWorker.h. One role per process. */
 int ssb_run_master(const char *config_path);
 int ssb_run_server(const char *config_path);
 int ssb_run_worker(const char *config_path, const char *app, const char *data_path);
+
+/* A GPU rank's control plane (system/group_exchange.h): the process hosts server shard g and worker g. It registers
+ * with the master as a server over ZeroMQ (NODE_INIT_ADDRESS; rank = assigned id - 1), adopts the route, fetches
+ * the fragment map (NODE_ASKFOR_HASHFRAG), all-gathers small byte strings through the master (NODE_GROUP_EXCHANGE:
+ * socket names for the VMM fd exchange, barriers, max-over-ranks), and shuts down with WORKER_FINISH_WORK ->
+ * SERVER_TOLD_TO_TERMINATE -> dump -> ack. ref: system/node_init.h:16-152, master/terminate.h, server/terminate.h */
+int ssb_node_start(const char *master_addr, const char *listen_addr, int init_timeout_s);  /* rank, or < 0 */
+int ssb_node_rank(void);
+int ssb_node_world(void);
+int ssb_node_hashfrag(int *out2, uint32_t *map_out, int cap);
+long ssb_node_exchange(const void *buf, long len, void *out, long out_cap, long *lens, int timeout_s);
+int ssb_node_finish(int timeout_s);
+void ssb_node_dump_done(void);
+void ssb_node_stop(void);
 
 #ifdef __cplusplus
 }

@@ -1,6 +1,7 @@
 """Build the sharded table for a job: one server shard per GPU, every shard visible to every
-worker.  Single process => plain local shard; ``torch.distributed`` initialised (one process
-per GPU, NCCL) => VMM peer mapping over NVLink (``peer.PeerMemory``).
+worker.  Single process => plain local shard; several ranks (``parallel.group``: registered with the
+master over ZeroMQ, or a torch.distributed job) => VMM peer mapping over NVLink (``peer.PeerMemory``);
+the fragment map is the one the master built (NODE_ASKFOR_HASHFRAG) when the master runs the job.
 
 Node numbering follows the reference (master 0, servers 1..S:
 /root/reference/src/core/system/ServerWorkerRoute.h:17-31); shard index = node id - 1 = rank.
@@ -34,12 +35,12 @@ def shard_layout(capacity, dim, with_state, with_shadow=False):
 
 def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, frag_num=1024, seed=0x5EED,
                load_factor=0.5, force_peer=False, with_shadow=False, init_kind=0):
-    import torch.distributed as dist
+    from . import group as _group
 
-    world = dist.get_world_size() if dist.is_initialized() else 1
-    rank = dist.get_rank() if dist.is_initialized() else 0
+    grp = _group.current()
+    world, rank = grp.world, grp.rank
     capacity = round_capacity(rows_per_shard, load_factor)
-    hf = HashFrag(world, max(frag_num, world))
+    hf = grp.hashfrag(frag_num) if world > 1 else HashFrag(world, max(frag_num, world))
     if world == 1 and not force_peer:
         shard = DeviceShard(capacity, dim, device, with_state, with_shadow=with_shadow)
         return ShardedTable(hf, capacity, dim, [shard.ptrs()], device, seed=seed, init_scale=init_scale,
@@ -64,7 +65,7 @@ def make_table(rows_per_shard, dim, device, with_state=False, init_scale=None, f
                         alloc=lambda shape, dtype: alloc_at(offs[next(order)], shape, dtype))
     torch.cuda.synchronize(device)
     if world > 1:
-        dist.barrier()  # every shard is initialised before anyone probes it
+        grp.barrier()  # every shard is initialised before anyone probes it
     ptrs = []
     for r in range(world):
         b = pm.segment_ptr(r)
@@ -97,10 +98,11 @@ class Inbox:
     def __init__(self, table: ShardedTable, capacity: int, device, bf16_rows: bool = False, barrier: str = "flags"):
         import ctypes as C
 
-        import torch.distributed as dist
+        from . import group as _group
 
         self.table, self.device = table, device
-        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.group = _group.current()
+        self.world, self.rank = self.group.world, self.group.rank
         self.seg_rows = max(64, (int(capacity) + self.world - 1) // self.world)     # rows per (owner, sender)
         self.capacity = self.seg_rows * self.world
         self.bf16_rows, self.barrier = bool(bf16_rows), barrier
@@ -144,13 +146,11 @@ class Inbox:
         self.step = 0
         self._C = C
         torch.cuda.synchronize(device)
-        dist.barrier()
+        self.group.barrier()
 
     def push(self, gslot, grads, lr, eps=1e-8, adagrad=True, n_dev=None, n=None, rule=None, **hyper):
         """``rule``: a named device-side update rule (ops.rules) instead of the built-in SGD / AdaGrad: the send
         kernel then only ships, this rank's own rows and the inbox are applied by the rule's own entry points."""
-        import torch.distributed as dist
-
         C = self._C
         n = gslot.numel() if n is None else n
         par = self.parity
@@ -173,6 +173,8 @@ class Inbox:
             _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), self.step, sp)
             _lib.call("ssb_flags_wait2", self.flags_l.data_ptr(), self.world, self.step, 0, self.err.data_ptr(), sp)
         else:
+            import torch.distributed as dist         # barrier="nccl": the collective variant needs a torch.distributed job
+
             _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), 0, sp)
             dist.all_reduce(self.token)      # every rank's shipment has landed in my inbox
         if self.bf16_rows and rule is not None:
@@ -238,9 +240,9 @@ class ChunkInbox:
 
         self.table, self.device = table, device
         if world is None:
-            import torch.distributed as dist
+            from . import group as _group
 
-            world, rank = dist.get_world_size(), dist.get_rank()
+            world, rank = _group.current().world, _group.current().rank
         self.world, self.rank = int(world), int(rank)
         D = table.dim
         lay = self.layout(capacity, D, self.world)
@@ -316,14 +318,17 @@ class ChunkInbox:
 
 def attach_inbox(table: ShardedTable, capacity: int, bf16_rows: bool = False, barrier: str = "flags"):
     """Give a peer-mapped table owner-side inboxes (no-op for a single process)."""
-    import torch.distributed as dist
+    from . import group as _group
 
-    if not dist.is_initialized() or dist.get_world_size() == 1:
+    grp = _group.current()
+    if grp.world == 1:
         table.inbox = None
         return None
+    if barrier == "nccl" and grp.kind != "torch":
+        raise ValueError('barrier="nccl" needs a torch.distributed job (parallel.group.init("torch"))')
     if barrier == "chunks":
         table.inbox = ChunkInbox(table, capacity, table.device)
-        dist.barrier()
+        grp.barrier()
     else:
         table.inbox = Inbox(table, capacity, table.device, bf16_rows=bf16_rows, barrier=barrier)
     return table.inbox

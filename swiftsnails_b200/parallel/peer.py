@@ -68,9 +68,9 @@ def exchange_fds(my_fd, rank, world, tag):
 
     th = threading.Thread(target=acceptor, daemon=True)
     th.start()
-    import torch.distributed as dist
+    from . import group as _group
 
-    dist.barrier()  # every rank is listening
+    _group.current().barrier()  # every rank is listening
     for p in range(world):
         if p == rank:
             continue
@@ -94,11 +94,11 @@ class PeerMemory:
     """
 
     def __init__(self, nbytes, device, align_to=1):
-        import torch.distributed as dist
+        from . import group as _group
 
+        grp = _group.current()       # the master-run job (ZeroMQ), torch.distributed if that is what runs, or one rank
         self.device = device
-        self.rank = dist.get_rank() if dist.is_initialized() else 0
-        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank, self.world = grp.rank, grp.world
         dev_index = device.index if device.index is not None else torch.cuda.current_device()
         gran = vmm_granularity(dev_index)
         unit = math.lcm(gran, int(align_to))
@@ -113,9 +113,8 @@ class PeerMemory:
         _vmm("ssb_vmm_map", C.c_uint64(self.base + self.rank * self.stride), C.c_uint64(self.stride),
              C.c_uint64(handle.value), C.c_int(dev_index))
         if self.world > 1:
-            tag = [uuid.uuid4().hex if self.rank == 0 else None]
-            dist.broadcast_object_list(tag, src=0)
-            fds = exchange_fds(fd.value, self.rank, self.world, tag[0])
+            tag = grp.broadcast_object(uuid.uuid4().hex if self.rank == 0 else None, src=0)
+            fds = exchange_fds(fd.value, self.rank, self.world, tag)
             for p, pfd in sorted(fds.items()):
                 h = C.c_uint64()
                 _vmm("ssb_vmm_import", C.c_int(pfd), C.byref(h))
@@ -123,7 +122,7 @@ class PeerMemory:
                 self._handles[p] = int(h.value)
                 _vmm("ssb_vmm_map", C.c_uint64(self.base + p * self.stride), C.c_uint64(self.stride),
                      C.c_uint64(h.value), C.c_int(dev_index))
-            dist.barrier()
+            grp.barrier()
         os.close(fd.value)
 
     def segment_ptr(self, r):

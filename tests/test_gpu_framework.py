@@ -94,7 +94,6 @@ def test_train_from_text_corpus_with_ragged_sentences(device, tmp_path):
     assert np.isfinite(last) and last < 4.0, last                                    # 6*ln2 = 4.16 at init
 
 
-@pytest.mark.xfail(strict=False, reason="passed on a B200 in round 1; backups / resume / state dump were added in round 2 after GPU access was closed, so this has not run on hardware since")
 def test_train_cli_one_gpu(device, tmp_path):
     """`python -m swiftsnails_b200.train -config … -data … -out …`: the GPU counterpart of
     `swift_worker -config … -data …` — trains from a text corpus and leaves a reference-format dump."""
@@ -135,6 +134,49 @@ def test_train_cli_one_gpu(device, tmp_path):
     p = subprocess.run([sys.executable, "-m", "swiftsnails_b200.train", "-config", conf, "-data", data, "-out", out, "--resume", ck,
                         "--epochs", "1"], capture_output=True, text=True, timeout=600, cwd=root, env=env)
     assert p.returncode == 0 and "resumed" in p.stdout, p.stdout[-2000:] + p.stderr[-2000:]
+
+
+def _write_lr_examples(path, n, n_feat, space, seed):
+    """`label key:value …` lines from a hidden sparse linear model (so there is something to learn)."""
+    rng = np.random.default_rng(seed)
+    w = rng.standard_normal(space) * 1.5
+    with open(path, "w") as f:
+        for _ in range(n):
+            ks = np.unique((space * rng.random(n_feat) ** 2).astype(np.int64))
+            vs = np.where(rng.random(len(ks)) < 0.3, np.round(rng.random(len(ks)) * 2, 3), 1.0)
+            y = int(rng.random() < 1.0 / (1.0 + np.exp(-float((w[ks] * vs).sum()))))
+            f.write(str(y) + " " + " ".join(("%d" % k) if v == 1.0 else ("%d:%g" % (k, v)) for k, v in zip(ks, vs)) + "\n")
+
+
+@pytest.mark.parametrize("update", ["adagrad", "ftrl"])
+def test_train_cli_lr_app_one_gpu(device, tmp_path, update):
+    """`-app lr`: sparse logistic regression from a `label key:value …` file through the fused GPU step; the dump
+    has one weight per seen feature, the loss falls."""
+    import json
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    data, conf, out = str(tmp_path / "ex.txt"), str(tmp_path / "lr.conf"), str(tmp_path / "w.txt")
+    _write_lr_examples(data, 20000, 12, 5000, 3)
+    with open(conf, "w") as f:
+        f.write("feature_bits: 16\nmax_features: 16\nminibatch: 2000\nupdate: %s\nlearning_rate: %s\nnum_iters: 4\n"
+                "l1: 0.001\ntable_rows: 65536\n" % (update, "0.1" if update == "adagrad" else "0.2"))
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    p = subprocess.run([sys.executable, "-m", "swiftsnails_b200.train", "-app", "lr", "-config", conf, "-data", data, "-out", out],
+                       capture_output=True, text=True, timeout=600, cwd=root, env=env)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    res = json.loads([l for l in p.stdout.splitlines() if l.startswith("RESULT ")][0][len("RESULT "):])
+    assert res["app"] == "lr" and res["examples"] == 4 * 20000 and res["update"] == update
+    assert res["loss_last"] < 0.8 * res["loss_first"] and res["loss_first"] < 0.75
+    assert res["health_rank0"]["table_full"] == 0 and res["health_rank0"]["touched_overflow"] == 0
+    seen = set()
+    for line in open(data):
+        seen |= set(int(t.split(":")[0]) for t in line.split()[1:])
+    lines = open(out).read().splitlines()
+    assert len(lines) == len(seen) == res["rows_dumped_rank0"]
+    keys = set(int(l.split("\t")[0]) for l in lines)
+    assert keys == seen
 
 
 @pytest.mark.parametrize("impl", ["cuda_core", "tcgen05"])
