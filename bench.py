@@ -114,7 +114,9 @@ def run_ours(args):
         from swiftsnails_b200.parallel.cluster import attach_inbox
 
         n_keys_max = 2 * cfg.tokens_per_step + ((cfg.tokens_per_step + 127) // 128) * cfg.neg_pool
-        attach_inbox(table, 2 * n_keys_max, bf16_rows=bool(args.inbox_bf16), barrier=args.inbox_barrier)
+        ib = attach_inbox(table, 2 * n_keys_max, bf16_rows=bool(args.inbox_bf16), barrier=args.inbox_barrier)
+        if os.environ.get("SSB200_SHIP_FIRST") == "0" and hasattr(ib, "ship_first"):
+            ib.ship_first = False
     if args.impl == "nccl":
         from swiftsnails_b200.parallel.nccl_baseline import NcclShardedTable
 

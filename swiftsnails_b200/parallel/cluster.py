@@ -95,14 +95,28 @@ class Inbox:
     inbox; a sender may use ``capacity // world`` of them (excess rows are counted in ``overflow``
     and dropped)."""
 
-    def __init__(self, table: ShardedTable, capacity: int, device, bf16_rows: bool = False, barrier: str = "flags"):
+    @staticmethod
+    def segment_bytes(capacity, dim, world, bf16_rows):
+        """Bytes of one rank's inbox segment (two parities + flags) for these parameters."""
+        seg_rows = max(64, (int(capacity) + world - 1) // world)
+        cap = seg_rows * world
+        count_off = cap * dim * (2 if bf16_rows else 4) + cap * 4
+        per = (count_off + 256 + 4095) // 4096 * 4096
+        return 2 * per + 4096
+
+    def __init__(self, table: ShardedTable, capacity: int, device, bf16_rows: bool = False, barrier: str = "flags",
+                 world=None, rank=None, segment_ptrs=None, local_shard=None):
+        """``world`` / ``rank`` / ``segment_ptrs`` / ``local_shard``: for callers that bring their own memory — tests
+        that emulate several ranks inside one process on one GPU (every rank's segment is then a plain device buffer
+        of ``segment_bytes`` bytes, zeroed) — instead of the job's group and a :class:`PeerMemory` exchange."""
         import ctypes as C
 
         from . import group as _group
+        from .peer import tensor_from_ptr
 
         self.table, self.device = table, device
-        self.group = _group.current()
-        self.world, self.rank = self.group.world, self.group.rank
+        self.group = _group.current() if world is None else None
+        self.world, self.rank = (self.group.world, self.group.rank) if world is None else (int(world), int(rank))
         self.seg_rows = max(64, (int(capacity) + self.world - 1) // self.world)     # rows per (owner, sender)
         self.capacity = self.seg_rows * self.world
         self.bf16_rows, self.barrier = bool(bf16_rows), barrier
@@ -113,19 +127,23 @@ class Inbox:
         count_off = slots_off + self.capacity * 4
         per = (count_off + 256 + 4095) // 4096 * 4096
         flags_off = 2 * per
-        self.pm = PeerMemory(flags_off + 4096, device)
-        seg = self.pm.local_tensor()
-        seg.zero_()
+        if segment_ptrs is None:
+            self.pm = PeerMemory(flags_off + 4096, device)
+            segment_ptrs = [self.pm.segment_ptr(r) for r in range(self.world)]
+            seg = self.pm.local_tensor()
+            seg.zero_()
+        else:
+            seg = tensor_from_ptr(segment_ptrs[self.rank], flags_off + 4096, device)
         self.views, self.rows_l, self.slots_l, self.count_l = [], [], [], []
         for par in range(2):
             # the view a SENDER uses: its private sub-region on every owner
             v = _lib.SsbInboxView()
             for r in range(self.world):
-                b = self.pm.segment_ptr(r) + par * per
+                b = segment_ptrs[r] + par * per
                 v.rows[r] = b + self.rank * self.seg_rows * D * esz
                 v.slots[r] = b + slots_off + self.rank * self.seg_rows * 4
                 v.count[r] = b + count_off + self.rank * 4
-                v.flags[r] = self.pm.segment_ptr(r) + flags_off
+                v.flags[r] = segment_ptrs[r] + flags_off
             v.capacity = self.seg_rows
             self.views.append(v)
             # what the OWNER applies: all sub-regions of its own inbox
@@ -135,7 +153,7 @@ class Inbox:
             self.slots_l.append(seg[base + slots_off:base + slots_off + self.capacity * 4].view(torch.int32))
             self.count_l.append(seg[base + count_off:base + count_off + 4 * self.world].view(torch.int32))
         self.flags_l = seg[flags_off:flags_off + 4 * self.world].view(torch.int32)
-        shard = table.owned[0]
+        shard = local_shard if local_shard is not None else table.owned[0]
         self.local = ShardedTable(HashFrag(1, 1), table.capacity, D, [shard.ptrs()], device, seed=table.seed,
                                   init_scale=table.init_scale, owned=[shard], init_kind=table.init_kind)
         self.overflow = torch.zeros(1, dtype=torch.int32, device=device)
@@ -144,13 +162,23 @@ class Inbox:
         self.token = torch.zeros(1, dtype=torch.int32, device=device)
         self.parity = 0
         self.step = 0
+        self.ship_first = True       # see push()
+        self.wait_limit = 0          # iterations (~0.2 us each) the hand-off wait may spin; 0 = the library default (~27 s)
         self._C = C
         torch.cuda.synchronize(device)
-        self.group.barrier()
+        if self.group is not None:
+            self.group.barrier()
 
     def push(self, gslot, grads, lr, eps=1e-8, adagrad=True, n_dev=None, n=None, rule=None, **hyper):
         """``rule``: a named device-side update rule (ops.rules) instead of the built-in SGD / AdaGrad: the send
         kernel then only ships, this rank's own rows and the inbox are applied by the rule's own entry points."""
+        ctx = self.ship(gslot, grads, lr, eps, adagrad, n_dev, n, rule, **hyper)
+        self.apply(ctx)
+
+    def ship(self, gslot, grads, lr, eps=1e-8, adagrad=True, n_dev=None, n=None, rule=None, **hyper):
+        """First half of :meth:`push`: ship the rows other ranks own, raise the hand-off flags, apply my own rows.
+        Returns the context for :meth:`apply`. (Split so that a test can run every emulated rank's ship before any
+        rank's apply on one stream — no kernel then ever waits for another launch.)"""
         C = self._C
         n = gslot.numel() if n is None else n
         par = self.parity
@@ -158,26 +186,51 @@ class Inbox:
         self.step += 1
         sp = _lib.stream_ptr()
         view = C.byref(self.views[par])
-        hy = None
-        if rule is not None:
-            from ..ops import rules as _rules
+        marks = getattr(self, "marks", None)       # benchmarks: a list that receives (name, CUDA event) per stage
 
+        def mark(name):
+            if marks is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                marks.append((name, e))
+        mark("start")
+        from ..ops import rules as _rules
+
+        # Ship first: the send kernel only ships the rows other ranks own and the hand-off flags go up right behind
+        # it; this rank's own rows are applied AFTERWARDS, while the peers' shipments are still landing, so the wait
+        # that follows finds its flags already raised. (ship_first = False: the older send kernel that applies the
+        # own rows between its shipments — built-in SGD / AdaGrad only — kept for comparison.)
+        ship_first = getattr(self, "ship_first", True) or rule is not None
+        if ship_first:
+            rule = rule if rule is not None else ("adagrad" if adagrad else "sgd")
             rule = rule if isinstance(rule, _rules.Rule) else _rules.Rule.get(rule)
             hy = rule.hyper(lr=lr, eps=eps, **hyper)
         _lib.call("ssb_push_send2", self.table._view_ref(), view, gslot.data_ptr(), grads.data_ptr(), n,
-                  _lib.ptr(n_dev), self.rank, float(lr), float(eps), -1 if rule is not None else (1 if adagrad else 0),
+                  _lib.ptr(n_dev), self.rank, float(lr), float(eps), -1 if ship_first else (1 if adagrad else 0),
                   1 if self.bf16_rows else 0, self.overflow.data_ptr(), self.cursor.data_ptr(), sp)
-        if rule is not None:         # my own rows (the rest travels)
-            rule.push(self.table, gslot, grads, hy, n_dev=n_dev, zero_grads=False, n=n, only_shard=self.rank)
+        mark("send")
         if self.barrier == "flags":
             _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), self.step, sp)
-            _lib.call("ssb_flags_wait2", self.flags_l.data_ptr(), self.world, self.step, 0, self.err.data_ptr(), sp)
+        else:
+            _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), 0, sp)
+        if ship_first:         # my own rows
+            rule.push(self.table, gslot, grads, hy, n_dev=n_dev, zero_grads=False, n=n, only_shard=self.rank)
+        mark("own")
+        return dict(par=par, step=self.step, ship_first=ship_first, rule=rule if ship_first else None, hy=hy if ship_first else None,
+                    lr=lr, eps=eps, adagrad=adagrad, mark=mark)
+
+    def apply(self, ctx):
+        """Second half of :meth:`push`: wait for every sender's hand-off, apply my inbox to my shard."""
+        par, ship_first, rule, hy, lr, eps, adagrad, mark = (ctx[k] for k in ("par", "ship_first", "rule", "hy", "lr", "eps", "adagrad", "mark"))
+        sp = _lib.stream_ptr()
+        if self.barrier == "flags":
+            _lib.call("ssb_flags_wait2", self.flags_l.data_ptr(), self.world, ctx["step"], int(self.wait_limit), self.err.data_ptr(), sp)
         else:
             import torch.distributed as dist         # barrier="nccl": the collective variant needs a torch.distributed job
 
-            _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), 0, sp)
             dist.all_reduce(self.token)      # every rank's shipment has landed in my inbox
-        if self.bf16_rows and rule is not None:
+        mark("handoff")
+        if self.bf16_rows and ship_first:
             rule.push_bf16_seg(self.local, self.slots_l[par], self.rows_l[par], self.seg_rows, self.count_l[par], self.world, hy)
         elif self.bf16_rows:
             _lib.call("ssb_push_bf16_seg", self.local._view_ref(), self.slots_l[par].data_ptr(), self.rows_l[par].data_ptr(),
@@ -188,12 +241,13 @@ class Inbox:
                 if r == self.rank:
                     continue                 # own rows were applied directly by the send kernel
                 sl, rw, cn = self.slots_l[par][r * S:(r + 1) * S], self.rows_l[par][r * S:(r + 1) * S], self.count_l[par][r:r + 1]
-                if rule is not None:
+                if ship_first:
                     rule.push(self.local, sl, rw, hy, n_dev=cn, zero_grads=False, n=S)
                 elif adagrad:
                     self.local.push_adagrad(sl, rw, lr, eps, n_dev=cn, zero_grads=False, n=S)
                 else:
                     self.local.push_sgd(sl, rw, lr, n_dev=cn, zero_grads=False, n=S)
+        mark("apply")
         # no clearing: every sender overwrites its count on its next publish (also with 0 rows)
 
 
