@@ -30,8 +30,13 @@ class GlobalPullAccess : public VirtualObject {
     for (auto& kv : node_reqs) {
       Request req;
       req.meta.message_class = WORKER_PULL_REQUEST;
-      req.cont.reserve(kv.second.size() * sizeof(key_t));
-      req.cont.put_array(kv.second.data(), kv.second.size());
+      if (reference_wire()) {      // the reference's form: (key, empty value)*  — ref: global_pull_access.h:84-88
+        val_t empty;
+        for (const key_t& k : kv.second) req.cont << k << empty;
+      } else {
+        req.cont.reserve(kv.second.size() * sizeof(key_t));
+        req.cont.put_array(kv.second.data(), kv.second.size());
+      }
       req.call_back_handler = [&cache, &barrier](std::shared_ptr<Request> rsp) {
         {
           rwlock_write_guard g(cache.rwlock());

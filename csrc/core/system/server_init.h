@@ -22,10 +22,22 @@ class ServerInitPullMethod {
       : transfer_(ps_transfer()), agent_(make_pull_access(table, method)) {}
   void operator()() {
     transfer_.message_class().add(WORKER_PULL_REQUEST, [this](std::shared_ptr<Request> req, Request& rsp) {
-      // ref: server/init.h:49-69
-      size_t n = (req->cont.size() - req->cont.status()) / sizeof(key_t);
-      std::vector<key_t> keys(n);
-      req->cont.get_array(keys.data(), n);
+      // ref: server/init.h:49-69. The reference's worker sends (key, empty value) pairs; this framework's worker
+      // sends the bare key array (a third of the bytes for dim-0 values). `wire_compat: reference` makes both ends
+      // speak the reference's form, so that nodes of the two code bases can share a cluster (tests/test_interop.py).
+      std::vector<key_t> keys;
+      if (reference_wire()) {
+        while (!req->cont.read_finished()) {
+          key_t key;
+          val_t unused;
+          req->cont >> key >> unused;
+          keys.push_back(key);
+        }
+      } else {
+        keys.resize((req->cont.size() - req->cont.status()) / sizeof(key_t));
+        req->cont.get_array(keys.data(), keys.size());
+      }
+      const size_t n = keys.size();
       val_t val;
       for (const key_t& key : keys) {
         agent_->get_pull_value(key, val);

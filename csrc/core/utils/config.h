@@ -89,4 +89,11 @@ inline ConfigParser& global_config() {
   return cfg;
 }
 
+// `wire_compat: reference`: pull requests carry (key, empty value) pairs like the reference's worker
+// (global_pull_access.h:84-88) instead of this framework's bare key array. Read once.
+inline bool reference_wire() {
+  static const bool on = global_config().get_config("wire_compat", "").to_string() == "reference";
+  return on;
+}
+
 }  // namespace ssb
