@@ -33,7 +33,8 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl", "nccl_padded"],
+                    help="nccl: all-to-all pull/push with exact splits (host sync per pull); nccl_padded: fixed buckets, no host sync, bf16 on the wire")
     ap.add_argument("--vocab", type=int, default=1_000_000)
     ap.add_argument("--dim", type=int, default=128)
     ap.add_argument("--window", type=int, default=5)
@@ -90,7 +91,8 @@ def run_ours(args):
     # The job is run by the master, as in the reference: every rank registers with swift_master over ZeroMQ and gets
     # its rank, the route and the fragment map from it (parallel/group.py). No torch.distributed / NCCL on this
     # path; only the NCCL baseline arm (and the collective hand-off variant of the inbox) initialises it.
-    grp = ps_group.init("torch" if (args.impl == "nccl" or args.inbox_barrier == "nccl") else "master", frag_num=max(1024, world))
+    nccl_arm = args.impl in ("nccl", "nccl_padded")
+    grp = ps_group.init("torch" if (nccl_arm or args.inbox_barrier == "nccl") else "master", frag_num=max(1024, world))
     rank = grp.rank
 
     tile_impl = args.tile_impl
@@ -117,17 +119,19 @@ def run_ours(args):
         ib = attach_inbox(table, 2 * n_keys_max, bf16_rows=bool(args.inbox_bf16), barrier=args.inbox_barrier)
         if os.environ.get("SSB200_SHIP_FIRST") == "0" and hasattr(ib, "ship_first"):
             ib.ship_first = False
-    if args.impl == "nccl":
+        if os.environ.get("SSB200_OWN_STREAM") == "0" and hasattr(ib, "own_stream"):
+            ib.own_stream = None
+    if nccl_arm:
         from swiftsnails_b200.parallel.nccl_baseline import NcclShardedTable
 
-        table = NcclShardedTable(table)
+        table = NcclShardedTable(table, padded=(args.impl == "nccl_padded"), wire_bf16=(args.impl == "nccl_padded"))
     K, W, B = args.steps, args.warmup, cfg.tokens_per_step
     # the model is fully materialised before timing (every input and output vector exists, like a
     # dense model whose weights are allocated at init): rank r creates the keys == r (mod world)
     if args.prepopulate:
         all_keys = torch.arange(rank, 2 * cfg.vocab, world, dtype=torch.int32, device=dev)
         for c in range(0, all_keys.numel(), 1 << 20):
-            table.pull(all_keys[c:c + (1 << 20)], want_fp32=False) if args.impl == "nccl" else table.resolve(all_keys[c:c + (1 << 20)])
+            table.pull(all_keys[c:c + (1 << 20)], want_fp32=False) if nccl_arm else table.resolve(all_keys[c:c + (1 << 20)])
         del all_keys
         torch.cuda.synchronize()
         grp.barrier()
@@ -305,7 +309,7 @@ def run_ours(args):
                        "window": cfg.window, "negatives": cfg.negatives,
                        "neg_pool_per_128_pair_tile": cfg.neg_pool, "global_batch": B * world,
                        "tokens_per_step_per_gpu": B, "seq_len": cfg.sent_len, "optimizer": cfg.optimizer,
-                       "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if args.impl == "nccl" else "P2P"),
+                       "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if nccl_arm else "P2P"),
                        "bf16_row_mirror": with_shadow, "worker_slot_cache": bool(cfg.slot_cache),
                        "inbox_push": bool(use_inbox), "inbox_rows_bf16": bool(use_inbox and args.inbox_bf16),
                        "inbox_handoff": args.inbox_barrier if use_inbox else None,

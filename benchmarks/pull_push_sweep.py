@@ -6,7 +6,11 @@ size.  Device-timed (CUDA events), max over ranks, >= 3 warm-up iterations per s
   python benchmarks/pull_push_sweep.py [--dim 64] [--max-keys 16777216] [--optimizer sgd]
   python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 benchmarks/pull_push_sweep.py
 One JSON line per (impl, size) on rank 0; roofline fractions are computed against the measured
-HBM copy bandwidth (MEASURED_PEAKS.json) at 1 GPU and 770 GB/s per direction NVLink otherwise.
+HBM copy bandwidth (MEASURED_PEAKS.json) and, with several GPUs, against NVLink bandwidths MEASURED at the start of
+the run by benchmarks/nvlink_probe.py (all-peers kernel reads for the pull, all-peers kernel writes for the push);
+the fraction against the nominal 900 GB/s per direction is printed next to it. The NCCL arm (`nccl`: split sizes
+through the host; `nccl_padded`: fixed-capacity buckets, no host sync, bf16 rows on the wire) runs in a
+torch.distributed job, each phase timed with its own CUDA events.
 """
 import argparse
 import json
@@ -33,7 +37,7 @@ def main():
     ap.add_argument("--key-space", type=int, default=0, help="distinct keys overall (default 2 x max-keys x world)")
     ap.add_argument("--optimizer", default="sgd", choices=["sgd", "adagrad"])
     ap.add_argument("--iters", type=int, default=5)
-    ap.add_argument("--impls", default="p2p,nccl")
+    ap.add_argument("--impls", default="p2p,nccl,nccl_padded")
     ap.add_argument("--out", default="")
     a = ap.parse_args()
 
@@ -42,20 +46,30 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+    from swiftsnails_b200.parallel import group as ps_group
+    grp = ps_group.init("torch")           # the NCCL arms need torch.distributed; the p2p arm only uses the group for set-up
     key_space = a.key_space or 2 * a.max_keys * world
     table = make_table((key_space + world - 1) // world, a.dim, dev, with_state=(a.optimizer == "adagrad"),
                        init_scale=0.1, frag_num=max(1024, world))
     tables = {"p2p": table}
-    if "nccl" in a.impls:
+    if "nccl" in a.impls.split(","):
         tables["nccl"] = NcclShardedTable(table)
+    if "nccl_padded" in a.impls.split(","):
+        tables["nccl_padded"] = NcclShardedTable(table, padded=True, wire_bf16=True)
     hbm = 6541.8e9
     try:
         hbm = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))["hbm_gbs"] * 1e9
     except Exception:
         pass
-    nvlink = 770e9
+    nv = None
+    if world > 1:
+        sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+        from nvlink_probe import probe
+        nv = probe(grp, dev)
+        if rank == 0:
+            print(json.dumps({"nvlink_probe": nv}), flush=True)
+    nv_read = (nv["read_all_gbs"] if nv else 900.0) * 1e9
+    nv_write = (nv["write_all_gbs"] if nv else 900.0) * 1e9
 
     def timed(fn, iters):
         if world > 1:
@@ -96,13 +110,18 @@ def main():
             # push = grad read + row read-modify-write (+ state RMW for AdaGrad)
             pull_bytes = n_eff * (128 + 2 * row_b)
             push_bytes = n_eff * (row_b * (3 + (2 if a.optimizer == "adagrad" else 0)))
-            roof_pull = max(pull_bytes / hbm, n_eff * remote * (128 + row_b) / nvlink) if world > 1 else pull_bytes / hbm
-            roof_push = max(push_bytes / hbm, n_eff * remote * row_b / nvlink) if world > 1 else push_bytes / hbm
+            roof_pull = max(pull_bytes / hbm, n_eff * remote * (128 + row_b) / nv_read) if world > 1 else pull_bytes / hbm
+            roof_push = max(push_bytes / hbm, n_eff * remote * row_b / nv_write) if world > 1 else push_bytes / hbm
+            nom_pull = max(pull_bytes / hbm, n_eff * remote * (128 + row_b) / 900e9) if world > 1 else pull_bytes / hbm
+            nom_push = max(push_bytes / hbm, n_eff * remote * row_b / 900e9) if world > 1 else push_bytes / hbm
             res = {"impl": impl, "n_gpus": world, "keys_per_batch_per_gpu": n_eff, "dim": a.dim, "optimizer": a.optimizer,
                    "pull_ms": ms_pull, "push_ms": ms_push,
                    "pull_keys_per_s_total": n_eff * world / (ms_pull * 1e-3),
                    "push_keys_per_s_total": n_eff * world / (ms_push * 1e-3),
-                   "pull_roofline_frac": roof_pull / (ms_pull * 1e-3), "push_roofline_frac": roof_push / (ms_push * 1e-3)}
+                   "pull_roofline_frac": roof_pull / (ms_pull * 1e-3), "push_roofline_frac": roof_push / (ms_push * 1e-3),
+                   "pull_frac_of_nominal_900": nom_pull / (ms_pull * 1e-3), "push_frac_of_nominal_900": nom_push / (ms_push * 1e-3),
+                   "nvlink_read_gbs_measured": nv["read_all_gbs"] if nv else None,
+                   "nvlink_write_gbs_measured": nv["write_all_gbs"] if nv else None}
             results.append(res)
             if rank == 0:
                 print(json.dumps(res), flush=True)

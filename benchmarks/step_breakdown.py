@@ -41,6 +41,8 @@ def main():
     inbox = getattr(table, "inbox", None)
     if inbox is not None and os.environ.get("SSB200_SHIP_FIRST") == "0":
         inbox.ship_first = False
+    if inbox is not None and os.environ.get("SSB200_OWN_STREAM") == "0":
+        inbox.own_stream = None
 
     def phase(name, fn):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -164,6 +164,8 @@ class Inbox:
         self.step = 0
         self.ship_first = True       # see push()
         self.wait_limit = 0          # iterations (~0.2 us each) the hand-off wait may spin; 0 = the library default (~27 s)
+        self.own_stream = torch.cuda.Stream(device=device)      # own-row updates run next to the shipment (None: in line)
+        self.own_done = torch.cuda.Event()
         self._C = C
         torch.cuda.synchronize(device)
         if self.group is not None:
@@ -205,6 +207,9 @@ class Inbox:
             rule = rule if rule is not None else ("adagrad" if adagrad else "sgd")
             rule = rule if isinstance(rule, _rules.Rule) else _rules.Rule.get(rule)
             hy = rule.hyper(lr=lr, eps=eps, **hyper)
+        if ship_first and self.own_stream is not None:
+            ev_ready = torch.cuda.Event()
+            ev_ready.record()              # the gradients are complete here (stream order): the side stream may start
         _lib.call("ssb_push_send2", self.table._view_ref(), view, gslot.data_ptr(), grads.data_ptr(), n,
                   _lib.ptr(n_dev), self.rank, float(lr), float(eps), -1 if ship_first else (1 if adagrad else 0),
                   1 if self.bf16_rows else 0, self.overflow.data_ptr(), self.cursor.data_ptr(), sp)
@@ -214,7 +219,17 @@ class Inbox:
         else:
             _lib.call("ssb_inbox_publish", view, self.world, self.rank, self.cursor.data_ptr(), 0, sp)
         if ship_first:         # my own rows
-            rule.push(self.table, gslot, grads, hy, n_dev=n_dev, zero_grads=False, n=n, only_shard=self.rank)
+            if self.own_stream is not None:
+                # next to the shipment, on a side stream: shipping is bound by NVLink, this update by HBM atomics
+                cur = torch.cuda.current_stream()
+                self.own_stream.wait_event(ev_ready)
+                with torch.cuda.stream(self.own_stream):
+                    rule.push(self.table, gslot, grads, hy, n_dev=n_dev, zero_grads=False, n=n, only_shard=self.rank)
+                    self.own_done.record()
+                gslot.record_stream(self.own_stream)
+                grads.record_stream(self.own_stream)
+            else:
+                rule.push(self.table, gslot, grads, hy, n_dev=n_dev, zero_grads=False, n=n, only_shard=self.rank)
         mark("own")
         return dict(par=par, step=self.step, ship_first=ship_first, rule=rule if ship_first else None, hy=hy if ship_first else None,
                     lr=lr, eps=eps, adagrad=adagrad, mark=mark)
@@ -229,6 +244,9 @@ class Inbox:
             import torch.distributed as dist         # barrier="nccl": the collective variant needs a torch.distributed job
 
             dist.all_reduce(self.token)      # every rank's shipment has landed in my inbox
+        if ship_first and self.own_stream is not None:
+            # own rows and inbox rows can be the same rows: the inbox apply (and its mirror refresh) goes after both
+            torch.cuda.current_stream().wait_event(self.own_done)
         mark("handoff")
         if self.bf16_rows and ship_first:
             rule.push_bf16_seg(self.local, self.slots_l[par], self.rows_l[par], self.seg_rows, self.count_l[par], self.world, hy)
