@@ -560,6 +560,74 @@ push_send_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__
   }
 }
 
+// Ship-only form of the send kernel (the own rows are applied by a separate launch next to it, cluster.Inbox): no
+// block-wide phases at all. A warp takes 32 gradient rows (one per lane), groups its lanes by owner
+// (__match_any_sync) so that each owner's cursor gets ONE local atomic per warp, then moves the remote rows four at
+// a time: four independent 512-byte reads in flight per warp, then four converted 256-byte peer stores.
+template <bool kBf16>
+__global__ void __launch_bounds__(256)
+push_ship_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__ SsbInboxView ib,
+                 const uint32_t* __restrict__ gslot, const float* __restrict__ grads, int64_t n,
+                 const uint32_t* __restrict__ n_dev, int self_shard, uint32_t* __restrict__ overflow,
+                 uint32_t* __restrict__ cursor) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t ne = effective_n(n, n_dev);
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const int D = v.dim;
+  for (uint32_t w0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; w0 < ne; w0 += warps * 32) {
+    const uint32_t r = w0 + lane;
+    const uint32_t g = r < ne ? __ldg(gslot + r) : SSB_INVALID_SLOT;
+    int o = -1;
+    uint32_t sl = 0;
+    if (g != SSB_INVALID_SLOT) { o = (int)(g / v.capacity); sl = g - (uint32_t)o * v.capacity; }
+    const bool remote = o >= 0 && o != self_shard;
+    const unsigned rm = __ballot_sync(0xffffffffu, remote);
+    if (!rm) continue;
+    // one cursor claim per (warp, owner)
+    const unsigned peers = __match_any_sync(0xffffffffu, remote ? o : -1);
+    const int leader = __ffs(peers) - 1;
+    uint32_t base = 0;
+    if (remote && lane == leader) base = cursor ? atomicAdd(cursor + o, (uint32_t)__popc(peers)) : atomicAdd(ib.count[o], (uint32_t)__popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    uint32_t idx = base + __popc(peers & ((1u << lane) - 1));
+    if (remote && idx >= ib.capacity) { atomicAdd(overflow, 1u); idx = 0xFFFFFFFFu; }
+    if (remote && idx != 0xFFFFFFFFu) ib.slots[o][idx] = sl;
+    unsigned todo = __ballot_sync(0xffffffffu, remote && idx != 0xFFFFFFFFu);
+    while (todo) {
+      int src[4];
+      float4 gv[4];
+      int cnt = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        src[k] = todo ? __ffs(todo) - 1 : -1;
+        if (todo) { todo &= todo - 1; ++cnt; }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (k < cnt)
+          for (int j = lane * 4; j < D && j < lane * 4 + 4; j += 4)       // D = 128: one float4 per lane
+            gv[k] = *reinterpret_cast<const float4*>(grads + (size_t)(w0 + src[k]) * D + j);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (k >= cnt) continue;
+        const int ok = __shfl_sync(0xffffffffu, o, src[k]);
+        const uint32_t ik = __shfl_sync(0xffffffffu, idx, src[k]);
+        if (D == 128) {
+          if (kBf16) *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(ib.rows[ok]) + (size_t)ik * D + lane * 4) = pack_bf16x4(gv[k]);
+          else *reinterpret_cast<float4*>(ib.rows[ok] + (size_t)ik * D + lane * 4) = gv[k];
+        } else {
+          const float* gr = grads + (size_t)(w0 + src[k]) * D;
+          for (int j = lane * 4; j < D; j += 128) {
+            const float4 x = *reinterpret_cast<const float4*>(gr + j);
+            if (kBf16) *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(ib.rows[ok]) + (size_t)ik * D + j) = pack_bf16x4(x);
+            else *reinterpret_cast<float4*>(ib.rows[ok] + (size_t)ik * D + j) = x;
+          }
+        }
+      }
+    }
+  }
+}
+
 // ---- chunked inbox push: ship and apply overlap -----------------------------------------------------
 // The inbox push above hands a whole shipment over at once (send -> publish counts -> wait for every sender ->
 // apply), so NVLink shipping and the owner's HBM update never overlap. Here a sender's sub-region is cut into
@@ -929,7 +997,11 @@ int ssb_push_send2(const SsbTableView* view, const SsbInboxView* inbox, const ui
 #define SSB_SEND(R, B) ssb::push_send_kernel<R, B><<<blocks, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, h, overflow, cursor)
   if (adagrad == 1) { if (bf16_rows) SSB_SEND(ssb::rule::AdaGrad, true); else SSB_SEND(ssb::rule::AdaGrad, false); }
   else if (adagrad == 0) { if (bf16_rows) SSB_SEND(ssb::rule::Sgd, true); else SSB_SEND(ssb::rule::Sgd, false); }
-  else if (adagrad == -1) { if (bf16_rows) SSB_SEND(ssb::ShipOnly, true); else SSB_SEND(ssb::ShipOnly, false); }
+  else if (adagrad == -1) {
+    const int sb = ssb::grid_for(n, 256, ssb::kNumSMs * 8);        // 8 warps x 32 rows per block trip
+    if (bf16_rows) ssb::push_ship_kernel<true><<<sb, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, overflow, cursor);
+    else ssb::push_ship_kernel<false><<<sb, 256, 0, (cudaStream_t)stream>>>(*view, *inbox, gslot, grads, n, n_dev, self_shard, overflow, cursor);
+  }
   else return (int)cudaErrorInvalidValue;
 #undef SSB_SEND
   SSB_LAUNCH_CHECK();

@@ -206,6 +206,24 @@ rule_push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restr
   const uint32_t ne = rule_effective_n(n, n_dev);
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
   const int D = v.dim;
+  if (only_shard >= 0 && (D & 3) == 0) {
+    // Most rows belong to other shards (7 of 8 at eight GPUs): a warp looks at 32 slots at once, one per lane, and
+    // then works through the ones its shard owns, instead of paying a dependent load per skipped row.
+    for (uint32_t w0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; w0 < ne; w0 += warps * 32) {
+      const uint32_t wl = w0 + lane;
+      const uint32_t gl = wl < ne ? __ldg(gslot + wl) : SSB_INVALID_SLOT;
+      unsigned mine = __ballot_sync(0xffffffffu, gl != SSB_INVALID_SLOT && (int)(gl / v.capacity) == only_shard);
+      while (mine) {
+        const int src = __ffs(mine) - 1;
+        mine &= mine - 1;
+        const uint32_t g = __shfl_sync(0xffffffffu, gl, src);
+        float* gr = grads + (size_t)(w0 + src) * D;
+        rule_apply_row<Rule, kShadow>(v, g, lane, h, [gr](int j) { return *reinterpret_cast<const float4*>(gr + j); },
+                                      zero_grads ? gr : nullptr);
+      }
+    }
+    return;
+  }
   for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
     const uint32_t g = __ldg(gslot + w);
     if (g == SSB_INVALID_SLOT) continue;
@@ -231,15 +249,31 @@ rule_push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restr
   }
 }
 
+// Which rows of a multi-writer launch really had a second writer. `seen[slot]` holds the tag of the last launch that
+// touched the slot: the first writer of a launch swaps its tag in and sees an older one, every later writer sees the
+// launch's own tag and appends the slot to `list`. Rows that are not on the list had ONE writer, so the mirror that
+// writer stored from its atomic's return value is final; only the listed rows (the hot words that every sender
+// carries) need the trailing refresh. count[tag & 1] counts the appends of this launch (more than max_list: the
+// refresh falls back to all rows); the refresh zeroes the other counter for the next launch. One-shard views only.
+struct MirrorTrack {
+  uint32_t* seen;        // [capacity], zero-initialised
+  uint32_t* list;        // [max_list]
+  uint32_t* count;       // [2], zero-initialised
+  uint32_t max_list;
+  uint32_t tag;          // != 0, different for every launch
+};
+
 // Owner-side apply of inbox segments whose gradient rows travelled as bf16 (half the NVLink bytes); the rule runs in
 // fp32 on fp32 rows / state. blockIdx.y = segment (one per sender): segment y holds rows
 // [y * seg_stride, y * seg_stride + n_dev[y]). Hot rows arrive from every sender, so a row can have several writers
-// in this launch: the mirror is NOT written here (see rule_mirror_refresh_kernel). D % 4 == 0.
-template <class Rule>
+// in this launch. kTrack = false: the mirror is NOT written here, rule_mirror_refresh_kernel rewrites it for every
+// row afterwards. kTrack = true: every writer stores the mirror from its atomic's return value and second writers
+// are recorded (MirrorTrack), so that the refresh only revisits rows that need it. D % 4 == 0.
+template <class Rule, bool kTrack>
 __global__ void __launch_bounds__(256)
 rule_push_bf16_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot,
                       const __nv_bfloat16* __restrict__ grads, int64_t n, const uint32_t* __restrict__ n_dev,
-                      const __grid_constant__ rule::Hyper h, int64_t seg_stride) {
+                      const __grid_constant__ rule::Hyper h, int64_t seg_stride, const __grid_constant__ MirrorTrack tr) {
   if (n_dev) n_dev += blockIdx.y;
   gslot += (size_t)blockIdx.y * seg_stride;
   grads += (size_t)blockIdx.y * seg_stride * v.dim;
@@ -250,8 +284,15 @@ rule_push_bf16_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __
   for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
     const uint32_t g = __ldg(gslot + w);
     if (g == SSB_INVALID_SLOT) continue;
+    if (kTrack) {
+      if (g >= v.capacity) continue;                                 // one-shard view: slot == global slot
+      if (lane == 0 && atomicExch(tr.seen + g, tr.tag) == tr.tag) {   // not the first writer of this launch
+        const uint32_t pos = atomicAdd(tr.count + (tr.tag & 1u), 1u);
+        if (pos < tr.max_list) tr.list[pos] = g;
+      }
+    }
     const __nv_bfloat16* gr = grads + (size_t)w * D;
-    rule_apply_row<Rule, false>(v, g, lane, h, [gr](int j) {
+    rule_apply_row<Rule, kTrack>(v, g, lane, h, [gr](int j) {
       const uint2 pk = *reinterpret_cast<const uint2*>(gr + j);
       const float2 a01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.x));
       const float2 a23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.y));
@@ -264,6 +305,43 @@ rule_push_bf16_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __
 // several writers per row: every writer of that launch is done, so whichever warp refreshes a row (a row listed by
 // three senders is refreshed three times) stores the same, final value — the mirror is bit-exactly bf16(row).
 // The rows were just written, so the reads are L2 hits.
+__device__ __forceinline__ void rule_refresh_row(const SsbTableView& v, uint32_t g, int lane) {
+  const int D = v.dim;
+  const uint32_t o = g / v.capacity, s = g - o * v.capacity;
+  if (o >= (uint32_t)v.num_shards || !v.shadow[o]) return;
+  const float* row = v.rows[o] + (size_t)s * D;
+  __nv_bfloat16* sh = reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)s * D;
+  if ((D & 3) == 0) {
+    for (int j = lane * 4; j < D; j += 128) *reinterpret_cast<uint2*>(sh + j) = rule_pack_bf16x4(ld_row_f4(row + j));
+  } else {
+    for (int j = lane; j < D; j += 32) sh[j] = __float2bfloat16_rn(ld_row_f1(row + j));
+  }
+}
+
+// The refresh after a TRACKED apply: only the rows on the list; all rows of the segments if the list overflowed.
+template <int kUnused = 0>
+__global__ void __launch_bounds__(256)
+rule_mirror_refresh_tracked_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot, int64_t n,
+                                   const uint32_t* __restrict__ n_dev, int64_t seg_stride, const __grid_constant__ MirrorTrack tr) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t cnt = tr.count[tr.tag & 1u];
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) tr.count[(tr.tag & 1u) ^ 1u] = 0u;     // for the next launch
+  if (cnt <= tr.max_list) {
+    const uint32_t warps = (gridDim.x * gridDim.y * blockDim.x) >> 5;
+    for (uint32_t i = ((blockIdx.y * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x) >> 5; i < cnt; i += warps)
+      rule_refresh_row(v, tr.list[i], lane);
+    return;
+  }
+  if (n_dev) n_dev += blockIdx.y;
+  gslot += (size_t)blockIdx.y * seg_stride;
+  const uint32_t ne = rule_effective_n(n, n_dev);
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
+    const uint32_t g = __ldg(gslot + w);
+    if (g != SSB_INVALID_SLOT) rule_refresh_row(v, g, lane);
+  }
+}
+
 template <int kUnused = 0>
 __global__ void __launch_bounds__(256)
 rule_mirror_refresh_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot, int64_t n,
@@ -274,18 +352,10 @@ rule_mirror_refresh_kernel(const __grid_constant__ SsbTableView v, const uint32_
   const uint32_t ne = rule_effective_n(n, n_dev);
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
   const int D = v.dim;
+  (void)D;
   for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
     const uint32_t g = __ldg(gslot + w);
-    if (g == SSB_INVALID_SLOT) continue;
-    const uint32_t o = g / v.capacity, s = g - o * v.capacity;
-    if (o >= (uint32_t)v.num_shards || !v.shadow[o]) continue;
-    const float* row = v.rows[o] + (size_t)s * D;
-    __nv_bfloat16* sh = reinterpret_cast<__nv_bfloat16*>(v.shadow[o]) + (size_t)s * D;
-    if ((D & 3) == 0) {
-      for (int j = lane * 4; j < D; j += 128) *reinterpret_cast<uint2*>(sh + j) = rule_pack_bf16x4(ld_row_f4(row + j));
-    } else {
-      for (int j = lane; j < D; j += 32) sh[j] = __float2bfloat16_rn(ld_row_f1(row + j));
-    }
+    if (g != SSB_INVALID_SLOT) rule_refresh_row(v, g, lane);
   }
 }
 
@@ -327,7 +397,7 @@ int launch_rule_push(const SsbTableView* view, const uint32_t* gslot, float* gra
 template <class Rule>
 int launch_rule_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, const void* grads_bf16, int64_t seg_rows,
                               const uint32_t* n_dev, int segments, int64_t seg_stride, const rule::Hyper* hyper, void* stream,
-                              int gx = 0) {
+                              int gx = 0, const MirrorTrack* track = nullptr) {
   if (int e = rule_check(view, Rule::kStateWords)) return e;
   if (!hyper || (view->dim & 3) || segments <= 0 || (segments > 1 && !n_dev)) return -1;
   if (seg_rows <= 0) return 0;
@@ -335,10 +405,15 @@ int launch_rule_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, c
   if (gx <= 0) gx = rule_grid(seg_rows) / segments;
   if (gx < 1) gx = 1;
   dim3 grid((unsigned)gx, (unsigned)segments);
-  rule_push_bf16_kernel<Rule><<<grid, 256, 0, s>>>(*view, gslot, reinterpret_cast<const __nv_bfloat16*>(grads_bf16), seg_rows,
-                                                   n_dev, *hyper, seg_stride);
-  if (rule_view_has_shadow(view))
-    rule_mirror_refresh_kernel<0><<<grid, 256, 0, s>>>(*view, gslot, seg_rows, n_dev, seg_stride, 1);
+  const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(grads_bf16);
+  const bool shadow = rule_view_has_shadow(view);
+  if (shadow && track && track->seen && track->list && track->count && track->tag != 0 && view->num_shards == 1) {
+    rule_push_bf16_kernel<Rule, true><<<grid, 256, 0, s>>>(*view, gslot, gb, seg_rows, n_dev, *hyper, seg_stride, *track);
+    rule_mirror_refresh_tracked_kernel<0><<<grid, 256, 0, s>>>(*view, gslot, seg_rows, n_dev, seg_stride, *track);
+    return (int)cudaGetLastError();
+  }
+  rule_push_bf16_kernel<Rule, false><<<grid, 256, 0, s>>>(*view, gslot, gb, seg_rows, n_dev, *hyper, seg_stride, MirrorTrack{});
+  if (shadow) rule_mirror_refresh_kernel<0><<<grid, 256, 0, s>>>(*view, gslot, seg_rows, n_dev, seg_stride, 1);
   return (int)cudaGetLastError();
 }
 
@@ -348,6 +423,7 @@ int launch_rule_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, c
 //   ssb_rule_<name>_info(int out[4])            -> {kStateWords, kInit, 0, 0}
 //   ssb_rule_<name>_push(...)                   -> fp32 gradient rows, local or direct-remote
 //   ssb_rule_<name>_push_bf16_seg(...)          -> owner-side apply of bf16 inbox segments
+//   ssb_rule_<name>_push_bf16_seg_tracked(...)  -> the same with second-writer tracking (MirrorTrack)
 #define SSB200_EXPORT_RULE(name, Rule)                                                                                      \
   extern "C" int ssb_rule_##name##_info(int32_t* out) {                                                                     \
     out[0] = Rule::kStateWords; out[1] = Rule::kInit; out[2] = 0; out[3] = 0;                                              \
@@ -363,4 +439,13 @@ int launch_rule_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, c
                                                  int64_t seg_stride, const ssb::rule::Hyper* hyper, void* stream) {        \
     return ssb::launch_rule_push_bf16_seg<Rule>(view, gslot, grads_bf16, seg_rows, n_dev, segments, seg_stride, hyper,      \
                                                 stream);                                                                   \
+  }                                                                                                                         \
+  extern "C" int ssb_rule_##name##_push_bf16_seg_tracked(const SsbTableView* view, const uint32_t* gslot,                   \
+                                                         const void* grads_bf16, int64_t seg_rows, const uint32_t* n_dev,   \
+                                                         int32_t segments, int64_t seg_stride,                              \
+                                                         const ssb::rule::Hyper* hyper, uint32_t* seen, uint32_t* list,     \
+                                                         uint32_t* count, uint32_t max_list, uint32_t tag, void* stream) {  \
+    const ssb::MirrorTrack tr{seen, list, count, max_list, tag};                                                            \
+    return ssb::launch_rule_push_bf16_seg<Rule>(view, gslot, grads_bf16, seg_rows, n_dev, segments, seg_stride, hyper,      \
+                                                stream, 0, &tr);                                                            \
   }

@@ -96,8 +96,8 @@ def build_kernels(verbose=False):
     os.makedirs(LIB_DIR, exist_ok=True)
     os.makedirs(OBJ_DIR, exist_ok=True)
     srcs = sorted(glob.glob(os.path.join(ROOT, "csrc", "kernels", "*.cu")))
-    hdrs = glob.glob(os.path.join(ROOT, "csrc", "kernels", "*.cuh")) + glob.glob(
-        os.path.join(ROOT, "include", "*.h"))
+    hdrs = (glob.glob(os.path.join(ROOT, "csrc", "kernels", "*.cuh")) + glob.glob(os.path.join(ROOT, "include", "*.h"))
+            + glob.glob(os.path.join(ROOT, "include", "*.cuh")))
     objs = []
     jobs = []
     for src in srcs:

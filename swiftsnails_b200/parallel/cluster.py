@@ -166,6 +166,13 @@ class Inbox:
         self.wait_limit = 0          # iterations (~0.2 us each) the hand-off wait may spin; 0 = the library default (~27 s)
         self.own_stream = torch.cuda.Stream(device=device)      # own-row updates run next to the shipment (None: in line)
         self.own_done = torch.cuda.Event()
+        # second-writer tracking of the inbox apply (ssb::MirrorTrack): only rows several senders carry get the
+        # trailing mirror refresh. None = refresh every applied row.
+        self.track = None
+        if shard.shadow is not None and self.bf16_rows:
+            self.track = (torch.zeros(table.capacity, dtype=torch.int32, device=device),
+                          torch.zeros(max(4096, self.capacity // 4), dtype=torch.int32, device=device),
+                          torch.zeros(2, dtype=torch.int32, device=device))
         self._C = C
         torch.cuda.synchronize(device)
         if self.group is not None:
@@ -249,7 +256,8 @@ class Inbox:
             torch.cuda.current_stream().wait_event(self.own_done)
         mark("handoff")
         if self.bf16_rows and ship_first:
-            rule.push_bf16_seg(self.local, self.slots_l[par], self.rows_l[par], self.seg_rows, self.count_l[par], self.world, hy)
+            rule.push_bf16_seg(self.local, self.slots_l[par], self.rows_l[par], self.seg_rows, self.count_l[par], self.world, hy,
+                               track=None if self.track is None else self.track + (ctx["step"],))
         elif self.bf16_rows:
             _lib.call("ssb_push_bf16_seg", self.local._view_ref(), self.slots_l[par].data_ptr(), self.rows_l[par].data_ptr(),
                       self.seg_rows, self.world, self.count_l[par].data_ptr(), float(lr), float(eps), 1 if adagrad else 0, sp)
