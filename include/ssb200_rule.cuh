@@ -206,24 +206,6 @@ rule_push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restr
   const uint32_t ne = rule_effective_n(n, n_dev);
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
   const int D = v.dim;
-  if (only_shard >= 0 && (D & 3) == 0) {
-    // Most rows belong to other shards (7 of 8 at eight GPUs): a warp looks at 32 slots at once, one per lane, and
-    // then works through the ones its shard owns, instead of paying a dependent load per skipped row.
-    for (uint32_t w0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; w0 < ne; w0 += warps * 32) {
-      const uint32_t wl = w0 + lane;
-      const uint32_t gl = wl < ne ? __ldg(gslot + wl) : SSB_INVALID_SLOT;
-      unsigned mine = __ballot_sync(0xffffffffu, gl != SSB_INVALID_SLOT && (int)(gl / v.capacity) == only_shard);
-      while (mine) {
-        const int src = __ffs(mine) - 1;
-        mine &= mine - 1;
-        const uint32_t g = __shfl_sync(0xffffffffu, gl, src);
-        float* gr = grads + (size_t)(w0 + src) * D;
-        rule_apply_row<Rule, kShadow>(v, g, lane, h, [gr](int j) { return *reinterpret_cast<const float4*>(gr + j); },
-                                      zero_grads ? gr : nullptr);
-      }
-    }
-    return;
-  }
   for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
     const uint32_t g = __ldg(gslot + w);
     if (g == SSB_INVALID_SLOT) continue;
@@ -249,18 +231,15 @@ rule_push_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restr
   }
 }
 
-// Which rows of a multi-writer launch really had a second writer. `seen[slot]` holds the tag of the last launch that
-// touched the slot: the first writer of a launch swaps its tag in and sees an older one, every later writer sees the
-// launch's own tag and appends the slot to `list`. Rows that are not on the list had ONE writer, so the mirror that
-// writer stored from its atomic's return value is final; only the listed rows (the hot words that every sender
-// carries) need the trailing refresh. count[tag & 1] counts the appends of this launch (more than max_list: the
-// refresh falls back to all rows); the refresh zeroes the other counter for the next launch. One-shard views only.
+// Which rows of a multi-writer launch really had a second writer. `seen[slot]` holds 2 * tag once a launch with that
+// tag has touched the slot and 2 * tag + 1 once it has touched it AGAIN (atomicMax: tags grow from launch to launch).
+// Rows that stay at 2 * tag had ONE writer, so the mirror that writer stored from its atomic's return value is final;
+// only the rows at 2 * tag + 1 (the hot words that every sender carries) need the trailing refresh, which walks the
+// slot lists again but touches the 768 bytes of a row only when its mark says so. No list, no shared counter.
+// One-shard views only (slot == global slot).
 struct MirrorTrack {
   uint32_t* seen;        // [capacity], zero-initialised
-  uint32_t* list;        // [max_list]
-  uint32_t* count;       // [2], zero-initialised
-  uint32_t max_list;
-  uint32_t tag;          // != 0, different for every launch
+  uint32_t tag;          // != 0, larger for every later launch, < 2^31
 };
 
 // Owner-side apply of inbox segments whose gradient rows travelled as bf16 (half the NVLink bytes); the rule runs in
@@ -286,10 +265,8 @@ rule_push_bf16_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __
     if (g == SSB_INVALID_SLOT) continue;
     if (kTrack) {
       if (g >= v.capacity) continue;                                 // one-shard view: slot == global slot
-      if (lane == 0 && atomicExch(tr.seen + g, tr.tag) == tr.tag) {   // not the first writer of this launch
-        const uint32_t pos = atomicAdd(tr.count + (tr.tag & 1u), 1u);
-        if (pos < tr.max_list) tr.list[pos] = g;
-      }
+      if (lane == 0 && atomicMax(tr.seen + g, 2u * tr.tag) >= 2u * tr.tag)     // not the first writer of this launch
+        atomicMax(tr.seen + g, 2u * tr.tag + 1u);
     }
     const __nv_bfloat16* gr = grads + (size_t)w * D;
     rule_apply_row<Rule, kTrack>(v, g, lane, h, [gr](int j) {
@@ -318,27 +295,28 @@ __device__ __forceinline__ void rule_refresh_row(const SsbTableView& v, uint32_t
   }
 }
 
-// The refresh after a TRACKED apply: only the rows on the list; all rows of the segments if the list overflowed.
+// The refresh after a TRACKED apply: walks the same slot lists, rewrites the mirror of the rows marked "several writers".
 template <int kUnused = 0>
 __global__ void __launch_bounds__(256)
 rule_mirror_refresh_tracked_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__ gslot, int64_t n,
                                    const uint32_t* __restrict__ n_dev, int64_t seg_stride, const __grid_constant__ MirrorTrack tr) {
   const int lane = threadIdx.x & 31;
-  const uint32_t cnt = tr.count[tr.tag & 1u];
-  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) tr.count[(tr.tag & 1u) ^ 1u] = 0u;     // for the next launch
-  if (cnt <= tr.max_list) {
-    const uint32_t warps = (gridDim.x * gridDim.y * blockDim.x) >> 5;
-    for (uint32_t i = ((blockIdx.y * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x) >> 5; i < cnt; i += warps)
-      rule_refresh_row(v, tr.list[i], lane);
-    return;
-  }
   if (n_dev) n_dev += blockIdx.y;
   gslot += (size_t)blockIdx.y * seg_stride;
   const uint32_t ne = rule_effective_n(n, n_dev);
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
-  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < ne; w += warps) {
-    const uint32_t g = __ldg(gslot + w);
-    if (g != SSB_INVALID_SLOT) rule_refresh_row(v, g, lane);
+  const uint32_t mark = 2u * tr.tag + 1u;
+  // a warp looks at 32 slots at once (one per lane) and then refreshes the marked ones together
+  for (uint32_t w0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; w0 < ne; w0 += warps * 32) {
+    const uint32_t wl = w0 + lane;
+    const uint32_t gl = wl < ne ? __ldg(gslot + wl) : SSB_INVALID_SLOT;
+    const bool hit = gl != SSB_INVALID_SLOT && gl < v.capacity && *reinterpret_cast<volatile const uint32_t*>(tr.seen + gl) == mark;
+    unsigned todo = __ballot_sync(0xffffffffu, hit);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      rule_refresh_row(v, __shfl_sync(0xffffffffu, gl, src), lane);
+    }
   }
 }
 
@@ -407,7 +385,7 @@ int launch_rule_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, c
   dim3 grid((unsigned)gx, (unsigned)segments);
   const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(grads_bf16);
   const bool shadow = rule_view_has_shadow(view);
-  if (shadow && track && track->seen && track->list && track->count && track->tag != 0 && view->num_shards == 1) {
+  if (shadow && track && track->seen && track->tag != 0 && view->num_shards == 1) {
     rule_push_bf16_kernel<Rule, true><<<grid, 256, 0, s>>>(*view, gslot, gb, seg_rows, n_dev, *hyper, seg_stride, *track);
     rule_mirror_refresh_tracked_kernel<0><<<grid, 256, 0, s>>>(*view, gslot, seg_rows, n_dev, seg_stride, *track);
     return (int)cudaGetLastError();
@@ -443,9 +421,9 @@ int launch_rule_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, c
   extern "C" int ssb_rule_##name##_push_bf16_seg_tracked(const SsbTableView* view, const uint32_t* gslot,                   \
                                                          const void* grads_bf16, int64_t seg_rows, const uint32_t* n_dev,   \
                                                          int32_t segments, int64_t seg_stride,                              \
-                                                         const ssb::rule::Hyper* hyper, uint32_t* seen, uint32_t* list,     \
-                                                         uint32_t* count, uint32_t max_list, uint32_t tag, void* stream) {  \
-    const ssb::MirrorTrack tr{seen, list, count, max_list, tag};                                                            \
+                                                         const ssb::rule::Hyper* hyper, uint32_t* seen, uint32_t tag,       \
+                                                         void* stream) {                                                    \
+    const ssb::MirrorTrack tr{seen, tag};                                                                                   \
     return ssb::launch_rule_push_bf16_seg<Rule>(view, gslot, grads_bf16, seg_rows, n_dev, segments, seg_stride, hyper,      \
                                                 stream, 0, &tr);                                                            \
   }

@@ -166,17 +166,22 @@ class Inbox:
         self.wait_limit = 0          # iterations (~0.2 us each) the hand-off wait may spin; 0 = the library default (~27 s)
         self.own_stream = torch.cuda.Stream(device=device)      # own-row updates run next to the shipment (None: in line)
         self.own_done = torch.cuda.Event()
-        # second-writer tracking of the inbox apply (ssb::MirrorTrack): only rows several senders carry get the
-        # trailing mirror refresh. None = refresh every applied row.
+        # Second-writer tracking of the inbox apply (ssb::MirrorTrack: only rows that several senders carry get the
+        # trailing mirror refresh) is available through enable_tracking() but off: with the tracked apply every
+        # writer needs the atomic's return value and stores the mirror itself, and about half of the incoming rows
+        # have a second writer anyway — measured 132 vs 119 us (2 ranks) and 246 vs 201 us (8 ranks) per apply of
+        # 152 K / 266 K rows (benchmarks/ship_probe.py). None = refresh every applied row.
         self.track = None
-        if shard.shadow is not None and self.bf16_rows:
-            self.track = (torch.zeros(table.capacity, dtype=torch.int32, device=device),
-                          torch.zeros(max(4096, self.capacity // 4), dtype=torch.int32, device=device),
-                          torch.zeros(2, dtype=torch.int32, device=device))
         self._C = C
         torch.cuda.synchronize(device)
         if self.group is not None:
             self.group.barrier()
+
+    def enable_tracking(self):
+        shard = self.local.owned[0]
+        if shard.shadow is not None and self.bf16_rows:
+            self.track = (torch.zeros(self.table.capacity, dtype=torch.int32, device=self.device),)
+        return self.track is not None
 
     def push(self, gslot, grads, lr, eps=1e-8, adagrad=True, n_dev=None, n=None, rule=None, **hyper):
         """``rule``: a named device-side update rule (ops.rules) instead of the built-in SGD / AdaGrad: the send

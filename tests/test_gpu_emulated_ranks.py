@@ -71,8 +71,9 @@ def test_sgd_keys_shared_between_senders(device, R, bf16_rows):
         assert ib.flags_l.tolist() == [3] * R                                   # every sender's hand-off flag carries step 3
 
 
+@pytest.mark.parametrize("tracked", [False, True])
 @pytest.mark.parametrize("rule,words,hy", [("adagrad", 1, dict(lr=0.05, eps=1e-8)), ("ftrl", 2, dict(lr=0.1, eps=1.0, a=0.01, b=0.0))])
-def test_named_rule_over_four_emulated_ranks_with_mirror(device, rule, words, hy):
+def test_named_rule_over_four_emulated_ranks_with_mirror(device, rule, words, hy, tracked):
     """Disjoint keys per sender -> an exact oracle for stateful rules; the table keeps a bf16 mirror, which must be
     bf16(row) bit for bit after own-row updates (single writer) and inbox applies (trailing refresh)."""
     from swiftsnails_b200.ops import rules
@@ -82,6 +83,8 @@ def test_named_rule_over_four_emulated_ranks_with_mirror(device, rule, words, hy
     R, dim = 4, 128
     rl = rules.Rule.get(rule)
     table, inboxes, _ = _setup(device, R, dim, 8192, 16384, words, True, shadow=True, init_kind=rl.init_kind)
+    if tracked:                                  # second-writer tracking: only multi-writer rows are refreshed
+        assert all(ib.enable_tracking() for ib in inboxes)
     rng = np.random.default_rng(1)
     pool = np.unique(rng.integers(0, 1 << 30, 8000).astype(np.uint32))
     parts = np.array_split(rng.permutation(pool), R)

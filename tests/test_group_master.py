@@ -37,10 +37,19 @@ CHILD = textwrap.dedent('''
 ''')
 
 
+def _free_port():
+    import socket
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
 def test_three_ranks_register_exchange_and_terminate_through_the_master(tmp_path, native_built):
     script = tmp_path / "child.py"
     script.write_text(CHILD % ROOT)
-    env = dict(os.environ, WORLD_SIZE="3", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(29000 + os.getpid() % 500),
+    port = _free_port() - 17                # group.init puts the master on MASTER_PORT + 17
+    env = dict(os.environ, WORLD_SIZE="3", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
                SSB200_MASTER_LOG=str(tmp_path / "master.log"))
     procs = [subprocess.Popen([sys.executable, str(script), str(tmp_path)], env=dict(env, RANK=str(r)),
                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for r in range(3)]
