@@ -70,10 +70,12 @@ class NcclShardedTable:
         cap = (int(n / W * self.slack) + 63) // 64 * 64 + 64
         bucketed, perm, counts, offsets = hashing.bucket_by_owner(keys, self.table.frag_map_dev, W)
         pos = torch.arange(n, device=keys.device, dtype=torch.int64)
-        owner = torch.searchsorted(offsets[1:W + 1].to(torch.int64).contiguous(), pos, right=True)
-        within = pos - offsets.to(torch.int64)[owner]
-        ok = within < cap
-        self.overflow += (~ok).sum()
+        off64 = offsets.to(torch.int64)
+        live = pos < off64[W]              # invalid (padding) keys are not routed: the bucketed list is shorter than n
+        owner = torch.searchsorted(off64[1:W + 1].contiguous(), pos, right=True).clamp_(max=W - 1)
+        within = pos - off64[owner]
+        ok = live & (within < cap)
+        self.overflow += (live & ~ok).sum()
         dst = torch.where(ok, owner * cap + within, torch.full_like(pos, W * cap))      # overflow -> a scratch slot
         send = torch.full((W * cap + 1,), -1, dtype=torch.int32, device=keys.device)
         send[dst] = bucketed
@@ -83,7 +85,9 @@ class NcclShardedTable:
             dist.all_to_all_single(recv, send)
         else:
             recv.copy_(send)
-        return {"perm": perm.long(), "dst": dst, "ok": ok, "cap": cap, "recv_keys": recv}
+        # positions past the routed keys hold no permutation entry: send them to a scratch row (index n)
+        perm_safe = torch.where(live, perm.long(), torch.full_like(pos, n))
+        return {"perm": perm_safe, "live": live, "dst": dst, "ok": ok, "cap": cap, "recv_keys": recv}
 
     def _pull_padded(self, keys, n, rows_out, rows_bf16, grads_zero, insert, want_fp32):
         plan = self._route_padded(keys[:n], n)
@@ -103,10 +107,12 @@ class NcclShardedTable:
         mine = back.index_select(0, plan["dst"])            # bucketed order
         if rows_out is None and want_fp32:
             rows_out = torch.empty((n, self.dim), dtype=torch.float32, device=keys.device)
+        tmp = torch.zeros((n + 1, self.dim), dtype=wire, device=keys.device)          # row n = scratch
+        tmp.index_copy_(0, plan["perm"], mine)
         if rows_out is not None:
-            rows_out[:n].index_copy_(0, plan["perm"], mine.to(torch.float32))
+            rows_out[:n].copy_(tmp[:n])
         if rows_bf16 is not None:
-            rows_bf16[:n].index_copy_(0, plan["perm"], mine.to(torch.bfloat16))
+            rows_bf16[:n].copy_(tmp[:n])
         if grads_zero is not None:
             grads_zero[:n].zero_()
         self._plan = (plan, n)
@@ -117,7 +123,7 @@ class NcclShardedTable:
         assert n_plan == n, "push must follow the pull of the same key set"
         W, cap = self.world, plan["cap"]
         wire = torch.bfloat16 if self.wire_bf16 else torch.float32
-        g = grads[:n].index_select(0, plan["perm"]).to(wire)
+        g = grads[:n].index_select(0, plan["perm"].clamp(max=n - 1)).to(wire) * plan["live"][:, None].to(wire)
         send = torch.zeros((W * cap + 1, self.dim), dtype=wire, device=grads.device)
         send[plan["dst"]] = g
         recv = torch.empty((W * cap, self.dim), dtype=wire, device=grads.device)
