@@ -33,6 +33,8 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--tc-ctas", type=int, default=-1, help="persistent CTAs of the tensor-core kernel (-1: 148 on one GPU, "
+                    "SSB200 default for several; 0: one per SM)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "nccl", "nccl_padded"],
                     help="nccl: all-to-all pull/push with exact splits (host sync per pull); nccl_padded: fixed buckets, no host sync, bf16 on the wire")
     ap.add_argument("--vocab", type=int, default=1_000_000)
@@ -61,6 +63,9 @@ def parse_args():
     ap.add_argument("--ref-minibatch-lines", default="8,32", help="reference arm: minibatch sizes (sentences) to sweep; the fastest run that trains is reported")
     ap.add_argument("--ref-tokens", type=int, default=204_800, help="tokens per worker for the reference arm")
     return ap.parse_args()
+
+
+DEFAULT_MULTI_GPU_TC_CTAS = 0      # persistent CTAs of the tensor-core kernel with several GPUs (0 = one per SM)
 
 
 def dist_env():
@@ -161,6 +166,9 @@ def run_ours(args):
     # batches are cycled through (the table keeps training, so no window repeats another's state).
     worker = Word2VecWorker(cfg, table, dev, pipeline=bool(args.pipeline) and args.impl == "ours")
     worker.tma_mode = args.tc_mode
+    tc_ctas = args.tc_ctas if args.tc_ctas >= 0 else (0 if world == 1 else DEFAULT_MULTI_GPU_TC_CTAS)
+    if tile_impl.startswith("tcgen05"):
+        _lib.call("ssb_sgns_tc_set_ctas", int(tc_ctas))
     dev_tokens = host.to(dev)
     nb = dev_tokens.shape[0]
     for s in range(W):
@@ -312,7 +320,7 @@ def run_ours(args):
                        "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if nccl_arm else "P2P"),
                        "bf16_row_mirror": with_shadow, "worker_slot_cache": bool(cfg.slot_cache),
                        "inbox_push": bool(use_inbox), "inbox_rows_bf16": bool(use_inbox and args.inbox_bf16),
-                       "inbox_handoff": args.inbox_barrier if use_inbox else None,
+                       "inbox_handoff": args.inbox_barrier if use_inbox else None, "tc_kernel_ctas": tc_ctas or 148,
                        "control_plane": {"single": "one process", "master": "swift_master over ZeroMQ (registration, route, fragment map, barriers); no torch.distributed / NCCL",
                                          "torch": "torch.distributed (NCCL)"}[grp.kind],
                        "same_switches_at_every_gpu_count": "slot cache, bf16 row mirror and bf16 inbox rows are on for every N; the inbox itself only exists with peers (N > 1)",

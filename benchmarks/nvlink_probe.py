@@ -39,7 +39,9 @@ def probe(grp, dev, mb=256, iters=5):
                 with torch.cuda.stream(st):
                     off = targets.index(p) * per
                     src, dst = (local.data_ptr() + off, pm.segment_ptr(p) + off) if write else (pm.segment_ptr(p) + off, local.data_ptr() + off)
-                    _lib.call("ssb_p2p_copy", src, dst, per, 148 * 4 // len(targets) or 1, _lib.stream_ptr())
+                    # every copy gets a full grid: the copies to different peers share the SMs, and a peer's share of
+                    # the loads in flight must not shrink with the number of peers (a divided grid under-measures)
+                    _lib.call("ssb_p2p_copy", src, dst, per, 148 * 4, _lib.stream_ptr())
             for st in streams[:len(targets)]:
                 cur.wait_stream(st)
         for _ in range(2):

@@ -861,6 +861,8 @@ extern "C" {
 // dedicated warps; 2 = perf experiment: skip the gradient reductions; 16 = perf experiment: skip the gather;
 // 64 = perf experiment: no tile-local dedup (every position reduces its own gradient row);
 // 8 = the round-1 serial kernel (sgns_tc_serial.cu; bit 4 = its diagonal epilogue).
+static int g_tc_ctas = [] { const char* e = getenv("SSB200_TC_CTAS"); return e ? atoi(e) : 0; }();   // 0 = one per SM
+
 static int launch_block_tc(const void* params, float* grads, int64_t n_rows, int32_t dim, const uint32_t* inv_in,
                            const uint32_t* inv_out, int64_t n_tok, int32_t sent_len, int32_t window, uint64_t seed,
                            uint64_t offset, const uint32_t* neg_idx, float neg_k, float* loss_out, int32_t mode,
@@ -889,12 +891,19 @@ static int launch_block_tc(const void* params, float* grads, int64_t n_rows, int
     attr_set[dev_id] = true;
   }
   int64_t tiles = (n_tok + kM - 1) / kM;
-  int blocks = (int)(tiles < ssb::kNumSMs ? tiles : ssb::kNumSMs);
+  // Persistent CTAs, one per SM. ssb_sgns_tc_set_ctas(n) (or SSB200_TC_CTAS) leaves 148 - n SMs entirely to the
+  // kernels of the other two pipeline stages: next to this kernel an SM only has room for one or two of their
+  // blocks, which starves the latency-bound NVLink loads / stores of a multi-GPU step.
+  int cap = g_tc_ctas > 0 ? g_tc_ctas : ssb::kNumSMs;
+  if (cap > ssb::kNumSMs) cap = ssb::kNumSMs;
+  int blocks = (int)(tiles < cap ? tiles : cap);
   if (debug) sgns_block_tc_kernel<true><<<blocks, kThreads, kSmemBytes, (cudaStream_t)stream>>>(a, tmap);
   else sgns_block_tc_kernel<false><<<blocks, kThreads, kSmemBytes, (cudaStream_t)stream>>>(a, tmap);
   SSB_LAUNCH_CHECK();
   return 0;
 }
+
+int ssb_sgns_tc_set_ctas(int32_t n) { g_tc_ctas = n; return 0; }
 
 int ssb_sgns_block_tc(const void* params, float* grads, int64_t n_rows, int32_t dim, const uint32_t* inv_in,
                       const uint32_t* inv_out, int64_t n_tok, int32_t sent_len, int32_t window, uint64_t seed,

@@ -237,6 +237,9 @@ int ssb_lr_fused_step(const SsbTableView *view, const uint32_t *keys, const floa
  * inv_in / inv_out [n_tok]: cache row of each token's input / output vector; neg_idx
  * [ceil(n_tok/128)*16]: cache rows of each tile's negatives; window <= 8.
  * mode: 0 = vector-load gather, 1 = TMA tile::gather4. box_rows must be 1; debug may be NULL. */
+/* Number of persistent CTAs of the tensor-core kernel (0 = one per SM = 148). Fewer leaves whole SMs to the pull /
+ * push kernels that run next to it in the pipelined multi-GPU step. Also: environment SSB200_TC_CTAS. */
+int ssb_sgns_tc_set_ctas(int32_t n);
 int ssb_sgns_block_tc(const void *params, float *grads, int64_t n_rows, int32_t dim,
                       const uint32_t *inv_in, const uint32_t *inv_out, int64_t n_tok,
                       int32_t sent_len, int32_t window, uint64_t seed, uint64_t offset,

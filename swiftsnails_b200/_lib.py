@@ -96,6 +96,7 @@ _KERNEL_SIGS = {
     "ssb_neg_sample": ([_vp, _vp, _u32, _u64, _u64, _u32, _vp, _i64, _vp], 1),
     "ssb_sgns_make_pairs": ([_vp, _vp, _i64, _i32, _i32, _u64, _u64, _vp, _vp, _vp, _vp], 1),
     "ssb_sgns_tiles": ([_vp, _vp, _i32, _vp, _vp, _vp, _i64, _vp, _i32, _f32, _vp, _vp], 1),
+    "ssb_sgns_tc_set_ctas": ([_i32], 0),
     "ssb_sgns_block_tc": ([_vp, _vp, _i64, _i32, _vp, _vp, _i64, _i32, _i32, _u64, _u64, _vp, _f32, _vp, _i32, _i32, _vp, _vp], 1),
     "ssb_sgns_block_tc_direct": ([_vp, _u64, _u32, _u32, _u32, _vp, _vp, _i32, _vp, _vp, _i64, _i32, _i32, _u64, _u64, _vp, _f32,
                                   _vp, _i32, _vp], 1),
