@@ -121,7 +121,8 @@ def run_ours(args):
         from swiftsnails_b200.parallel.cluster import attach_inbox
 
         n_keys_max = 2 * cfg.tokens_per_step + ((cfg.tokens_per_step + 127) // 128) * cfg.neg_pool
-        ib = attach_inbox(table, 2 * n_keys_max, bf16_rows=bool(args.inbox_bf16), barrier=args.inbox_barrier)
+        ib = attach_inbox(table, 2 * n_keys_max, bf16_rows=bool(args.inbox_bf16), barrier=args.inbox_barrier,
+                          owner_pulls=(None if os.environ.get("SSB200_OWNER_PULLS") is None else os.environ["SSB200_OWNER_PULLS"] != "0"))
         if os.environ.get("SSB200_SHIP_FIRST") == "0" and hasattr(ib, "ship_first"):
             ib.ship_first = False
         if os.environ.get("SSB200_OWN_STREAM") == "0" and hasattr(ib, "own_stream"):
@@ -320,7 +321,8 @@ def run_ours(args):
                        "parallelism": "ps%d (1 server shard + 1 worker per GPU, %s pull/push)" % (world, "NCCL all-to-all" if nccl_arm else "P2P"),
                        "bf16_row_mirror": with_shadow, "worker_slot_cache": bool(cfg.slot_cache),
                        "inbox_push": bool(use_inbox), "inbox_rows_bf16": bool(use_inbox and args.inbox_bf16),
-                       "inbox_handoff": args.inbox_barrier if use_inbox else None, "tc_kernel_ctas": tc_ctas or 148,
+                       "inbox_handoff": args.inbox_barrier if use_inbox else None,
+                       "inbox_rows_cross_nvlink_as": ("loads by the owner's apply kernel (senders fill local outboxes)" if getattr(getattr(table, "inbox", None), "owner_pulls", False) else "stores by the sender") if use_inbox else None, "tc_kernel_ctas": tc_ctas or 148,
                        "control_plane": {"single": "one process", "master": "swift_master over ZeroMQ (registration, route, fragment map, barriers); no torch.distributed / NCCL",
                                          "torch": "torch.distributed (NCCL)"}[grp.kind],
                        "same_switches_at_every_gpu_count": "slot cache, bf16 row mirror and bf16 inbox rows are on for every N; the inbox itself only exists with peers (N > 1)",

@@ -14,6 +14,7 @@ def main():
 
     R = int(sys.argv[1]) if len(sys.argv) > 1 else 2
     n = int(sys.argv[2]) if len(sys.argv) > 2 else 304000
+    pulls = (sys.argv[3] != "0") if len(sys.argv) > 3 else True
     dim, dev = 128, torch.device("cuda", 0)
     vocab = 2_000_000
     table = ShardedTable.local(round_capacity(vocab // R), dim, dev, num_shards=R, frag_num=1024, with_state=True, with_shadow=True)
@@ -21,14 +22,15 @@ def main():
     nbytes = Inbox.segment_bytes(cap_rows, dim, R, True)
     segs = [torch.zeros(nbytes, dtype=torch.uint8, device=dev) for _ in range(R)]
     ptrs = [t.data_ptr() for t in segs]
-    inboxes = [Inbox(table, cap_rows, dev, bf16_rows=True, world=R, rank=r, segment_ptrs=ptrs, local_shard=table.owned[r]) for r in range(R)]
+    inboxes = [Inbox(table, cap_rows, dev, bf16_rows=True, world=R, rank=r, segment_ptrs=ptrs, local_shard=table.owned[r],
+                     owner_pulls=pulls) for r in range(R)]
     rng = np.random.default_rng(0)
     keysets = [u32_tensor(rng.choice(vocab, n, replace=False).astype(np.uint32), dev) for _ in range(R)]
     gslots = [table.pull(k, want_fp32=False)[1] for k in keysets]
     grads = [torch.randn(n, dim, device=dev) * 0.01 for _ in range(R)]
     for ib in inboxes:
         ib.own_stream = None
-    out = {"ranks": R, "rows_per_rank": n}
+    out = {"ranks": R, "rows_per_rank": n, "owner_pulls": pulls}
     acc = {"send": 0.0, "own": 0.0, "handoff": 0.0, "apply": 0.0}
     reps = 8
     for it in range(reps + 2):

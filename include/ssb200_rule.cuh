@@ -337,6 +337,89 @@ rule_mirror_refresh_kernel(const __grid_constant__ SsbTableView v, const uint32_
   }
 }
 
+// ---- owner PULLS its gradient rows: apply straight from the senders' outboxes -------------------------------------
+// Measured on eight B200s: kernel STORES to seven peers at once move ~360 GB/s per GPU, kernel LOADS from seven peers
+// ~620 GB/s. So instead of every sender writing rows into the owners' inboxes, a sender compacts what it has for each
+// owner into ITS OWN memory (an outbox: local stores at HBM speed), raises the hand-off flags, and the owner's apply
+// kernel reads the rows over NVLink while it applies them — the shipment and the apply are one kernel, and the
+// rows cross the fabric as loads. src.rows[y] / src.slots[y] / src.count[y] point at sender y's sub-region FOR THIS
+// owner (peer memory); blockIdx.y = sender. A warp reads 32 slots with one coalesced load and keeps the next row's
+// 256 bytes in flight while it applies the current one. One-shard view (the owner's own shard); D % 4 == 0.
+__device__ __forceinline__ uint2 ld_peer_u2(const void* p) {
+  uint2 r;
+  asm volatile("ld.relaxed.sys.global.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ uint32_t ld_peer_u32(const uint32_t* p) {
+  uint32_t r;
+  asm volatile("ld.relaxed.sys.global.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ float4 rule_unpack_bf16x4(uint2 pk) {
+  const float2 a01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.x));
+  const float2 a23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.y));
+  return make_float4(a01.x, a01.y, a23.x, a23.y);
+}
+
+template <class Rule>
+__global__ void __launch_bounds__(256)
+rule_apply_outbox_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__ SsbInboxView src, int self,
+                         const __grid_constant__ rule::Hyper h) {
+  const int y = blockIdx.y;
+  if (y == self || !src.rows[y]) return;
+  const int lane = threadIdx.x & 31;
+  const int D = v.dim;
+  const uint32_t* slots = src.slots[y];
+  const __nv_bfloat16* rows = reinterpret_cast<const __nv_bfloat16*>(src.rows[y]);
+  uint32_t ne = ld_peer_u32(src.count[y]);
+  if (ne > src.capacity) ne = src.capacity;
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  for (uint32_t w0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; w0 < ne; w0 += warps * 32) {
+    const uint32_t nr = min(32u, ne - w0);
+    const uint32_t sl = (uint32_t)lane < nr ? ld_peer_u32(slots + w0 + lane) : SSB_INVALID_SLOT;
+    if (D == 128) {
+      uint2 cur = ld_peer_u2(rows + (size_t)w0 * D + lane * 4);
+      for (uint32_t k = 0; k < nr; ++k) {
+        uint2 nxt = make_uint2(0u, 0u);
+        if (k + 1 < nr) nxt = ld_peer_u2(rows + (size_t)(w0 + k + 1) * D + lane * 4);
+        const uint32_t g = __shfl_sync(0xffffffffu, sl, (int)k);
+        if (g < v.capacity) {
+          const float4 gv = rule_unpack_bf16x4(cur);
+          rule_apply_row<Rule, false>(v, g, lane, h, [gv](int) { return gv; }, nullptr);
+        }
+        cur = nxt;
+      }
+    } else {
+      for (uint32_t k = 0; k < nr; ++k) {
+        const uint32_t g = __shfl_sync(0xffffffffu, sl, (int)k);
+        if (g >= v.capacity) continue;
+        const __nv_bfloat16* gr = rows + (size_t)(w0 + k) * D;
+        rule_apply_row<Rule, false>(v, g, lane, h, [gr](int j) { return rule_unpack_bf16x4(ld_peer_u2(gr + j)); }, nullptr);
+      }
+    }
+  }
+}
+
+// mirror[slot] = bf16(row[slot]) for every slot the senders listed for this owner (after rule_apply_outbox_kernel).
+template <int kUnused = 0>
+__global__ void __launch_bounds__(256)
+rule_mirror_refresh_outbox_kernel(const __grid_constant__ SsbTableView v, const __grid_constant__ SsbInboxView src, int self) {
+  const int y = blockIdx.y;
+  if (y == self || !src.rows[y]) return;
+  const int lane = threadIdx.x & 31;
+  uint32_t ne = ld_peer_u32(src.count[y]);
+  if (ne > src.capacity) ne = src.capacity;
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  for (uint32_t w0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; w0 < ne; w0 += warps * 32) {
+    const uint32_t nr = min(32u, ne - w0);
+    const uint32_t sl = (uint32_t)lane < nr ? ld_peer_u32(src.slots[y] + w0 + lane) : SSB_INVALID_SLOT;
+    for (uint32_t k = 0; k < nr; ++k) {
+      const uint32_t g = __shfl_sync(0xffffffffu, sl, (int)k);
+      if (g < v.capacity) rule_refresh_row(v, g, lane);
+    }
+  }
+}
+
 // ---- host-side launchers -----------------------------------------------------------------------------------------
 inline int rule_grid(int64_t rows, int max_blocks_per_sm = 8) {
   int64_t b = (rows + 7) / 8;                  // 8 warps per block, one row per warp per trip
@@ -395,6 +478,25 @@ int launch_rule_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, c
   return (int)cudaGetLastError();
 }
 
+// Apply (and refresh the mirror) straight from the senders' outboxes. src: per sender y the sub-region it filled for
+// this owner; senders = world size; max_rows = rows a sub-region can hold (sizes the grid).
+template <class Rule>
+int launch_rule_apply_outbox(const SsbTableView* view, const SsbInboxView* src, int self, int senders, int64_t max_rows,
+                             const rule::Hyper* hyper, void* stream) {
+  if (int e = rule_check(view, Rule::kStateWords)) return e;
+  if (!hyper || !src || (view->dim & 3) || view->num_shards != 1 || senders < 1 || senders > SSB_MAX_SHARDS) return -1;
+  if (senders == 1) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  int gx = (int)((max_rows + 255) / 256);                 // a block trip covers 8 warps x 32 rows
+  const int cap = 148 * 8 / (senders > 2 ? 2 : 1);
+  if (gx > cap) gx = cap;
+  if (gx < 1) gx = 1;
+  dim3 grid((unsigned)gx, (unsigned)senders);
+  rule_apply_outbox_kernel<Rule><<<grid, 256, 0, s>>>(*view, *src, self, *hyper);
+  if (rule_view_has_shadow(view)) rule_mirror_refresh_outbox_kernel<0><<<grid, 256, 0, s>>>(*view, *src, self);
+  return (int)cudaGetLastError();
+}
+
 }  // namespace ssb
 
 // extern "C" entry points of a rule, found by name from Python (ops/rules.py):
@@ -402,6 +504,7 @@ int launch_rule_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, c
 //   ssb_rule_<name>_push(...)                   -> fp32 gradient rows, local or direct-remote
 //   ssb_rule_<name>_push_bf16_seg(...)          -> owner-side apply of bf16 inbox segments
 //   ssb_rule_<name>_push_bf16_seg_tracked(...)  -> the same with second-writer tracking (MirrorTrack)
+//   ssb_rule_<name>_apply_outbox(...)           -> owner-side apply that READS the rows from the senders' outboxes
 #define SSB200_EXPORT_RULE(name, Rule)                                                                                      \
   extern "C" int ssb_rule_##name##_info(int32_t* out) {                                                                     \
     out[0] = Rule::kStateWords; out[1] = Rule::kInit; out[2] = 0; out[3] = 0;                                              \
@@ -417,6 +520,11 @@ int launch_rule_push_bf16_seg(const SsbTableView* view, const uint32_t* gslot, c
                                                  int64_t seg_stride, const ssb::rule::Hyper* hyper, void* stream) {        \
     return ssb::launch_rule_push_bf16_seg<Rule>(view, gslot, grads_bf16, seg_rows, n_dev, segments, seg_stride, hyper,      \
                                                 stream);                                                                   \
+  }                                                                                                                         \
+  extern "C" int ssb_rule_##name##_apply_outbox(const SsbTableView* view, const SsbInboxView* src, int32_t self,            \
+                                                int32_t senders, int64_t max_rows, const ssb::rule::Hyper* hyper,          \
+                                                void* stream) {                                                            \
+    return ssb::launch_rule_apply_outbox<Rule>(view, src, self, senders, max_rows, hyper, stream);                          \
   }                                                                                                                         \
   extern "C" int ssb_rule_##name##_push_bf16_seg_tracked(const SsbTableView* view, const uint32_t* gslot,                   \
                                                          const void* grads_bf16, int64_t seg_rows, const uint32_t* n_dev,   \

@@ -23,7 +23,7 @@ def _bf16(x):
     return torch.from_numpy(np.ascontiguousarray(x)).to(torch.bfloat16).to(torch.float32).numpy()
 
 
-def _setup(device, R, dim, cap_rows, inbox_rows, state_words, bf16_rows, shadow=False, init_kind=0):
+def _setup(device, R, dim, cap_rows, inbox_rows, state_words, bf16_rows, shadow=False, init_kind=0, owner_pulls=None):
     from swiftsnails_b200.ops.table import ShardedTable
     from swiftsnails_b200.parallel.cluster import Inbox
 
@@ -33,18 +33,19 @@ def _setup(device, R, dim, cap_rows, inbox_rows, state_words, bf16_rows, shadow=
     segs = [torch.zeros(nbytes, dtype=torch.uint8, device=device) for _ in range(R)]
     ptrs = [t.data_ptr() for t in segs]
     inboxes = [Inbox(table, inbox_rows, device, bf16_rows=bf16_rows, world=R, rank=r, segment_ptrs=ptrs,
-                     local_shard=table.owned[r]) for r in range(R)]
+                     local_shard=table.owned[r], owner_pulls=owner_pulls) for r in range(R)]
     return table, inboxes, segs
 
 
-@pytest.mark.parametrize("R,bf16_rows", [(2, True), (4, True), (4, False)])
-def test_sgd_keys_shared_between_senders(device, R, bf16_rows):
+@pytest.mark.parametrize("R,bf16_rows,owner_pulls", [(2, True, True), (4, True, True), (4, True, False), (4, False, False)])
+def test_sgd_keys_shared_between_senders(device, R, bf16_rows, owner_pulls):
     """SGD is order-independent: w = w0 - lr * (sum of the gradients), where a gradient that crossed to another owner
     as bf16 was rounded on the wire and one applied by its own owner stayed fp32. Three steps = both parities."""
     from swiftsnails_b200.ops._util import to_u32_numpy, u32_tensor
 
     dim, lr = 64, 0.5
-    table, inboxes, _ = _setup(device, R, dim, 8192, 16384, 0, bf16_rows)
+    table, inboxes, _ = _setup(device, R, dim, 8192, 16384, 0, bf16_rows, owner_pulls=owner_pulls)
+    assert all(ib.owner_pulls == owner_pulls for ib in inboxes)     # outbox + owner reads, or inbox + owner applies local rows
     rng = np.random.default_rng(0)
     pool = np.unique(rng.integers(0, 1 << 30, 6000).astype(np.uint32))
     w0, _ = table.pull(u32_tensor(pool, device))
@@ -71,9 +72,9 @@ def test_sgd_keys_shared_between_senders(device, R, bf16_rows):
         assert ib.flags_l.tolist() == [3] * R                                   # every sender's hand-off flag carries step 3
 
 
-@pytest.mark.parametrize("tracked", [False, True])
+@pytest.mark.parametrize("path", ["owner_pulls", "inbox", "inbox_tracked"])
 @pytest.mark.parametrize("rule,words,hy", [("adagrad", 1, dict(lr=0.05, eps=1e-8)), ("ftrl", 2, dict(lr=0.1, eps=1.0, a=0.01, b=0.0))])
-def test_named_rule_over_four_emulated_ranks_with_mirror(device, rule, words, hy, tracked):
+def test_named_rule_over_four_emulated_ranks_with_mirror(device, rule, words, hy, path):
     """Disjoint keys per sender -> an exact oracle for stateful rules; the table keeps a bf16 mirror, which must be
     bf16(row) bit for bit after own-row updates (single writer) and inbox applies (trailing refresh)."""
     from swiftsnails_b200.ops import rules
@@ -82,8 +83,9 @@ def test_named_rule_over_four_emulated_ranks_with_mirror(device, rule, words, hy
 
     R, dim = 4, 128
     rl = rules.Rule.get(rule)
-    table, inboxes, _ = _setup(device, R, dim, 8192, 16384, words, True, shadow=True, init_kind=rl.init_kind)
-    if tracked:                                  # second-writer tracking: only multi-writer rows are refreshed
+    table, inboxes, _ = _setup(device, R, dim, 8192, 16384, words, True, shadow=True, init_kind=rl.init_kind,
+                               owner_pulls=(path == "owner_pulls"))
+    if path == "inbox_tracked":                  # second-writer tracking: only multi-writer rows are refreshed
         assert all(ib.enable_tracking() for ib in inboxes)
     rng = np.random.default_rng(1)
     pool = np.unique(rng.integers(0, 1 << 30, 8000).astype(np.uint32))
@@ -125,7 +127,7 @@ def test_overflow_is_counted_and_a_silent_sender_is_reported_not_trapped(device)
     from swiftsnails_b200.ops._util import u32_tensor
 
     R, dim = 2, 64
-    table, inboxes, _ = _setup(device, R, dim, 8192, 512, 0, True)              # 256 rows per (owner, sender)
+    table, inboxes, _ = _setup(device, R, dim, 8192, 512, 0, True)              # 256 rows per (owner, sender); owner-pull path
     keys = np.unique(np.random.default_rng(2).integers(0, 1 << 30, 4000).astype(np.uint32))
     _, gslot = table.pull(u32_tensor(keys, device))
     g = torch.randn(len(keys), dim, device=device)
