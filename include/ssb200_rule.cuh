@@ -378,16 +378,27 @@ rule_apply_outbox_kernel(const __grid_constant__ SsbTableView v, const __grid_co
     const uint32_t nr = min(32u, ne - w0);
     const uint32_t sl = (uint32_t)lane < nr ? ld_peer_u32(slots + w0 + lane) : SSB_INVALID_SLOT;
     if (D == 128) {
-      uint2 cur = ld_peer_u2(rows + (size_t)w0 * D + lane * 4);
-      for (uint32_t k = 0; k < nr; ++k) {
-        uint2 nxt = make_uint2(0u, 0u);
-        if (k + 1 < nr) nxt = ld_peer_u2(rows + (size_t)(w0 + k + 1) * D + lane * 4);
-        const uint32_t g = __shfl_sync(0xffffffffu, sl, (int)k);
-        if (g < v.capacity) {
-          const float4 gv = rule_unpack_bf16x4(cur);
-          rule_apply_row<Rule, false>(v, g, lane, h, [gv](int) { return gv; }, nullptr);
+      // rows in groups of kAhead: the next group's loads (kAhead x 256 bytes per warp) are in flight over NVLink while
+      // the current group is applied (each row's update waits on an atomic's round trip to local HBM)
+      constexpr uint32_t kAhead = 4;
+      uint2 cur[kAhead], nxt[kAhead];
+#pragma unroll
+      for (uint32_t i = 0; i < kAhead; ++i) cur[i] = i < nr ? ld_peer_u2(rows + (size_t)(w0 + i) * D + lane * 4) : make_uint2(0u, 0u);
+      for (uint32_t k0 = 0; k0 < nr; k0 += kAhead) {
+#pragma unroll
+        for (uint32_t i = 0; i < kAhead; ++i)
+          nxt[i] = (k0 + kAhead + i < nr) ? ld_peer_u2(rows + (size_t)(w0 + k0 + kAhead + i) * D + lane * 4) : make_uint2(0u, 0u);
+#pragma unroll
+        for (uint32_t i = 0; i < kAhead; ++i) {
+          if (k0 + i >= nr) break;
+          const uint32_t g = __shfl_sync(0xffffffffu, sl, (int)(k0 + i));
+          if (g < v.capacity) {
+            const float4 gv = rule_unpack_bf16x4(cur[i]);
+            rule_apply_row<Rule, false>(v, g, lane, h, [gv](int) { return gv; }, nullptr);
+          }
         }
-        cur = nxt;
+#pragma unroll
+        for (uint32_t i = 0; i < kAhead; ++i) cur[i] = nxt[i];
       }
     } else {
       for (uint32_t k = 0; k < nr; ++k) {
