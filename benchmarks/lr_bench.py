@@ -18,6 +18,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--feature-bits", type=int, default=28)
     ap.add_argument("--fused", type=int, default=1)
+    ap.add_argument("--feature-major", type=int, default=1, help="minibatches stored feature by feature ([39, B]): coalesced loads in the fused kernel")
     ap.add_argument("--optimizer", default="adagrad")
     a = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -25,13 +26,16 @@ def main():
     from swiftsnails_b200.parallel import group as ps_group
     grp = ps_group.init("master")            # ranks register with swift_master over ZeroMQ; no torch.distributed
     rank = grp.rank
-    cfg = LRConfig(feature_bits=a.feature_bits, batch_size=a.batch, fused=bool(a.fused), optimizer=a.optimizer)
+    fm = bool(a.feature_major) and bool(a.fused)
+    cfg = LRConfig(feature_bits=a.feature_bits, batch_size=a.batch, fused=bool(a.fused), optimizer=a.optimizer, feature_major=fm)
     # touched features are far fewer than 2^28; size the table for 64M rows in total
     table = make_table((1 << 26) // world, 1, dev, with_state=(2 if a.optimizer == "ftrl" else True), init_scale=0.0,
                        frag_num=max(1024, world))
     w = LRWorker(cfg, table, dev)
     n_batches = 4
     data = [criteo_like_batch(cfg, a.batch, seed=1000 * rank + b) for b in range(n_batches)]
+    if fm:            # the data pipeline hands the minibatch over feature by feature
+        data = [(np.ascontiguousarray(k.T), np.ascontiguousarray(v.T), y) for k, v, y in data]
     dev_data = [(u32_tensor(k, dev), torch.from_numpy(v).to(dev), torch.from_numpy(y).to(dev)) for k, v, y in data]
     for s in range(a.warmup):
         w.step(*dev_data[s % n_batches])
@@ -50,7 +54,7 @@ def main():
         print(json.dumps({"bench": "sparse_lr_adagrad", "n_gpus": world, "feature_bits": a.feature_bits, "batch_per_gpu": a.batch,
                           "features_per_example": cfg.n_feat, "ms_per_step": ms / a.steps, "examples_per_s": ex / (ms * 1e-3),
                           "feature_keys_per_s": ex * cfg.n_feat / (ms * 1e-3), "unique_keys_last_step": int(w.n_unique.item()),
-                          "mean_loss": w.mean_loss(), "fused": bool(a.fused), "optimizer": a.optimizer, "health": w.health(),
+                          "mean_loss": w.mean_loss(), "fused": bool(a.fused), "feature_major": fm, "optimizer": a.optimizer, "health": w.health(),
                           "phase_us_last_step": (w.fused.phase_us() if w.fused is not None else None)}))
     torch.cuda.synchronize()
     grp.barrier()

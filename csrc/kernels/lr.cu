@@ -97,8 +97,9 @@ namespace lrf {
 
 struct Args {
   SsbTableView v;
-  const uint32_t* keys;      // [n_ex][n_feat]; SSB_EMPTY_KEY = no feature in this position
-  const float* x;            // [n_ex][n_feat] or nullptr (all ones)
+  const uint32_t* keys;      // [n_ex][n_feat] (or [n_feat][n_ex] when feature_major); SSB_EMPTY_KEY = no feature in this position
+  const float* x;            // same layout as keys, or nullptr (all ones)
+  int feature_major;         // 1: keys / x are stored feature by feature, so that the 32 examples of a warp are contiguous
   const float* labels;       // [n_ex] in {0, 1}
   int64_t n_ex;
   int n_feat;
@@ -220,7 +221,10 @@ lr_fused_step_kernel(const __grid_constant__ Args a) {
   for (int64_t c = next_chunk(a.counters + 4, lane); c < chunks; c = next_chunk(a.counters + 4, lane)) {
     const int64_t e = c * 32 + lane;
     const bool live = e < n_ex;
-    const uint32_t* ke = a.keys + (live ? e : 0) * F;
+    // element (e, f): example-major [e][f] (lanes 4 * n_feat bytes apart: a sector per key) or feature-major [f][e]
+    // (32 consecutive keys per load)
+    const size_t ks_e = a.feature_major ? 1 : (size_t)F, ks_f = a.feature_major ? (size_t)n_ex : 1;
+    const uint32_t* ke = a.keys + (live ? (size_t)e : 0) * ks_e;
     // warps start at different feature groups, so the features every example has (the numeric fields) are not hit
     // by all warps at the same moment: the first warp installs the tag, the others then see it with a plain load
     const int rot = (int)(c % n_groups);
@@ -232,7 +236,7 @@ lr_fused_step_kernel(const __grid_constant__ Args a) {
       bool valid[kGroup];
 #pragma unroll
       for (int g = 0; g < kGroup; ++g) {
-        key[g] = (live && f0 + g < F) ? __ldg(ke + f0 + g) : SSB_EMPTY_KEY;
+        key[g] = (live && f0 + g < F) ? __ldg(ke + (size_t)(f0 + g) * ks_f) : SSB_EMPTY_KEY;
         valid[g] = key[g] < SSB_LOCKED_KEY;
       }
       if (a.dense_keys) {
@@ -325,12 +329,13 @@ lr_fused_step_kernel(const __grid_constant__ Args a) {
   for (int64_t c = next_chunk(a.counters + 5, lane); c < chunks; c = next_chunk(a.counters + 5, lane)) {
     const int64_t e = c * 32 + lane;
     const bool live = e < n_ex;
-    const float* xe = a.x ? a.x + (live ? e : 0) * F : nullptr;
+    const size_t xs_e = a.feature_major ? 1 : (size_t)F, xs_f = a.feature_major ? (size_t)n_ex : 1;
+    const float* xe = a.x ? a.x + (live ? (size_t)e : 0) * xs_e : nullptr;
     float z = 0.f;
 #pragma unroll 4
     for (int f = 0; f < F; ++f) {
       const uint32_t idx = live ? a.stash[(size_t)f * n_ex + e] : SSB_INVALID_SLOT;
-      if (idx != SSB_INVALID_SLOT) z += ld_strong_f32(a.wc + idx) * (xe ? __ldg(xe + f) : 1.0f);
+      if (idx != SSB_INVALID_SLOT) z += ld_strong_f32(a.wc + idx) * (xe ? __ldg(xe + (size_t)f * xs_f) : 1.0f);
     }
     float g = 0.f;
     if (live) {
@@ -341,7 +346,7 @@ lr_fused_step_kernel(const __grid_constant__ Args a) {
 #pragma unroll 2
     for (int f = 0; f < F; ++f) {
       const uint32_t idx = live ? a.stash[(size_t)f * n_ex + e] : SSB_INVALID_SLOT;
-      float cgrad = (idx != SSB_INVALID_SLOT) ? g * (xe ? __ldg(xe + f) : 1.0f) : 0.f;
+      float cgrad = (idx != SSB_INVALID_SLOT) ? g * (xe ? __ldg(xe + (size_t)f * xs_f) : 1.0f) : 0.f;
       uint32_t tgt = idx;
       // a feature the whole warp shares (a numeric field): one add for the warp
       const uint32_t idx0 = __shfl_sync(0xffffffffu, idx, 0);
@@ -439,12 +444,15 @@ extern "C" int ssb_lr_fused_step(const SsbTableView* view, const uint32_t* keys,
                                  int32_t n_feat, void* entries, uint64_t dense_keys, uint32_t* stash, uint32_t* touched,
                                  float* wc, float* gc, uint32_t max_touched, uint32_t* counters, uint32_t step, float* loss_out,
                                  int32_t rule_id, const void* hyper, int32_t blocks_per_sm, void* stream) {
+  // blocks_per_sm bit 30: keys / x are feature-major ([n_feat][n_ex])
+  const int feature_major = (blocks_per_sm >> 30) & 1;
+  blocks_per_sm &= 0x3FFFFFFF;
   if (!view || view->dim != 1 || !keys || !labels || n_feat < 1 || !entries || !stash || !touched || !wc || !gc || !counters ||
       !loss_out || !hyper || step == 0 || max_touched == 0)
     return (int)cudaErrorInvalidValue;
   if (n_ex <= 0) return 0;
   ssb::lrf::Args a;
-  a.v = *view; a.keys = keys; a.x = x; a.labels = labels; a.n_ex = n_ex; a.n_feat = n_feat;
+  a.v = *view; a.keys = keys; a.x = x; a.labels = labels; a.n_ex = n_ex; a.n_feat = n_feat; a.feature_major = feature_major;
   a.ent = reinterpret_cast<uint4*>(entries); a.dense_keys = dense_keys; a.stash = stash; a.touched = touched; a.wc = wc; a.gc = gc;
   a.max_touched = max_touched; a.counters = counters; a.step = step; a.loss_out = loss_out;
   a.h = *static_cast<const ssb::rule::Hyper*>(hyper);

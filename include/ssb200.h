@@ -224,7 +224,8 @@ int ssb_lr_fwd_bwd(const float *params, float *grads, const uint32_t *inv, const
  * (gc zeroed once; max_touched >= n_ex * n_feat is always enough); counters[16] (out: [0] compact indices used,
  * [2] index overflow, [3] keys without a slot — both must stay 0; [8..12] globaltimer stamps of the phases).
  * step: non-zero, different from every earlier call's. rule_id: 0 SGD, 1 AdaGrad, 2 FTRL; hyper points to an
- * ssb::rule::Hyper {lr, eps, a, b, c, step}. blocks_per_sm: 0 = as many as fit.
+ * ssb::rule::Hyper {lr, eps, a, b, c, step}. blocks_per_sm: 0 = as many as fit; bit 30 set: keys / x are FEATURE-major
+ * ([n_feat][n_ex]: the 32 examples a warp works on are contiguous, so its loads are coalesced).
  * ref: core/framework/SwiftWorker.h:19-57 (the worker loop), parameter/sparse_access_method.h:33-46. */
 int ssb_lr_fused_step(const SsbTableView *view, const uint32_t *keys, const float *x, const float *labels, int64_t n_ex,
                       int32_t n_feat, void *entries, uint64_t dense_keys, uint32_t *stash, uint32_t *touched, float *wc,

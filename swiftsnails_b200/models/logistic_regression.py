@@ -32,6 +32,7 @@ class LRConfig:
     l1: float = 0.0                 # FTRL only
     l2: float = 0.0
     fused: bool = True              # one cooperative kernel per step (K6 fused) instead of dedup -> pull -> fwd/bwd -> push
+    feature_major: bool = False     # step() is given keys / vals as [n_feat, B] (coalesced loads in the fused kernel)
 
     @property
     def n_feat(self):
@@ -93,7 +94,7 @@ class LRWorker:
             hy = dict(lr=cfg.lr, eps=cfg.adagrad_eps)
             if cfg.optimizer == "ftrl":
                 hy = dict(lr=cfg.lr, eps=1.0, a=cfg.l1, b=cfg.l2)
-            lr_ops.lr_fused_step(self.fused, keys, vals, labels, self.loss, rule=cfg.optimizer, **hy)
+            lr_ops.lr_fused_step(self.fused, keys, vals, labels, self.loss, rule=cfg.optimizer, feature_major=cfg.feature_major, **hy)
             return self.loss
         if cfg.optimizer != "adagrad":
             raise ValueError("the unfused path implements AdaGrad only; use fused=True for %r" % cfg.optimizer)

@@ -49,9 +49,10 @@ class FusedLRState:
         return sum(t.numel() * 4 for t in (self.entries, self.stash, self.touched, self.wc, self.gc))
 
 
-def lr_fused_step(state: FusedLRState, keys, x, labels, loss_out, rule="adagrad", blocks_per_sm=0, **hyper):
+def lr_fused_step(state: FusedLRState, keys, x, labels, loss_out, rule="adagrad", blocks_per_sm=0, feature_major=False, **hyper):
     """One training step. keys int32 [B, n_feat] (uint32 bits, -1 = empty position), x float32 [B, n_feat] or None,
-    labels float32 [B]; hyper = lr, eps, a, b (ops.rules.Hyper)."""
+    labels float32 [B]; hyper = lr, eps, a, b (ops.rules.Hyper). ``feature_major``: keys / x are [n_feat, B] instead
+    (the minibatch stored feature by feature: a warp's 32 examples are contiguous, its loads coalesced)."""
     from .rules import Hyper
     import ctypes as C
 
@@ -66,4 +67,5 @@ def lr_fused_step(state: FusedLRState, keys, x, labels, loss_out, rule="adagrad"
     _lib.call("ssb_lr_fused_step", t._view_ref(), keys.data_ptr(), None if x is None else x.data_ptr(), labels.data_ptr(),
               n_ex, state.n_feat, state.entries.data_ptr(), state.dense_keys, state.stash.data_ptr(), state.touched.data_ptr(),
               state.wc.data_ptr(), state.gc.data_ptr(), state.max_touched, state.counters.data_ptr(), state.step,
-              loss_out.data_ptr(), RULE_IDS[rule], C.addressof(hy), int(blocks_per_sm), _lib.stream_ptr())
+              loss_out.data_ptr(), RULE_IDS[rule], C.addressof(hy), int(blocks_per_sm) | ((1 << 30) if feature_major else 0),
+              _lib.stream_ptr())

@@ -55,8 +55,8 @@ def _oracle_step(w, st, keys, x, y, rule, hy):
 
 @pytest.mark.parametrize("rule,hy,words", [("sgd", dict(lr=0.01), 0), ("adagrad", dict(lr=0.05, eps=1e-6), 1),
                                            ("ftrl", dict(lr=0.1, eps=1.0, a=0.05, b=0.01), 2)])
-@pytest.mark.parametrize("use_map", [True, False])
-def test_fused_step_matches_the_minibatch_oracle(device, rule, hy, words, use_map):
+@pytest.mark.parametrize("use_map,feature_major", [(True, False), (False, False), (True, True)])
+def test_fused_step_matches_the_minibatch_oracle(device, rule, hy, words, use_map, feature_major):
     from swiftsnails_b200.ops import lr as lr_ops
     from swiftsnails_b200.ops._util import u32_tensor
     from swiftsnails_b200.ops.table import ShardedTable
@@ -72,8 +72,9 @@ def test_fused_step_matches_the_minibatch_oracle(device, rule, hy, words, use_ma
         keys, x, y = _batch(rng, n_ex, n_feat, (1 << bits) - 32)
         want_loss = _oracle_step(w, st, keys, x, y, rule, hy)
         loss.zero_()
-        lr_ops.lr_fused_step(state, u32_tensor(keys.reshape(-1), device), torch.from_numpy(x).to(device),
-                             torch.from_numpy(y).to(device), loss, rule=rule, **hy)
+        kk, xx = (np.ascontiguousarray(keys.T), np.ascontiguousarray(x.T)) if feature_major else (keys, x)
+        lr_ops.lr_fused_step(state, u32_tensor(kk.reshape(-1), device), torch.from_numpy(xx).to(device),
+                             torch.from_numpy(y).to(device), loss, rule=rule, feature_major=feature_major, **hy)
         torch.cuda.synchronize()
         c = state.counters.tolist()
         uniq = np.unique(keys[keys != 0xFFFFFFFF])
