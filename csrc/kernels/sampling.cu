@@ -26,7 +26,26 @@ neg_sample_kernel(const float* __restrict__ prob, const uint32_t* __restrict__ a
   }
 }
 
+// The step's key list in one pass: keys[0..B) = the tokens (input vectors), keys[B..2B) = token + vocab (output
+// vectors; padding stays padding). Replaces three eager framework ops (copy_, add, masked_fill_) per step.
+__global__ void __launch_bounds__(256)
+build_keys_kernel(const uint32_t* __restrict__ tokens, int64_t n, uint32_t vocab, uint32_t* __restrict__ keys) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint32_t t = __ldg(tokens + i);
+    keys[i] = t;
+    keys[n + i] = (t >= SSB_LOCKED_KEY) ? t : t + vocab;
+  }
+}
+
 }  // namespace ssb
+
+extern "C" int ssb_build_keys(const uint32_t* tokens, int64_t n, uint32_t vocab, uint32_t* keys, void* stream) {
+  if (n <= 0) return 0;
+  if (!tokens || !keys) return (int)cudaErrorInvalidValue;
+  ssb::build_keys_kernel<<<ssb::grid_for(n, 256 * 4), 256, 0, (cudaStream_t)stream>>>(tokens, n, vocab, keys);
+  SSB_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" int ssb_neg_sample(const float* prob, const uint32_t* alias, uint32_t vocab, uint64_t seed,
                               uint64_t offset, uint32_t key_offset, uint32_t* out, int64_t n, void* stream) {

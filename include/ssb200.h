@@ -191,6 +191,9 @@ int ssb_push_apply_chunks(const SsbTableView *local_view, const uint32_t *slots,
                           uint32_t tag, float lr, float eps, int32_t adagrad, uint32_t spin_limit, uint32_t *err,
                           void *stream);
 
+/* keys[0..n) = tokens, keys[n..2n) = tokens + vocab (padding 0xFFFFFFFF stays padding): the word2vec step's input and
+ * output-vector keys in one pass. */
+int ssb_build_keys(const uint32_t *tokens, int64_t n, uint32_t vocab, uint32_t *keys, void *stream);
 /* ---- K9: negative sampling (alias method, Philox4x32-10 counter RNG) ---------------------- */
 int ssb_neg_sample(const float *prob, const uint32_t *alias, uint32_t vocab, uint64_t seed,
                    uint64_t offset, uint32_t key_offset, uint32_t *out, int64_t n, void *stream);

@@ -93,6 +93,7 @@ _KERNEL_SIGS = {
     "ssb_flags_wait2": ([_vp, _i32, _u32, _u32, _vp, _vp], 1),
     "ssb_dump_compact_range": ([_vp, _vp, _vp, _u32, _i32, _u32, _u32, _vp, _vp, _vp, _vp, _u32, _i32, _vp], 1),
     "ssb_red_probe": ([_vp, _u32, _i32, _i32, _i32, _vp], 1),
+    "ssb_build_keys": ([_vp, _i64, _u32, _vp, _vp], 1),
     "ssb_neg_sample": ([_vp, _vp, _u32, _u64, _u64, _u32, _vp, _i64, _vp], 1),
     "ssb_sgns_make_pairs": ([_vp, _vp, _i64, _i32, _i32, _u64, _u64, _vp, _vp, _vp, _vp], 1),
     "ssb_sgns_tiles": ([_vp, _vp, _i32, _vp, _vp, _vp, _i64, _vp, _i32, _f32, _vp, _vp], 1),

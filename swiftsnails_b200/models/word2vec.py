@@ -169,10 +169,8 @@ class Word2VecWorker:
     def _comm(self, s, tokens):
         cfg, B = self.cfg, self.cfg.tokens_per_step
         ka = s.keys_all
-        ka[:B].copy_(tokens)                               # input keys  = w
-        torch.add(tokens, cfg.vocab, out=ka[B:2 * B])      # output keys = w + vocab
-        if self.has_padding:                               # padding tokens (0xFFFFFFFF) stay padding
-            ka[B:2 * B].masked_fill_(tokens == -1, -1)
+        # input keys = w, output keys = w + vocab (padding tokens stay padding): one kernel
+        _lib.call("ssb_build_keys", tokens.data_ptr(), B, cfg.vocab, ka.data_ptr(), _lib.stream_ptr())
         self.sampler.sample(self.n_negs, out=ka[2 * B:], key_offset=cfg.vocab)
         # K2: unique keys + inverse index (the cache has one entry per key)
         s.dedup(ka, unique=s.unique, inverse=s.inverse, n_unique=s.n_unique)
