@@ -197,12 +197,20 @@ def spawn_master(listen_addr: str, world: int, frag_num: int = 1024, extra=None,
         _build.build_core()
     conf = tempfile.NamedTemporaryFile("w", suffix=".conf", prefix="ssb200_master_", delete=False)
     conf.write("listen_addr: %s\nexpected_node_num: %d\nfrag_num: %d\ncolocated_workers: 1\nmaster_time_out: 300\n"
-               % (listen_addr, world, max(frag_num, world)))
+               "master_longest_alive_duration: 86400\n" % (listen_addr, world, max(frag_num, world)))
     for k, v in (extra or {}).items():
         conf.write("%s: %s\n" % (k, v))
     conf.close()
     log = open(log_path, "w") if log_path else subprocess.DEVNULL
-    return subprocess.Popen([exe, "-config", conf.name], stdout=log, stderr=subprocess.STDOUT)
+
+    def _die_with_parent():
+        # the master belongs to this job: if the rank that started it dies, the master must not stay behind holding
+        # the port (it would otherwise wait for WORKER_FINISH_WORK messages that never come)
+        try:
+            C.CDLL("libc.so.6", use_errno=True).prctl(1, 15)       # PR_SET_PDEATHSIG, SIGTERM
+        except OSError:
+            pass
+    return subprocess.Popen([exe, "-config", conf.name], stdout=log, stderr=subprocess.STDOUT, preexec_fn=_die_with_parent)
 
 
 def init(kind="master", master_addr=None, frag_num=1024, world=None, rank=None):
