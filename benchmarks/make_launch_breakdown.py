@@ -2,7 +2,7 @@
 """profiles/launch_breakdown.md from an `ncu --metrics gpu__time_duration.sum --csv` log of
 `bench.py --pipeline 0`: every kernel launched by the word2vec steps with its device time, aggregated
 per kernel.  Launches before the first step (table set-up, pre-population) are left out: the first
-step starts two launches before the first `neg_sample_kernel` (the two key-building element-wise ops).
+step starts one launch before the first `neg_sample_kernel` (`build_keys_kernel`).
 usage: python benchmarks/make_launch_breakdown.py gpurun_out/launches.csv [tokens_per_step]"""
 import collections
 import csv
@@ -19,7 +19,7 @@ def main():
     rows = list(csv.DictReader(lines))
     launches = [(r["Kernel Name"], float(r["Metric Value"]) / 1e3) for r in rows if r["Metric Name"] == "gpu__time_duration.sum"]
     first = next(i for i, (k, _) in enumerate(launches) if "neg_sample_kernel" in k)
-    step = launches[max(0, first - 2):]
+    step = launches[max(0, first - 1):]          # the step starts with build_keys_kernel, one launch before the sampler
     n_steps = sum(1 for k, _ in step if "sgns_block_tc_kernel" in k or "sgns_tiles_kernel" in k)
     agg = collections.OrderedDict()
     for k, us in step:
