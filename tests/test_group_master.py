@@ -61,3 +61,21 @@ def test_three_ranks_register_exchange_and_terminate_through_the_master(tmp_path
         assert (tmp_path / ("dump.%d" % r)).read_text() == "dumped"
     log = (tmp_path / "master.log").read_text()
     assert "cluster is up (3 servers" in log and "Master terminated normally" in log
+
+
+def test_own_launcher_starts_one_process_per_rank(tmp_path, native_built):
+    """`python -m swiftsnails_b200.parallel.launch_gpu N script`: RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* for every child,
+    no torch.distributed rendezvous; a failing child takes the job down with a non-zero exit."""
+    ok = tmp_path / "ok.py"
+    ok.write_text("import os, sys\nsys.path.insert(0, %r)\nfrom swiftsnails_b200.parallel import group\n"
+                  "g = group.init('master')\nv = g.all_gather_object(int(os.environ['LOCAL_RANK']))\n"
+                  "assert sorted(v) == list(range(g.world)) and g.world == 3\ng.finish(); g.close(); print('LAUNCHED_OK')\n" % ROOT)
+    env = dict(os.environ, MASTER_PORT=str(_free_port() - 17))
+    p = subprocess.run([sys.executable, "-m", "swiftsnails_b200.parallel.launch_gpu", "3", str(ok)], capture_output=True, text=True,
+                       timeout=180, cwd=ROOT, env=env)
+    assert p.returncode == 0 and p.stdout.count("LAUNCHED_OK") == 3, p.stdout[-1500:] + p.stderr[-1500:]
+    bad = tmp_path / "bad.py"
+    bad.write_text("import os, sys, time\nif os.environ['RANK'] == '1': sys.exit(7)\ntime.sleep(60)\n")
+    p = subprocess.run([sys.executable, "-m", "swiftsnails_b200.parallel.launch_gpu", "3", str(bad)], capture_output=True, text=True,
+                       timeout=60, cwd=ROOT, env=env)
+    assert p.returncode == 7
