@@ -182,3 +182,60 @@ def sgns_block_ref(params, inv_in, inv_out, neg_idx, sent_len, window, seed, off
         ok_n = torch.from_numpy(neg_ok).to(dev)
         grads.index_add_(0, torch.from_numpy(np.where(neg_ok, negs, 0)).to(dev).long()[ok_n], d_neg[ok_n])
     return grads, loss, n_pairs
+
+
+def sgns_block_ref_batched(params, inv_in, inv_out, neg_idx, sent_len, window, seed, offset, neg_k, tile=128, halo=8, n_neg=16,
+                           chunk_tiles=1024):
+    """The same block-formulation SGNS step as :func:`sgns_block_ref`, all tiles at once with batched fp32 matmuls on
+    ``params.device`` (the loop version takes a Python iteration per tile). ``inv_in`` / ``inv_out`` / ``neg_idx``: int64
+    torch tensors on the device (EMPTY = invalid). Returns (grads, loss_sum, n_pairs). Used by
+    benchmarks/precision_parity.py for the fp32 arm at full size; tests/test_reference_batched.py checks it against the loop."""
+    dev = params.device
+    params = params.detach().to(torch.float32)
+    n_tok = int(inv_in.numel())
+    n_tiles = (n_tok + tile - 1) // tile
+    grads = torch.zeros_like(params)
+    r0 = philox4x32(seed, np.arange(n_tok, dtype=np.uint64) + np.uint64(offset))[:, 0]
+    eff_all = torch.from_numpy((window - (r0 % np.uint32(window)).astype(np.int64))).to(dev)
+    pad = n_tiles * tile - n_tok
+    inv_in_p = torch.cat([inv_in, torch.full((pad,), EMPTY, dtype=torch.int64, device=dev)]) if pad else inv_in
+    eff_p = torch.cat([eff_all, torch.zeros(pad, dtype=torch.int64, device=dev)]) if pad else eff_all
+    loss_sum = torch.zeros((), dtype=torch.float64, device=dev)
+    n_pairs = torch.zeros((), dtype=torch.int64, device=dev)
+    W = tile + 2 * halo
+    for t0 in range(0, n_tiles, chunk_tiles):
+        t1 = min(t0 + chunk_tiles, n_tiles)
+        T = t1 - t0
+        tt = torch.arange(t0, t1, device=dev)
+        rows = tt[:, None] * tile + torch.arange(tile, device=dev)[None, :]                   # [T, tile] token positions
+        ctx_tok = tt[:, None] * tile - halo + torch.arange(W, device=dev)[None, :]            # [T, W]
+        in_rows = inv_in_p[rows]
+        in_ok = in_rows != EMPTY
+        ctx_in = (ctx_tok >= 0) & (ctx_tok < n_tok)
+        ctx_rows = torch.where(ctx_in, inv_out[ctx_tok.clamp(0, n_tok - 1)], torch.full_like(ctx_tok, EMPTY))
+        ctx_ok = ctx_in & (ctx_rows != EMPTY)
+        rel = ctx_tok[:, None, :] - rows[:, :, None]                                           # [T, tile, W]
+        mask = (rel != 0) & (rel.abs() <= eff_p[rows][:, :, None]) & ctx_ok[:, None, :] & \
+               ((ctx_tok[:, None, :] // sent_len) == (rows[:, :, None] // sent_len)) & in_ok[:, :, None]
+        mt = mask.to(torch.float32)
+        negs = neg_idx[t0 * n_neg:t1 * n_neg].view(T, n_neg)
+        neg_ok = negs != EMPTY
+        a = params[torch.where(in_ok, in_rows, torch.zeros_like(in_rows))]                     # [T, tile, D]
+        c = params[torch.where(ctx_ok, ctx_rows, torch.zeros_like(ctx_rows))]                  # [T, W, D]
+        ng = params[torch.where(neg_ok, negs, torch.zeros_like(negs))]                         # [T, n_neg, D]
+        s_pos = torch.bmm(a, c.transpose(1, 2))
+        s_neg = torch.bmm(a, ng.transpose(1, 2))
+        m_i = mt.sum(2)
+        w = (m_i * (neg_k / n_neg))[:, :, None] * neg_ok[:, None, :].to(torch.float32)
+        g_pos = (torch.sigmoid(s_pos) - 1.0) * mt
+        g_neg = w * torch.sigmoid(s_neg)
+        loss_sum += (torch.nn.functional.softplus(-s_pos) * mt).double().sum() + (w * torch.nn.functional.softplus(s_neg)).double().sum()
+        n_pairs += mask.sum()
+        d_in = torch.bmm(g_pos, c) + torch.bmm(g_neg, ng)
+        d_ctx = torch.bmm(g_pos.transpose(1, 2), a)
+        d_neg = torch.bmm(g_neg.transpose(1, 2), a)
+        D = params.shape[1]
+        grads.index_add_(0, in_rows[in_ok], d_in[in_ok].reshape(-1, D))
+        grads.index_add_(0, ctx_rows[ctx_ok], d_ctx[ctx_ok].reshape(-1, D))
+        grads.index_add_(0, negs[neg_ok], d_neg[neg_ok].reshape(-1, D))
+    return grads, float(loss_sum.item()), int(n_pairs.item())
