@@ -264,7 +264,7 @@ pull_kernel(const __grid_constant__ SsbTableView v, const uint32_t* __restrict__
   }
 }
 
-// ---- pull, bulk-copy form (opt-in: SSB200_PULL_BULK=1) -----------------------------------------
+// ---- pull, bulk-copy form (default for bf16-mirror pulls; SSB200_PULL_BULK=0/1 forces) ------------
 // The kernel above keeps every row it is waiting for in registers (a float4 per lane per key), and its
 // per-key state caps a warp at kPullK = 4 rows in flight: 128 rows per SM at 64 registers, which is what
 // bounds it (its time scales with 1 / resident warps: 3.7 TB/s of 6.5). Here a LANE resolves one key
@@ -914,8 +914,14 @@ int ssb_pull_cached(const SsbTableView* view, const uint32_t* keys, int64_t n, c
     return (int)cudaErrorInvalidValue;
   if (n <= 0) return 0;
   ssb::PullArgs a{0u, gslot, rows_out, (__nv_bfloat16*)rows_bf16, grads_zero, insert, stats, (unsigned long long*)slot_cache, cache_bits};
-  static const int use_bulk = [] { const char* e = getenv("SSB200_PULL_BULK"); return e ? atoi(e) : 0; }();
+  // Which pull kernel: the bulk-copy form (rows travel by cp.async.bulk into shared memory, no registers held while
+  // they are in flight) is the default for bf16-mirror pulls — the training step's pull. Alone it is no faster than
+  // the register form (168 vs 161 us at 2 GPUs), but next to the tensor-core kernel of the previous step, whose
+  // reductions keep the load/store units busy, the whole pipelined step is: 0.474 vs 0.507 ms on one GPU, 0.577 vs
+  // 0.590 on two. SSB200_PULL_BULK=0 / 1 forces one form for every pull.
+  static const int bulk_env = [] { const char* e = getenv("SSB200_PULL_BULK"); return e ? atoi(e) : -1; }();
   const bool from_shadow = !rows_out && rows_bf16 && view->shadow[0] != nullptr;
+  const int use_bulk = bulk_env >= 0 ? bulk_env : (from_shadow ? 1 : 0);
   const uint32_t row_bytes = (uint32_t)view->dim * (from_shadow ? 2u : 4u);
   if (use_bulk && (rows_out || rows_bf16) && (view->dim & 3) == 0 && row_bytes % 16 == 0 && row_bytes <= 512) {
     const size_t smem = (size_t)ssb::kBulkWarps * 32 * row_bytes + 64;
