@@ -58,7 +58,8 @@ def _run_cluster(rr, wd, roles):
     return out
 
 
-@pytest.mark.parametrize("mix", ["ref-ref-ours", "ours-ref-ours", "ref-ours-ours", "ours-ours-ref", "ref-ours-ref", "ours-ref-ref"])
+@pytest.mark.parametrize("mix", ["ref-ref-ours", "ours-ref-ours", "ref-ours-ours", "ours-ours-ref", "ref-ours-ref", "ours-ref-ref",
+                                 "ours-ours-ours"])          # the last one: this core alone, speaking the reference's pull form
 def test_mixed_cluster_runs_to_completion(ref_bin, tmp_path, mix):
     m, s, w = mix.split("-")
     res = _run_cluster(ref_bin, str(tmp_path), {"master": m, "server": s, "worker": w})
