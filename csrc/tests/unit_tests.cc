@@ -7,6 +7,7 @@
 #include <fstream>
 #include <set>
 #include "../core/swiftsnails.h"
+#include "../../include/ssb200_core.h"
 
 using namespace ssb;
 
@@ -358,6 +359,42 @@ TEST(transfer_reply_to_not_yet_routed_requester) {
   EXPECT(ok.load() == 8);
   worker.shutdown();
   server.shutdown();
+}
+
+TEST(dump_text_with_state_words_roundtrip) {  // Param-style lines: row + every optimizer-state word (AdaGrad 1, FTRL 2)
+  const int n = 5, dim = 3, sdim = 6;
+  std::vector<uint32_t> keys = {7, 11, 4000000000u, 0, 42};
+  std::vector<float> rows(n * dim), state(n * sdim);
+  for (int i = 0; i < n * dim; ++i) rows[i] = 0.1f * (float)i - 0.7f;
+  for (int i = 0; i < n * sdim; ++i) state[i] = 1.0f / (float)(i + 1);
+  const std::string path = "/tmp/ssb200_unit_dump3.txt";
+  EXPECT(ssb_dump_write_text3(path.c_str(), keys.data(), rows.data(), state.data(), n, dim, sdim, 0, 9) == n);
+  std::vector<uint32_t> k2(n);
+  std::vector<float> r2(n * dim), s2(n * sdim);
+  int has = 0;
+  EXPECT(ssb_dump_read_text3(path.c_str(), k2.data(), r2.data(), s2.data(), n, dim, sdim, &has) == n);
+  EXPECT(has == 1 && k2 == keys && r2 == rows && s2 == state);                  // 9 digits: exact float round trip
+  // the reference's plain form (no state) is read by the same reader, state comes back as zeros
+  EXPECT(ssb_dump_write_text3(path.c_str(), keys.data(), rows.data(), nullptr, n, dim, sdim, 0, 6) == n);
+  EXPECT(ssb_dump_read_text3(path.c_str(), k2.data(), r2.data(), s2.data(), n, dim, sdim, &has) == n);
+  EXPECT(has == 0 && k2 == keys && s2[0] == 0.f && std::fabs(r2[4] - rows[4]) < 1e-5f);
+  std::remove(path.c_str());
+}
+
+TEST(lr_example_file_parser) {  // `label key:value ...`, the CPU lr app's format, into padded arrays for the GPU step
+  const std::string path = "/tmp/ssb200_unit_lr.txt";
+  { std::ofstream f(path); f << "1 3:0.5 7 9:2\n# comment\n\n-1 100001:1.5\n0 1 2 3 4 5\n"; }
+  long long stats[2] = {0, 0};
+  EXPECT(ssb_lr_parse_file(path.c_str(), 4, nullptr, nullptr, nullptr, 0, 100000, 1, 0, stats) == 3);
+  std::vector<uint32_t> k(3 * 4);
+  std::vector<float> v(3 * 4), y(3);
+  EXPECT(ssb_lr_parse_file(path.c_str(), 4, k.data(), v.data(), y.data(), 3, 100000, 1, 0, stats) == 3);
+  EXPECT(y[0] == 1.f && y[1] == 0.f && y[2] == 0.f);
+  EXPECT(k[0] == 3 && v[0] == 0.5f && k[1] == 7 && v[1] == 1.f && k[2] == 9 && v[2] == 2.f && k[3] == 0xFFFFFFFFu);
+  EXPECT(k[4] == 1 && v[4] == 1.5f && k[5] == 0xFFFFFFFFu);                      // 100001 % 100000
+  EXPECT(k[8] == 1 && k[11] == 4 && stats[1] == 1);                              // the fifth feature of line 3 is dropped
+  EXPECT(ssb_lr_parse_file(path.c_str(), 4, nullptr, nullptr, nullptr, 0, 0, 2, 1, stats) == 1);   // worker 1 of 2: line index 1
+  std::remove(path.c_str());
 }
 
 int main(int argc, char** argv) {
